@@ -1,0 +1,26 @@
+# Top-level build: the product's CUDA libraries (sm_100a only) and, via oracle/Makefile, the test
+# oracles and (in the build container) the reference baselines.  `python -c "import
+# __graft_entry__ as g; g.build()"` runs exactly this.
+NVCC  ?= /usr/local/cuda/bin/nvcc
+ARCH  := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
+PKG   := cuda_pathtracer_b200
+CSRC  := $(PKG)/csrc
+
+SC_SRCS := $(CSRC)/sc_kernels.cu $(CSRC)/sc_api.cu
+SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/lookback.cuh include/b200_sc.h
+
+.PHONY: all lib oracle clean
+all: lib oracle
+
+lib: $(PKG)/libb200sc.so
+
+$(PKG)/libb200sc.so: $(SC_SRCS) $(SC_HDRS)
+	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(SC_SRCS)
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -f $(PKG)/*.so
+	$(MAKE) -C oracle clean

@@ -1,0 +1,39 @@
+// sc_kernels.cuh -- internal launcher interface between sc_kernels.cu (device code) and
+// sc_api.cu (the C ABI of include/b200_sc.h).  Not part of the public boundary.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+constexpr int SC_THREADS = 256;                       // 8 warps per CTA
+constexpr int SC_VEC = 4;                             // int4 loads per thread
+constexpr int SC_ITEMS = SC_VEC * 4;                  // 16 ints per thread
+constexpr int SC_TILE = SC_THREADS * SC_ITEMS;        // 4096 ints = 16 KB per tile
+
+inline unsigned sc_num_tiles(unsigned n) { return (n + SC_TILE - 1) / SC_TILE; }
+
+// Single-pass decoupled look-back exclusive scan (B4/B6 replacement).  desc: >= num_tiles words,
+// zero at allocation; tickets: 2 unsigned, zero at allocation; epoch: bumped per launch.
+cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
+                                 unsigned* tickets, unsigned epoch, const int* d_seed, int* d_total,
+                                 cudaStream_t s);
+
+// Single-pass compaction: keep in[i] != 0, order preserving (B5 replacement).
+cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
+                                    unsigned* tickets, unsigned epoch, int* d_count, cudaStream_t s);
+
+// Work-efficient three-phase scan pieces: per-tile reduce (up-sweep) and per-tile scan with a
+// tile offset (down-sweep).  tile_offsets == nullptr => single tile, offset 0.
+cudaError_t launch_reduce_tiles(const int* d_in, unsigned n, int* d_tile_sums, cudaStream_t s);
+cudaError_t launch_downsweep(const int* d_in, int* d_out, unsigned n, const int* d_tile_offsets,
+                             const int* d_seed, int* d_total, cudaStream_t s);
+
+// Naive Hillis-Steele pass and the inclusive->exclusive shift (B3 replacement).
+cudaError_t launch_naive_pass(unsigned n, unsigned offset, int* d_out, const int* d_in, cudaStream_t s);
+cudaError_t launch_naive_shift(unsigned n, int* d_out, const int* d_incl, const int* d_seed,
+                               int* d_total, cudaStream_t s);
+
+// Whole-array sum into *d_total (must be zero on entry).
+cudaError_t launch_reduce_total(const int* d_in, unsigned n, int* d_total, int num_sms, cudaStream_t s);
+
+}  // namespace b200

@@ -1,0 +1,86 @@
+// TEST / BASELINE INFRASTRUCTURE -- not product code.
+//
+// Times the reference's own GPU scan/compact variants (Naive, Efficient, Thrust:
+// stream_compaction/stream_compaction/{naive,efficient,thrust}.cu, unmodified, compiled
+// from /root/reference by oracle/Makefile) at a size given on the command line.  The
+// reference's harness hard-codes SIZE = 1 << 28 (stream_compaction/src/main.cpp:8); this
+// driver follows the same sequence (main.cpp:22-140): genArray -> CPU result is the truth
+// -> each GPU variant compared element-wise -> the variant's own timer() printed.
+// Data generator is the reference's (testing_helpers.hpp:52-58) with a FIXED seed.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stream_compaction/cpu.h>
+#include <stream_compaction/naive.h>
+#include <stream_compaction/efficient.h>
+#include <stream_compaction/thrust.h>
+
+static int cmp(int n, const int* a, const int* b)
+{
+    for (int i = 0; i < n; ++i) if (a[i] != b[i]) return 1;
+    return 0;
+}
+
+static void gen(int n, int* a, int maxval, unsigned seed)
+{
+    srand(seed);
+    for (int i = 0; i < n; ++i) a[i] = rand() % maxval;
+}
+
+int main(int argc, char** argv)
+{
+    int lg = argc > 1 ? atoi(argv[1]) : 20;
+    int npot_delta = argc > 2 ? atoi(argv[2]) : 0;     // 3 => n = 2^lg - 3
+    int skip_naive = argc > 3 ? atoi(argv[3]) : 0;
+    const int SIZE = 1 << lg;
+    const int n = SIZE - npot_delta;
+    int* a = new int[SIZE];
+    int* b = new int[SIZE];
+    int* c = new int[SIZE];
+
+    gen(SIZE - 1, a, 50, 565u);
+    a[SIZE - 1] = 0;
+    StreamCompaction::CPU::scan(n, b, a);
+    float cpu_scan_ms = StreamCompaction::CPU::timer().getCpuElapsedTimeForPreviousOperation();
+
+    float naive_ms = -1.f, eff_ms = -1.f, thrust_ms = -1.f;
+    int ok_naive = -1, ok_eff, ok_thrust;
+    if (!skip_naive) {
+        memset(c, 0, sizeof(int) * SIZE);
+        StreamCompaction::Naive::scan(n, c, a);
+        naive_ms = StreamCompaction::Naive::timer().getGpuElapsedTimeForPreviousOperation();
+        ok_naive = !cmp(n, b, c);
+    }
+    // warm-up + measured (the reference harness has no warm-up; we report the 2nd call)
+    for (int rep = 0; rep < 2; ++rep) {
+        memset(c, 0, sizeof(int) * SIZE);
+        StreamCompaction::Efficient::scan(n, c, a);
+        eff_ms = StreamCompaction::Efficient::timer().getGpuElapsedTimeForPreviousOperation();
+    }
+    ok_eff = !cmp(n, b, c);
+    for (int rep = 0; rep < 2; ++rep) {
+        memset(c, 0, sizeof(int) * SIZE);
+        StreamCompaction::Thrust::scan(n, c, a);
+        thrust_ms = StreamCompaction::Thrust::timer().getGpuElapsedTimeForPreviousOperation();
+    }
+    ok_thrust = !cmp(n, b, c);
+
+    gen(SIZE - 1, a, 4, 565u);
+    a[SIZE - 1] = 0;
+    memset(b, 0, sizeof(int) * SIZE);
+    int expected = StreamCompaction::CPU::compactWithoutScan(n, b, a);
+    float cpu_compact_ms = StreamCompaction::CPU::timer().getCpuElapsedTimeForPreviousOperation();
+    memset(c, 0, sizeof(int) * SIZE);
+    int count = StreamCompaction::Efficient::compact(n, c, a);
+    float compact_inner_scan_ms = StreamCompaction::Efficient::timer().getGpuElapsedTimeForPreviousOperation();
+    int ok_compact = (count == expected) && !cmp(count, b, c);
+
+    printf("{\"impl\": \"reference_cuda_scan\", \"n\": %d, \"cpu_scan_ms\": %.4f, \"naive_ms\": %.4f, "
+           "\"efficient_ms\": %.4f, \"thrust_ms\": %.4f, \"cpu_compact_ms\": %.4f, "
+           "\"efficient_compact_inner_scan_ms\": %.4f, \"ok\": {\"naive\": %d, \"efficient\": %d, "
+           "\"thrust\": %d, \"compact\": %d}}\n",
+           n, cpu_scan_ms, naive_ms, eff_ms, thrust_ms, cpu_compact_ms, compact_inner_scan_ms,
+           ok_naive, ok_eff, ok_thrust, ok_compact);
+    delete[] a; delete[] b; delete[] c;
+    return 0;
+}

@@ -1,0 +1,78 @@
+"""ctypes access to the CPU oracles under oracle/ -- for tests ONLY (and bench.py's cpu_baseline).
+
+oracle/_build/*.so are built by `make oracle` (gcc/g++, no GPU needed).  oracle/_ref/*.so are the
+reference's own sources compiled from /root/reference in the build container; they may be absent
+elsewhere, in which case the committed golden vectors are the pin.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE = os.path.join(REPO, "oracle")
+
+
+def _ensure_built(rel):
+    path = os.path.join(ORACLE, rel)
+    if not os.path.exists(path) and rel.startswith("_build/"):
+        subprocess.run(["make", "-s", "-C", ORACLE, "own"], check=True)
+    return path
+
+
+def _iptr(a):
+    assert a.dtype == np.int32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+
+
+class ScOracle:
+    """oracle/sc_oracle.c (restatement of reference cpu.cu) or the reference's cpu.cu itself."""
+
+    def __init__(self, reference=False):
+        if reference:
+            path = os.path.join(ORACLE, "_ref", "libref_sc_cpu.so")
+            if not os.path.exists(path):
+                raise FileNotFoundError(path)
+            self.lib = ctypes.CDLL(path)
+            self._scan = self.lib.ref_cpu_scan
+            self._cwo = self.lib.ref_cpu_compact_without_scan
+            self._cws = self.lib.ref_cpu_compact_with_scan
+            self.lib.ref_cpu_last_ms.restype = ctypes.c_float
+        else:
+            self.lib = ctypes.CDLL(_ensure_built("_build/liboracle_sc.so"))
+            self._scan = self.lib.oracle_scan
+            self._cwo = self.lib.oracle_compact_without_scan
+            self._cws = self.lib.oracle_compact_with_scan
+        self.reference = reference
+
+    def scan(self, a):
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        o = np.zeros_like(a)
+        self._scan(ctypes.c_int(a.size), _iptr(o), _iptr(a))
+        return o
+
+    def compact_without_scan(self, a):
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        o = np.zeros_like(a)
+        n = self._cwo(ctypes.c_int(a.size), _iptr(o), _iptr(a))
+        return o[:n].copy()
+
+    def compact_with_scan(self, a):
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        o = np.zeros_like(a)
+        n = self._cws(ctypes.c_int(a.size), _iptr(o), _iptr(a))
+        return o[:n].copy()
+
+    def last_ms(self):
+        return float(self.lib.ref_cpu_last_ms()) if self.reference else None
+
+
+def gen_array(n_pot, maxval, seed=565):
+    """The harness's input (stream_compaction/src/main.cpp:22-23,97-98 with testing_helpers.hpp:52-58):
+    n_pot-1 values glibc rand() % maxval after srand(seed), last element forced to 0."""
+    lib = ctypes.CDLL(_ensure_built("_build/liboracle_sc.so"))
+    a = np.zeros(n_pot, dtype=np.int32)
+    if n_pot > 1:
+        lib.oracle_gen_array(ctypes.c_int(n_pot - 1), _iptr(a), ctypes.c_int(maxval), ctypes.c_uint(seed))
+    return a

@@ -1,0 +1,191 @@
+"""GPU parity tests of the scan / compact library, through the C ABI (include/b200_sc.h).
+
+Mirrors the reference's self-checking harness (stream_compaction/src/main.cpp:29-140): the CPU
+result is the truth, every GPU variant is compared element-wise, POT and NPOT (= POT-3), last POT
+element 0.  The bar is BIT-EXACT (int32, two's-complement wrap).  Full-size cases (2^28) use the
+numpy closed form of the same definition (exclusive cumsum mod 2^32; x[x != 0]) which
+test_oracle_sc.py ties to the oracle and the reference's golden vectors."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle_bindings import ScOracle, gen_array
+
+pytestmark = pytest.mark.gpu
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "sc_golden.npz"))
+
+
+@pytest.fixture(scope="module")
+def sc():
+    from cuda_pathtracer_b200 import stream_compaction as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    return ScOracle()
+
+
+def np_exclusive_scan(a):
+    c = np.cumsum(a.astype(np.int64))
+    out = np.empty(a.size, dtype=np.int64)
+    out[0:1] = 0
+    out[1:] = c[:-1]
+    return out.astype(np.uint64).astype(np.uint32).view(np.int32)
+
+
+VARIANTS = ["Naive", "Efficient", "Thrust"]
+SIZES = [1, 2, 3, 4, 5, 31, 32, 33, 63, 64, 65, 255, 256, 257, 4095, 4096, 4097, 8191, 12289,
+         (1 << 16) - 3, 1 << 16, (1 << 20) - 3, 1 << 20]
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("n", SIZES)
+def test_scan_vs_oracle(sc, oracle, variant, n):
+    pot = 1 << int(np.ceil(np.log2(max(n, 2))))
+    a = gen_array(pot, 50)[:n].copy()
+    o = np.full(n, -7, dtype=np.int32)
+    getattr(sc, variant).scan(n, o, a)
+    assert np.array_equal(o, oracle.scan(a))
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_compact_vs_oracle(sc, oracle, n):
+    pot = 1 << int(np.ceil(np.log2(max(n, 2))))
+    a = gen_array(pot, 4)[:n].copy()
+    want = oracle.compact_without_scan(a)
+    o = np.full(n, -7, dtype=np.int32)
+    cnt = sc.Efficient.compact(n, o, a)
+    assert cnt == want.size
+    assert np.array_equal(o[:cnt], want)
+    assert np.all(o[cnt:] == -7)          # nothing written past the count
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_golden_vectors(sc, variant):
+    a = GOLD["scan_in"]
+    for src, want in ((a, GOLD["scan_pot"]), (a[:-3].copy(), GOLD["scan_npot"]),
+                      (GOLD["wrap_in"], GOLD["wrap_scan"])):
+        o = np.zeros_like(src)
+        getattr(sc, variant).scan(src.size, o, src)
+        assert np.array_equal(o, want)
+    b = GOLD["compact_in"]
+    for src, want in ((b, GOLD["compact_pot"]), (b[:-3].copy(), GOLD["compact_npot"])):
+        o = np.zeros_like(src)
+        cnt = sc.Efficient.compact(src.size, o, src)
+        assert cnt == want.size and np.array_equal(o[:cnt], want)
+
+
+def test_edge_cases(sc):
+    e = np.zeros(0, dtype=np.int32)
+    sc.Thrust.scan(0, e, e)
+    assert sc.Efficient.compact(0, e, e) == 0
+    z = np.zeros(10000, dtype=np.int32)
+    o = np.ones_like(z)
+    assert sc.Efficient.compact(z.size, o, z) == 0            # everything removed
+    ones = np.ones(10000, dtype=np.int32)
+    assert sc.Efficient.compact(ones.size, o, ones) == 10000  # nothing removed
+    assert np.array_equal(o, ones)
+    for v in VARIANTS:
+        getattr(sc, v).scan(ones.size, o, ones)
+        assert np.array_equal(o, np.arange(10000, dtype=np.int32))
+    neg = np.array([5, -3, 0, 7, -2**31, 1], dtype=np.int32)   # negatives are "non-zero"
+    o = np.zeros_like(neg)
+    assert sc.Efficient.compact(neg.size, o, neg) == 5
+    assert np.array_equal(o[:5], neg[neg != 0])
+
+
+def test_unaligned_pointers(sc, oracle):
+    """host arrays at 4-byte (not 16-byte) alignment, and device pointers at odd offsets"""
+    import torch
+    base = gen_array(1 << 14, 50)
+    a = base[1:9001]
+    assert a.ctypes.data % 16 != 0
+    o = np.zeros(9000, dtype=np.int32)
+    sc.Thrust.scan(9000, o, np.ascontiguousarray(a))
+    assert np.array_equal(o, oracle.scan(a))
+    d = torch.from_numpy(base).cuda()
+    dout = torch.zeros(1 << 14, dtype=torch.int32, device="cuda")
+    for v in VARIANTS:
+        dout.zero_()
+        getattr(sc, v).scan(9000, dout[3:], d[1:])             # device pointers, both misaligned
+        torch.cuda.synchronize()
+        assert np.array_equal(dout[3:9003].cpu().numpy(), oracle.scan(base[1:9001]))
+    dout.zero_()
+    cnt = sc.Efficient.compact(9000, dout[1:], d[5:])
+    want = oracle.compact_without_scan(base[5:9005])
+    assert cnt == want.size and np.array_equal(dout[1:1 + cnt].cpu().numpy(), want)
+
+
+def test_device_ctx_seed_total_and_reduce(sc):
+    import torch
+    ctx = sc.Context()
+    n = (1 << 18) + 5
+    a = torch.randint(-1000, 1000, (n,), dtype=torch.int32, device="cuda")
+    out = torch.empty_like(a)
+    seed = torch.tensor([123456], dtype=torch.int32, device="cuda")
+    total = torch.zeros(1, dtype=torch.int32, device="cuda")
+    want = np_exclusive_scan(a.cpu().numpy())
+    for variant in (sc.LOOKBACK, sc.EFFICIENT, sc.NAIVE):
+        out.zero_(); total.zero_()
+        ctx.scan(n, out, a, variant, d_seed=seed, d_total=total)
+        torch.cuda.synchronize()
+        assert ctx.last_launches() >= 1
+        assert np.array_equal(out.cpu().numpy(), (want.astype(np.int64) + 123456).astype(np.int32))
+        assert int(total.item()) == int(np.int32(np.int64(a.sum().item()) + 123456))
+    ctx.reduce(n, a, total)
+    torch.cuda.synchronize()
+    assert int(total.item()) == int(a.sum().item())
+    ctx.close()
+
+
+def test_repeated_launches_reuse_workspace(sc):
+    """descriptor epochs: many back-to-back launches of different sizes on one context"""
+    import torch
+    ctx = sc.Context()
+    rng = np.random.RandomState(1)
+    for _ in range(40):
+        n = int(rng.randint(1, 300000))
+        a = torch.randint(0, 4, (n,), dtype=torch.int32, device="cuda")
+        out = torch.empty_like(a)
+        cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ctx.scan(n, out, a)
+        ctx.compact(n, out, a, cnt)
+        torch.cuda.synchronize()
+        h = a.cpu().numpy()
+        k = int(cnt.item())
+        assert k == int((h != 0).sum())
+        assert np.array_equal(out[:k].cpu().numpy(), h[h != 0])
+    ctx.close()
+
+
+@pytest.mark.parametrize("delta", [0, 3])
+def test_full_size_2p28(sc, delta):
+    """BASELINE size (2^28, and 2^28-3): bit-exact against the closed form, data resident on the
+    device (torch RNG instead of glibc rand so the test stays fast); int32 wrap exercised because
+    the running sum passes 2^31."""
+    import torch
+    n = (1 << 28) - delta
+    g = torch.Generator(device="cuda").manual_seed(565)
+    a = torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda", generator=g)
+    a[-1] = 0
+    out = torch.empty_like(a)
+    ctx = sc.Context()
+    want = torch.cumsum(a, 0, dtype=torch.int64)
+    want = (want - a).to(torch.int32)                 # exclusive, wraps like int32
+    for variant in (sc.LOOKBACK, sc.EFFICIENT):
+        out.zero_()
+        ctx.scan(n, out, a, variant)
+        torch.cuda.synchronize()
+        assert torch.equal(out, want)
+    del want
+    b = a % 4
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ctx.compact(n, out, b, cnt)
+    torch.cuda.synchronize()
+    keep = b[b != 0]
+    assert int(cnt.item()) == keep.numel()
+    assert torch.equal(out[: keep.numel()], keep)
+    ctx.close()
