@@ -13,10 +13,16 @@ SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/lookback.cuh include/b200_sc.h
 .PHONY: all lib oracle clean
 all: lib oracle
 
-lib: $(PKG)/libb200sc.so
+PT_SRCS := $(CSRC)/pt_kernels.cu $(CSRC)/pt_api.cu
+PT_HDRS := $(CSRC)/pt_kernels.cuh $(CSRC)/pt_math.cuh $(CSRC)/pt_shade.cuh $(CSRC)/lookback.cuh include/b200_pt.h
+
+lib: $(PKG)/libb200sc.so $(PKG)/libb200pt.so
 
 $(PKG)/libb200sc.so: $(SC_SRCS) $(SC_HDRS)
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(SC_SRCS)
+
+$(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS)
+	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(PT_SRCS)
 
 oracle:
 	$(MAKE) -C oracle all

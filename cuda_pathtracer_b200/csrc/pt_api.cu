@@ -1,0 +1,334 @@
+// pt_api.cu -- the C ABI of include/b200_pt.h on top of the kernels in pt_kernels.cu.
+//
+// Host-side mirror of the reference's render driver (path_tracer/src/pathtrace.cu:113-177 init /
+// free, :423-528 the per-iteration loop) without its per-bounce host work: no cudaMalloc / stream
+// create / cudaDeviceSynchronize / D2H inside the loop; the live-path count of every bounce stays
+// in device memory and `depth` bounce kernels are simply enqueued (tiles past the live range
+// exit at once).  Several iterations are traced concurrently as independent batch slots of the
+// same launches (each slot compacts in its own index space, so the per-(iteration, slot-index,
+// depth) seeds -- and therefore the random paths -- are exactly the reference's).
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/b200_pt.h"
+#include "pt_kernels.cuh"
+
+using namespace ptk;
+
+enum { B200_OK = 0, B200_E_BADARG = 10001, B200_E_NODEVICE = 10002, B200_E_NOMEM = 10003, B200_E_UNSUPPORTED = 10004 };
+
+struct b200pt {
+    int device = 0;
+    int W = 0, H = 0, P = 0, depth = 0, tiles = 0;
+    int n_prims = 0, n_mats = 0;
+    CamRec cam{};
+    b200pt_options opt{};
+    int batch_cap = 0;                 // allocated batch slots
+    PrimRec* d_prims = nullptr;
+    MatRec* d_mats = nullptr;
+    float4* d_pool = nullptr;          // 2 pools x 3 arrays x batch_cap x P
+    int* d_counts = nullptr;           // (depth + 1) x batch_cap
+    unsigned long long* d_desc = nullptr;
+    unsigned long long* d_segments = nullptr;
+    float* d_image = nullptr;
+    unsigned epoch = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint64_t iterations = 0, launches = 0;
+    float last_ms = 0.f;
+    int last_batch = 0;
+};
+
+namespace {
+
+#define CK(x)                                    \
+    do {                                         \
+        cudaError_t e__ = (x);                   \
+        if (e__ != cudaSuccess) return (int)e__; \
+    } while (0)
+
+int dev_alloc(void** p, size_t bytes)
+{
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? B200_E_NOMEM : (int)e; }
+    return 0;
+}
+
+// struct Geom -> PrimRec: keep rows 0..2 of the three column-major matrices
+void pack_prim(const b200pt_geom& g, PrimRec& r)
+{
+    for (int c = 0; c < 4; ++c)
+        for (int row = 0; row < 3; ++row) {
+            r.inv[c * 3 + row] = g.inverseTransform[c * 4 + row];
+            r.fwd[c * 3 + row] = g.transform[c * 4 + row];
+            r.itr[c * 3 + row] = g.invTranspose[c * 4 + row];
+        }
+    r.type = g.type;
+    r.material = g.materialid;
+    r.pad0 = r.pad1 = 0;
+}
+
+int default_batch(int P)
+{
+    int b = (int)((4u << 20) / (unsigned)(P > 0 ? P : 1));
+    if (b < 1) b = 1;
+    if (b > 16) b = 16;
+    return b;
+}
+
+int ensure_batch(b200pt* h, int batch)
+{
+    if (batch <= h->batch_cap) return 0;
+    cudaFree(h->d_pool); cudaFree(h->d_counts); cudaFree(h->d_desc);
+    h->d_pool = nullptr; h->d_counts = nullptr; h->d_desc = nullptr; h->batch_cap = 0;
+    int r = dev_alloc((void**)&h->d_pool, sizeof(float4) * 6 * (size_t)batch * h->P);
+    if (r) return r;
+    r = dev_alloc((void**)&h->d_counts, sizeof(int) * (size_t)(h->depth + 1) * batch);
+    if (r) return r;
+    r = dev_alloc((void**)&h->d_desc, sizeof(unsigned long long) * (size_t)batch * h->tiles);
+    if (r) return r;
+    CK(cudaMemset(h->d_counts, 0, sizeof(int) * (size_t)(h->depth + 1) * batch));
+    CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->tiles));
+    h->epoch = 0;
+    h->batch_cap = batch;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+void b200pt_default_options(b200pt_options* o)
+{
+    if (!o) return;
+    o->russian_roulette = 1;      // utilities.h:23-33
+    o->sort_by_material = 0;
+    o->ssaa = 1;
+    o->dof = 1;
+    o->aperture = 0.1f;
+    o->focal_len = 10.0f;
+    o->first_bounce_cache = 0;
+    o->batch = 0;
+}
+
+int b200pt_create(const b200pt_scene* sc, b200pt** out)
+{
+    if (!sc || !out || !sc->geoms || !sc->materials || sc->n_geoms <= 0 || sc->n_materials <= 0) return B200_E_BADARG;
+    if (sc->camera.resolution[0] <= 0 || sc->camera.resolution[1] <= 0 || sc->trace_depth <= 0 || sc->trace_depth > 511)
+        return B200_E_BADARG;
+    for (int i = 0; i < sc->n_geoms; ++i) {
+        if (sc->geoms[i].type != B200PT_SPHERE && sc->geoms[i].type != B200PT_CUBE) return B200_E_UNSUPPORTED;
+        if (sc->geoms[i].materialid < 0 || sc->geoms[i].materialid >= sc->n_materials) return B200_E_BADARG;
+    }
+    for (int i = 0; i < sc->n_materials; ++i)
+        if (sc->materials[i].texture_id != -1) return B200_E_UNSUPPORTED;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { cudaGetLastError(); return B200_E_NODEVICE; }
+
+    b200pt* h = new (std::nothrow) b200pt();
+    if (!h) return B200_E_NOMEM;
+    CK(cudaGetDevice(&h->device));
+    CK(configure_kernels());
+    h->W = sc->camera.resolution[0];
+    h->H = sc->camera.resolution[1];
+    h->P = h->W * h->H;
+    h->depth = sc->trace_depth;
+    h->tiles = (h->P + PT_THREADS - 1) / PT_THREADS;
+    h->n_prims = sc->n_geoms;
+    h->n_mats = sc->n_materials;
+    h->cam.W = h->W;
+    h->cam.H = h->H;
+    for (int k = 0; k < 3; ++k) {
+        h->cam.pos[k] = sc->camera.position[k];
+        h->cam.view[k] = sc->camera.view[k];
+        h->cam.up[k] = sc->camera.up[k];
+        h->cam.right[k] = sc->camera.right[k];
+    }
+    h->cam.plx = sc->camera.pixelLength[0];
+    h->cam.ply = sc->camera.pixelLength[1];
+    b200pt_default_options(&h->opt);
+
+    std::vector<PrimRec> prims(sc->n_geoms);
+    for (int i = 0; i < sc->n_geoms; ++i) pack_prim(sc->geoms[i], prims[i]);
+    int r = dev_alloc((void**)&h->d_prims, sizeof(PrimRec) * prims.size());
+    if (!r) r = dev_alloc((void**)&h->d_mats, sizeof(MatRec) * (size_t)sc->n_materials);
+    if (!r) r = dev_alloc((void**)&h->d_image, sizeof(float) * 3 * (size_t)h->P);
+    if (!r) r = dev_alloc((void**)&h->d_segments, sizeof(unsigned long long));
+    if (r) { b200pt_destroy(h); return r; }
+    CK(cudaMemcpy(h->d_prims, prims.data(), sizeof(PrimRec) * prims.size(), cudaMemcpyHostToDevice));
+    static_assert(sizeof(b200pt_material) == sizeof(MatRec), "material layouts must agree");
+    CK(cudaMemcpy(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice));
+    CK(cudaEventCreate(&h->ev0));
+    CK(cudaEventCreate(&h->ev1));
+    r = b200pt_reset(h);
+    if (r) { b200pt_destroy(h); return r; }
+    *out = h;
+    return 0;
+}
+
+int b200pt_destroy(b200pt* h)
+{
+    if (!h) return 0;
+    cudaFree(h->d_prims); cudaFree(h->d_mats); cudaFree(h->d_pool); cudaFree(h->d_counts);
+    cudaFree(h->d_desc); cudaFree(h->d_segments); cudaFree(h->d_image);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    delete h;
+    return 0;
+}
+
+int b200pt_set_options(b200pt* h, const b200pt_options* o)
+{
+    if (!h || !o || o->batch < 0 || o->batch > 64) return B200_E_BADARG;
+    if (o->sort_by_material || o->first_bounce_cache) return B200_E_UNSUPPORTED;
+    h->opt = *o;
+    return 0;
+}
+
+int b200pt_reset(b200pt* h)
+{
+    if (!h) return B200_E_BADARG;
+    CK(cudaMemset(h->d_image, 0, sizeof(float) * 3 * (size_t)h->P));
+    CK(cudaMemset(h->d_segments, 0, sizeof(unsigned long long)));
+    h->iterations = 0;
+    h->launches = 0;
+    return 0;
+}
+
+int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void* stream, int sync)
+{
+    if (!h || n_iters < 0 || iter_stride < 1 || first_iter < 0) return B200_E_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int batch = h->opt.batch > 0 ? h->opt.batch : default_batch(h->P);
+    int r = ensure_batch(h, batch);
+    if (r) return r;
+
+    RenderParams p{};
+    const size_t plane = (size_t)h->batch_cap * h->P;
+    Pool pools[2];
+    for (int k = 0; k < 2; ++k) {
+        pools[k].a = h->d_pool + (size_t)(3 * k + 0) * plane;
+        pools[k].b = h->d_pool + (size_t)(3 * k + 1) * plane;
+        pools[k].c = h->d_pool + (size_t)(3 * k + 2) * plane;
+    }
+    p.counts = h->d_counts;
+    p.desc = h->d_desc;
+    p.segments = h->d_segments;
+    p.image = h->d_image;
+    p.prims = h->d_prims;
+    p.mats = h->d_mats;
+    p.n_prims = h->n_prims;
+    p.n_mats = h->n_mats;
+    p.cam = h->cam;
+    p.opt.rr = h->opt.russian_roulette;
+    p.opt.ssaa = h->opt.ssaa;
+    p.opt.dof = h->opt.dof;
+    p.opt.focal = h->opt.focal_len;
+    p.opt.aperture = h->opt.aperture;
+    p.depth = h->depth;
+    p.P = h->P;
+    p.tiles = h->tiles;
+    p.stride = iter_stride;
+
+    CK(cudaEventRecord(h->ev0, s));
+    for (int done = 0; done < n_iters; done += batch) {
+        const int nb = n_iters - done < batch ? n_iters - done : batch;
+        p.batch = nb;
+        p.iter0 = first_iter + done * iter_stride;
+        p.in = pools[0];
+        p.out = pools[1];
+        CK(launch_raygen(p, s));
+        for (int b = 0; b < h->depth; ++b) {
+            p.bounce = b;
+            if (++h->epoch >= (1u << 30)) {
+                CK(cudaMemsetAsync(h->d_desc, 0, sizeof(unsigned long long) * (size_t)h->batch_cap * h->tiles, s));
+                h->epoch = 1;
+            }
+            p.epoch = h->epoch;
+            CK(launch_bounce(p, s));
+            const Pool t = p.in; p.in = p.out; p.out = t;
+        }
+        h->launches += 1 + (uint64_t)h->depth;
+        h->last_batch = nb;
+    }
+    CK(cudaEventRecord(h->ev1, s));
+    h->iterations += (uint64_t)n_iters;
+    if (sync) {
+        CK(cudaEventSynchronize(h->ev1));
+        CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+    }
+    return 0;
+}
+
+int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream)
+{
+    if (!h || !dev_rgba8 || iter_divisor <= 0) return B200_E_BADARG;
+    CK(launch_tonemap(h->d_image, h->P, iter_divisor, (uchar4*)dev_rgba8, (cudaStream_t)stream));
+    h->launches += 1;
+    return 0;
+}
+
+int b200pt_read_sum(b200pt* h, float* host_rgb)
+{
+    if (!h || !host_rgb) return B200_E_BADARG;
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(host_rgb, h->d_image, sizeof(float) * 3 * (size_t)h->P, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats)
+{
+    if (!h || !dev_ptr) return B200_E_BADARG;
+    *dev_ptr = h->d_image;
+    if (n_floats) *n_floats = 3 * (size_t)h->P;
+    return 0;
+}
+
+int b200pt_get_stats(b200pt* h, b200pt_stats* st)
+{
+    if (!h || !st) return B200_E_BADARG;
+    CK(cudaDeviceSynchronize());
+    unsigned long long seg = 0;
+    CK(cudaMemcpy(&seg, h->d_segments, sizeof(seg), cudaMemcpyDeviceToHost));
+    st->path_segments = seg;
+    st->iterations = h->iterations;
+    st->kernel_launches = h->launches;
+    if (h->ev1 && cudaEventQuery(h->ev1) == cudaSuccess && h->iterations) cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    cudaGetLastError();
+    st->last_render_ms = h->last_ms;
+    st->traced_depth = 0;
+    if (h->batch_cap && h->last_batch) {
+        // TracedDepth (pathtrace.cu:510): bounces the last iteration ran before its pool emptied
+        std::vector<int> counts((size_t)(h->depth + 1) * h->last_batch);
+        CK(cudaMemcpy(counts.data(), h->d_counts, sizeof(int) * counts.size(), cudaMemcpyDeviceToHost));
+        int d = 0;
+        for (int b = 0; b < h->depth; ++b)
+            if (counts[(size_t)b * h->last_batch + (h->last_batch - 1)] > 0) d = b + 1;
+        st->traced_depth = d;
+    }
+    return 0;
+}
+
+int b200pt_debug_intersect(b200pt* h, int n, const float* d_rays, float* d_t, float* d_normal, int* d_geom, void* stream)
+{
+    if (!h || n < 0 || (n > 0 && (!d_rays || !d_t || !d_normal || !d_geom))) return B200_E_BADARG;
+    if (n == 0) return 0;
+    CK(launch_debug_intersect(h->d_prims, h->n_prims, n, d_rays, d_t, d_normal, d_geom, (cudaStream_t)stream));
+    h->launches += 1;
+    return 0;
+}
+
+const char* b200pt_error_string(int code)
+{
+    switch (code) {
+    case B200_OK: return "ok";
+    case B200_E_BADARG: return "b200pt: bad argument";
+    case B200_E_NODEVICE: return "b200pt: no CUDA device (this library has no CPU fallback)";
+    case B200_E_NOMEM: return "b200pt: out of device memory";
+    case B200_E_UNSUPPORTED: return "b200pt: scene feature not supported (meshes, textures, material sort or first-bounce cache)";
+    default: return cudaGetErrorString((cudaError_t)code);
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,51 @@
+// pt_kernels.cuh -- launcher interface between pt_kernels.cu (device code) and pt_api.cu (the
+// C ABI of include/b200_pt.h).  Not part of the public boundary.
+#pragma once
+#include <cuda_runtime.h>
+#include "pt_shade.cuh"
+
+namespace ptk {
+
+constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
+constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
+constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
+
+// SoA path pool: three 16-byte words per path.
+//   a = origin.xyz    | pixelIndex
+//   b = direction.xyz | remainingBounces
+//   c = colour.xyz    | bounces
+struct Pool {
+    float4* a;
+    float4* b;
+    float4* c;
+};
+
+struct RenderParams {
+    Pool in, out;                      // ping-pong pools, batch slot s at offset s * P
+    int* counts;                       // [(depth + 1)][batch]: live paths entering each bounce
+    unsigned long long* desc;          // [batch][tiles]: look-back descriptors (epoch-tagged)
+    unsigned long long* segments;      // running sum of live paths entering intersection
+    float* image;                      // float SUM image, 3 floats per pixel
+    const PrimRec* prims;
+    const MatRec* mats;
+    int n_prims, n_mats;
+    CamRec cam;
+    OptRec opt;
+    int depth;
+    int P;                             // pixels = paths per iteration
+    int tiles;                         // ceil(P / PT_THREADS)
+    int batch;                         // iterations in flight in this launch (grid.y)
+    int iter0, stride;                 // slot s traces iteration iter0 + s * stride
+    int bounce;                        // which bounce this launch is
+    unsigned epoch;                    // look-back epoch of this launch
+};
+
+size_t bounce_smem_bytes(int n_prims, int n_mats);
+cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
+cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);
+cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s);
+cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* rays, float* t,
+                                   float* normal, int* geom, cudaStream_t s);
+cudaError_t configure_kernels();
+
+}  // namespace ptk

@@ -1,0 +1,149 @@
+/* b200_pt.h -- C ABI of the B200-native wavefront path tracer.
+ *
+ * Drop-in boundary for the reference's render driver, path_tracer/src/pathtrace.h:6-9:
+ *
+ *   void InitDataContainer(GuiDataContainer*)        -> b200pt_set_options
+ *   void pathtraceInit(Scene*)                       -> b200pt_create (+ b200pt_reset)
+ *   void pathtraceFree()                             -> b200pt_destroy
+ *   void pathtrace(uchar4* pbo, int frame, int iter) -> b200pt_render (+ b200pt_tonemap_u8,
+ *                                                       b200pt_read_sum)
+ *
+ * The POD structs below have the SAME byte layout as the reference's sceneStructs.h types
+ * (Geom 272 B, Material 48 B, Camera 84 B: path_tracer/src/sceneStructs.h:24-72, offsets in
+ * SURVEY.md section 8), so a maintainer's shim can pass scene->geoms.data() etc. unchanged.
+ * Matrices are column-major float[16] exactly as glm::mat4 stores them.
+ *
+ * Conventions kept from the reference: `iteration` is 1-based and is both an RNG seed
+ * component and the divisor of the 8-bit preview (pathtrace.cu:57-62,65-86, main.cpp:148-151);
+ * the accumulation image is the float SUM over iterations, index x + y*W, 3 floats per pixel
+ * (pathtrace.cu:347-356,524); per-(iteration, index, depth) seeding reproduces the reference's
+ * random paths bit for bit.
+ * Differences: errors are returned (0 = ok, else cudaError_t or B200_E_*), nothing exits;
+ * several renderers may coexist (state lives in the handle, not in file statics); iterations
+ * are rendered in batches without any per-bounce host round trip.  No CPU fallback.
+ *
+ * Plain C: pointers and sizes only (a stream is a void*).
+ */
+#ifndef B200_PT_H
+#define B200_PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { B200PT_SPHERE = 0, B200PT_CUBE = 1, B200PT_MESH = 2 }; /* GeomType, sceneStructs.h:12-17 */
+
+/* == struct Geom (272 bytes) */
+typedef struct b200pt_geom {
+    int32_t type;
+    int32_t materialid;
+    float translation[3];
+    float rotation[3];
+    float scale[3];
+    float transform[16];
+    float inverseTransform[16];
+    float invTranspose[16];
+    int32_t tri_start_idx;
+    int32_t tri_end_idx;
+    int32_t boundingbox_idx;
+    float min_bound[3];
+    float max_bound[3];
+} b200pt_geom;
+
+/* == struct Material (48 bytes) */
+typedef struct b200pt_material {
+    float color[3];
+    float specular_exponent;
+    float specular_color[3];
+    float hasReflective;
+    float hasRefractive;
+    float indexOfRefraction;
+    float emittance;
+    int32_t texture_id; /* -1 = none; textures are not supported yet: create() rejects others */
+} b200pt_material;
+
+/* == struct Camera (84 bytes) */
+typedef struct b200pt_camera {
+    int32_t resolution[2];
+    float position[3];
+    float lookAt[3];
+    float view[3];
+    float up[3];
+    float right[3];
+    float fov[2];
+    float pixelLength[2];
+} b200pt_camera;
+
+typedef struct b200pt_scene {
+    b200pt_camera camera;
+    int32_t trace_depth;          /* RenderState::traceDepth */
+    int32_t n_geoms;
+    const b200pt_geom* geoms;
+    int32_t n_materials;
+    const b200pt_material* materials;
+} b200pt_scene;
+
+/* The run-time toggles of GuiDataContainer (utilities.h:17-34) with the reference's defaults,
+ * plus the knobs that are new here. */
+typedef struct b200pt_options {
+    int32_t russian_roulette;   /* default 1 */
+    int32_t sort_by_material;   /* default 0 */
+    int32_t ssaa;               /* default 1 */
+    int32_t dof;                /* default 1 */
+    float aperture;             /* default 0.1 */
+    float focal_len;            /* default 10.0 */
+    int32_t first_bounce_cache; /* NEW, default 0; only honoured when ssaa == 0 && dof == 0 */
+    int32_t batch;              /* NEW: iterations traced concurrently in one wavefront
+                                   (0 = library default).  1 keeps the reference's accumulation
+                                   order so the float sum image is bit-identical to it.       */
+} b200pt_options;
+
+typedef struct b200pt b200pt;
+
+typedef struct b200pt_stats {
+    uint64_t path_segments;   /* sum over bounces of live paths entering intersection */
+    uint64_t iterations;      /* iterations accumulated since the last reset                     */
+    uint64_t kernel_launches; /* kernels launched since the last reset                           */
+    float last_render_ms;     /* CUDA-event time of the most recent b200pt_render call           */
+    int32_t traced_depth;     /* GuiDataContainer::TracedDepth of the last iteration             */
+} b200pt_stats;
+
+void b200pt_default_options(b200pt_options* o);
+
+/* Allocate device state for `scene` on the current device and zero the accumulation image. */
+int b200pt_create(const b200pt_scene* scene, b200pt** out);
+int b200pt_destroy(b200pt* h);
+int b200pt_set_options(b200pt* h, const b200pt_options* o);
+/* Zero the accumulation image and the statistics (what pathtraceInit does, pathtrace.cu:121-122). */
+int b200pt_reset(b200pt* h);
+
+/* Trace iterations first_iter .. first_iter + (n_iters-1)*iter_stride (1-based, stride >= 1) and
+ * add them to the accumulation image.  Asynchronous on `stream` unless `sync` != 0. */
+int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void* stream, int sync);
+
+/* sendImageToPBO (pathtrace.cu:65-86): dev_rgba8[i] = clamp(int(sum/iter*255.0),0,255), w = 0.
+ * dev_rgba8 is a DEVICE buffer of W*H*4 bytes. */
+int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream);
+
+/* Copy the float SUM image (3*W*H floats) to host memory; synchronises. */
+int b200pt_read_sum(b200pt* h, float* host_rgb);
+/* Device pointer of the float SUM image (for NCCL all-reduce across GPUs). */
+int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats);
+
+int b200pt_get_stats(b200pt* h, b200pt_stats* s);
+
+/* Per-stage entry points used by the parity tests (device pointers, n items each):
+ * closest hit of n rays (origin xyz + direction xyz, 6 floats each) against the scene:
+ * out_t[n], out_normal[3n], out_geom[n] (-1 = miss). */
+int b200pt_debug_intersect(b200pt* h, int n, const float* d_rays, float* d_t, float* d_normal,
+                           int* d_geom, void* stream);
+
+const char* b200pt_error_string(int code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PT_H */
