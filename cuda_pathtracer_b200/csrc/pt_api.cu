@@ -310,11 +310,45 @@ int b200pt_get_stats(b200pt* h, b200pt_stats* st)
     return 0;
 }
 
-int b200pt_debug_intersect(b200pt* h, int n, const float* d_rays, float* d_t, float* d_normal, int* d_geom, void* stream)
+static void fill_params(const b200pt* h, RenderParams& p)
 {
-    if (!h || n < 0 || (n > 0 && (!d_rays || !d_t || !d_normal || !d_geom))) return B200_E_BADARG;
+    p.cam = h->cam;
+    p.opt.rr = h->opt.russian_roulette;
+    p.opt.ssaa = h->opt.ssaa;
+    p.opt.dof = h->opt.dof;
+    p.opt.focal = h->opt.focal_len;
+    p.opt.aperture = h->opt.aperture;
+    p.depth = h->depth;
+    p.P = h->P;
+    p.tiles = h->tiles;
+}
+
+int b200pt_debug_raygen(b200pt* h, int iter, void* d_segments, void* stream)
+{
+    if (!h || !d_segments) return B200_E_BADARG;
+    RenderParams p{};
+    fill_params(h, p);
+    CK(launch_debug_raygen(p, iter, (float*)d_segments, (cudaStream_t)stream));
+    h->launches += 1;
+    return 0;
+}
+
+int b200pt_debug_intersect(b200pt* h, int n, const void* d_segments, void* d_isects, void* stream)
+{
+    if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
     if (n == 0) return 0;
-    CK(launch_debug_intersect(h->d_prims, h->n_prims, n, d_rays, d_t, d_normal, d_geom, (cudaStream_t)stream));
+    CK(launch_debug_intersect(h->d_prims, h->n_prims, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
+    h->launches += 1;
+    return 0;
+}
+
+int b200pt_debug_shade(b200pt* h, int iter, int n, const void* d_isects, void* d_segments, void* stream)
+{
+    if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
+    if (n == 0) return 0;
+    RenderParams p{};
+    fill_params(h, p);
+    CK(launch_debug_shade(h->d_prims, h->d_mats, p.opt, iter, n, (const float*)d_isects, (float*)d_segments, (cudaStream_t)stream));
     h->launches += 1;
     return 0;
 }

@@ -249,25 +249,69 @@ __global__ void __launch_bounds__(256) k_tonemap(const float* __restrict__ image
     out[i] = make_uchar4((unsigned char)c[0], (unsigned char)c[1], (unsigned char)c[2], 0);
 }
 
-// per-stage parity probe: closest hit of arbitrary rays, primitives read from global memory
+// ---- per-stage parity probes on the reference's AoS layouts (tier T1) ---------------------------
+__device__ __forceinline__ PathState load_segment(const float* __restrict__ seg)
+{
+    PathState s;
+    s.o = v3(seg[0], seg[1], seg[2]);
+    s.d = v3(seg[3], seg[4], seg[5]);
+    s.c = v3(seg[6], seg[7], seg[8]);
+    s.pixel = __float_as_int(seg[9]);
+    s.remaining = __float_as_int(seg[10]);
+    s.bounces = __float_as_int(seg[11]);
+    return s;
+}
+__device__ __forceinline__ void store_segment(float* __restrict__ seg, const PathState& s)
+{
+    seg[0] = s.o.x; seg[1] = s.o.y; seg[2] = s.o.z;
+    seg[3] = s.d.x; seg[4] = s.d.y; seg[5] = s.d.z;
+    seg[6] = s.c.x; seg[7] = s.c.y; seg[8] = s.c.z;
+    seg[9] = __int_as_float(s.pixel);
+    seg[10] = __int_as_float(s.remaining);
+    seg[11] = __int_as_float(s.bounces);
+}
+
+__global__ void __launch_bounds__(256) k_debug_raygen(const __grid_constant__ RenderParams p, int iter,
+                                                      float* __restrict__ segments)
+{
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= p.P) return;
+    const int y = idx / p.cam.W, x = idx - y * p.cam.W;
+    store_segment(segments + 12 * (size_t)idx, make_camera_path(p.cam, p.opt, iter, p.depth, x, y));
+}
+
 __global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restrict__ prims, int n_prims, int n,
-                                                         const float* __restrict__ rays, float* __restrict__ t_out,
-                                                         float* __restrict__ n_out, int* __restrict__ g_out)
+                                                         const float* __restrict__ segments,
+                                                         float* __restrict__ isects)
 {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
-    const V3 o = v3(rays[6 * i + 0], rays[6 * i + 1], rays[6 * i + 2]);
-    const V3 d = v3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+    const PathState s = load_segment(segments + 12 * (size_t)i);
     float t_min = 3.402823466e+38f;
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-    closest_in_chunk(prims, n_prims, 0, o, d, t_min, hit, best);
+    closest_in_chunk(prims, n_prims, 0, s.o, s.d, t_min, hit, best);
+    float* o = isects + 7 * (size_t)i;           // the reference memsets the record to 0 first
     V3 nn = v3(0.f, 0.f, 0.f);
-    if (hit >= 0) nn = prim_normal(prims[hit], best);
-    t_out[i] = hit >= 0 ? t_min : -1.0f;
-    n_out[3 * i + 0] = nn.x; n_out[3 * i + 1] = nn.y; n_out[3 * i + 2] = nn.z;
-    g_out[i] = hit;
+    int mat = 0;
+    if (hit >= 0) { nn = prim_normal(prims[hit], best); mat = prims[hit].material; }
+    o[0] = hit >= 0 ? t_min : -1.0f;
+    o[1] = nn.x; o[2] = nn.y; o[3] = nn.z;
+    o[4] = __int_as_float(mat);
+    o[5] = 0.f; o[6] = 0.f;
+}
+
+__global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ mats, OptRec opt, int iter, int n,
+                                                     const float* __restrict__ isects, float* __restrict__ segments)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    PathState s = load_segment(segments + 12 * (size_t)i);
+    const float* is = isects + 7 * (size_t)i;
+    const MatRec m = mats[__float_as_int(is[4])];
+    shade_exact(s, is[0], v3(is[1], is[2], is[3]), m, iter, i, opt.rr);
+    store_segment(segments + 12 * (size_t)i, s);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -303,10 +347,23 @@ cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* o
     return cudaGetLastError();
 }
 
-cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* rays, float* t,
-                                   float* normal, int* geom, cudaStream_t s)
+cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments, cudaStream_t s)
 {
-    k_debug_intersect<<<(n + 255) / 256, 256, 0, s>>>(prims, n_prims, n, rays, t, normal, geom);
+    k_debug_raygen<<<(p.P + 255) / 256, 256, 0, s>>>(p, iter, segments);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* segments, float* isects,
+                                   cudaStream_t s)
+{
+    k_debug_intersect<<<(n + 255) / 256, 256, 0, s>>>(prims, n_prims, n, segments, isects);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_debug_shade(const PrimRec*, const MatRec* mats, OptRec opt, int iter, int n, const float* isects,
+                               float* segments, cudaStream_t s)
+{
+    k_debug_shade<<<(n + 255) / 256, 256, 0, s>>>(mats, opt, iter, n, isects, segments);
     return cudaGetLastError();
 }
 

@@ -44,8 +44,12 @@ size_t bounce_smem_bytes(int n_prims, int n_mats);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s);
-cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* rays, float* t,
-                                   float* normal, int* geom, cudaStream_t s);
+// per-stage probes on the reference's AoS layouts (PathSegment 12 words, ShadeableIntersection 7 words)
+cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments, cudaStream_t s);
+cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* segments, float* isects,
+                                   cudaStream_t s);
+cudaError_t launch_debug_shade(const PrimRec* prims, const MatRec* mats, OptRec opt, int iter, int n, const float* isects,
+                               float* segments, cudaStream_t s);
 cudaError_t configure_kernels();
 
 }  // namespace ptk

@@ -6,8 +6,10 @@
 // path traced here takes bit-for-bit the same values as in the reference's CUDA build and the
 // per-(iteration, slot, depth) seeded random paths are reproduced exactly.
 // The intrinsics are never re-associated or contracted, so the result does not depend on this
-// file's compiler heuristics.  Operation order per function was taken from the PTX nvcc emits
-// for the reference sources cited at each function.
+// file's compiler heuristics.  Operation order per function was taken from the SASS of the
+// reference build (nvcc 12.9, sm_100a) for the sources cited at each function -- SASS, not PTX:
+// ptxas fuses PTX's unsuffixed mul.f32 + add/sub.f32 pairs into FFMA on its own (e.g. 1 - up*up,
+// glm::cross, view - right*sx), and which product of a*b - c*d it fuses varies per site.
 //
 // vec3 helpers are deliberately tiny: GLM is not used.
 #pragma once
@@ -44,12 +46,13 @@ __device__ __forceinline__ float distance_exact(const V3& a, const V3& b)
     return __fsqrt_rn(__fmaf_rn(d.z, d.z, __fmaf_rn(d.x, d.x, __fmul_rn(d.y, d.y))));
 }
 
-// glm::cross: NOT contracted in the reference's PTX (mul, mul, sub per component).
+// glm::cross as it ends up in the reference's SASS: the second product is rounded, the first
+// is fused into the subtraction (FMUL; FFMA a, b, -t).
 __device__ __forceinline__ V3 cross_exact(const V3& a, const V3& b)
 {
-    return v3(__fsub_rn(__fmul_rn(a.y, b.z), __fmul_rn(b.y, a.z)),
-              __fsub_rn(__fmul_rn(a.z, b.x), __fmul_rn(b.z, a.x)),
-              __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(b.x, a.y)));
+    return v3(__fmaf_rn(a.y, b.z, -__fmul_rn(b.y, a.z)),
+              __fmaf_rn(a.z, b.x, -__fmul_rn(b.z, a.x)),
+              __fmaf_rn(a.x, b.y, -__fmul_rn(b.x, a.y)));
 }
 
 // ---- RNG -----------------------------------------------------------------------------------

@@ -41,9 +41,10 @@ __device__ __forceinline__ PathState make_camera_path(const CamRec& cam, const O
     }
     const V3 rp = v3(__fmul_rn(cam.right[0], cam.plx), __fmul_rn(cam.right[1], cam.plx), __fmul_rn(cam.right[2], cam.plx));
     const V3 upv = v3(__fmul_rn(cam.up[0], cam.ply), __fmul_rn(cam.up[1], cam.ply), __fmul_rn(cam.up[2], cam.ply));
-    V3 dir = v3(__fsub_rn(__fsub_rn(cam.view[0], __fmul_rn(rp.x, sx)), __fmul_rn(upv.x, sy)),
-                __fsub_rn(__fsub_rn(cam.view[1], __fmul_rn(rp.y, sx)), __fmul_rn(upv.y, sy)),
-                __fsub_rn(__fsub_rn(cam.view[2], __fmul_rn(rp.z, sx)), __fmul_rn(upv.z, sy)));
+    // SASS: both subtractions are fused (FFMA -rp, sx, view ; FFMA -upv, sy, .)
+    V3 dir = v3(__fmaf_rn(-upv.x, sy, __fmaf_rn(-rp.x, sx, cam.view[0])),
+                __fmaf_rn(-upv.y, sy, __fmaf_rn(-rp.y, sx, cam.view[1])),
+                __fmaf_rn(-upv.z, sy, __fmaf_rn(-rp.z, sx, cam.view[2])));
     p.d = normalize_exact(dir);
 
     if (opt.dof) {                        // thin lens: r = u*aperture (not sqrt), lens in world XY
@@ -76,7 +77,7 @@ __device__ __forceinline__ V3 cosine_hemisphere(const V3& n, uint32_t& rng)
 {
     const float up = __fsqrt_rn(rng_u01(rng));
     const float around = __fmul_rn(rng_u01(rng), 6.2831853071795864769252867665590057683943f);
-    const float over = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(up, up)));
+    const float over = __fsqrt_rn(__fmaf_rn(-up, up, 1.0f));          // SASS: FFMA -up, up, 1
     const float S = 0.5773502691896257645091487805019574556476f;
     V3 nn;
     if (fabsf(n.x) < S) nn = v3(1.f, 0.f, 0.f);
@@ -108,12 +109,13 @@ __device__ __forceinline__ void scatter_exact(PathState& p, const V3& hit, const
         const float R = __fmaf_rn(__fsub_rn(1.0f, R0), __fmul_rn(X2, __fmul_rn(X, X2)), R0);
         const float u = rng_u01(rng);
         if (R < u) {                      // glm::refract(I, n, ior): eta is the ior itself
-            const float k = __fsub_rn(1.0f, __fmul_rn(__fmul_rn(ior, ior), __fsub_rn(1.0f, __fmul_rn(dn, dn))));
+            // SASS: k = FFMA(-(ior*ior), FFMA(-dn, dn, 1), 1); d = FFMA(n, -s, ior*I) * sel
+            const float k = __fmaf_rn(-__fmul_rn(ior, ior), __fmaf_rn(-dn, dn, 1.0f), 1.0f);
             const float s = __fmaf_rn(ior, dn, __fsqrt_rn(k));
             const float sel = k >= 0.0f ? 1.0f : 0.0f;
-            p.d = v3(__fmul_rn(__fsub_rn(__fmul_rn(ior, I.x), __fmul_rn(s, n.x)), sel),
-                     __fmul_rn(__fsub_rn(__fmul_rn(ior, I.y), __fmul_rn(s, n.y)), sel),
-                     __fmul_rn(__fsub_rn(__fmul_rn(ior, I.z), __fmul_rn(s, n.z)), sel));
+            p.d = v3(__fmul_rn(__fmaf_rn(n.x, -s, __fmul_rn(ior, I.x)), sel),
+                     __fmul_rn(__fmaf_rn(n.y, -s, __fmul_rn(ior, I.y)), sel),
+                     __fmul_rn(__fmaf_rn(n.z, -s, __fmul_rn(ior, I.z)), sel));
             p.c = v3(__fmul_rn(m.color[0], p.c.x), __fmul_rn(m.color[1], p.c.y), __fmul_rn(m.color[2], p.c.z));
         } else {
             p.d = reflect_exact(I, n);

@@ -135,11 +135,16 @@ int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats);
 
 int b200pt_get_stats(b200pt* h, b200pt_stats* s);
 
-/* Per-stage entry points used by the parity tests (device pointers, n items each):
- * closest hit of n rays (origin xyz + direction xyz, 6 floats each) against the scene:
- * out_t[n], out_normal[3n], out_geom[n] (-1 = miss). */
-int b200pt_debug_intersect(b200pt* h, int n, const float* d_rays, float* d_t, float* d_normal,
-                           int* d_geom, void* stream);
+/* Per-stage entry points used by the parity tests (tier T1): each runs ONE stage on arrays in the
+ * reference's own AoS layouts so the result can be compared bit for bit with the reference's
+ * kernel on identical inputs.  All pointers are DEVICE pointers.
+ *   segment = struct PathSegment (48 B: origin 3f, direction 3f, colour 3f, pixelIndex,
+ *             remainingBounces, bounces), isect = struct ShadeableIntersection (28 B: t, normal 3f,
+ *             materialId, texture_coord 2f)                       sceneStructs.h:78-97 */
+int b200pt_debug_raygen(b200pt* h, int iter, void* d_segments /* W*H */, void* stream);
+int b200pt_debug_intersect(b200pt* h, int n, const void* d_segments, void* d_isects, void* stream);
+int b200pt_debug_shade(b200pt* h, int iter, int n, const void* d_isects, void* d_segments /* in/out */,
+                       void* stream);
 
 const char* b200pt_error_string(int code);
 

@@ -1,0 +1,64 @@
+"""Generates the path-tracer golden fixtures.
+
+Step 1 (here, CPU only): scene POD dumps produced by the reference's OWN loader
+(oracle/_ref/ref_scene_dump = /root/reference/path_tracer/src/scene.cpp + BVH_tree.cpp +
+utilities.cpp compiled unmodified) for the scenes under scenes/:
+    python tests/golden/make_pt_golden.py scenes
+Step 2 (on a B200, under gpurun): float SUM images rendered by the reference's own CUDA build
+(oracle/_ref/ref_pathtracer, unmodified pathtrace.cu / intersections.cu / interactions.cu) on
+the small scenes, written to gpurun_out/ and then copied into tests/golden/ by
+    python tests/golden/make_pt_golden.py renders [--collect]
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(HERE))
+REF = os.path.join(REPO, "oracle", "_ref")
+
+# scene -> extra args (--refract MATERIAL_ID IOR: material ids follow the alphabetical key order)
+SCENES = {
+    "cornell": [],
+    "cornell_mirror": [],
+    "cornell_small": [],
+    "cornell_small_mirror": [],
+    "cornell_glass_small": ["--refract", "4", "1.5"],
+    "cornell_glass_1080p": ["--refract", "4", "1.5"],
+    "synthetic_600_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
+    "synthetic_4096": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
+}
+# (scene, iterations, extra renderer flags, tag)
+RENDERS = [
+    ("cornell_small", 16, [], "default"),
+    ("cornell_small", 16, ["--no-ssaa", "--no-dof", "--no-rr"], "plain"),
+    ("cornell_small_mirror", 16, [], "default"),
+    ("cornell_glass_small", 16, [], "default"),
+    ("synthetic_600_small", 4, [], "default"),
+]
+
+
+def scenes():
+    for name, extra in SCENES.items():
+        subprocess.run([os.path.join(REF, "ref_scene_dump"), os.path.join(REPO, "scenes", name + ".json"),
+                        os.path.join(HERE, name + ".scene.bin")] + extra, check=True, stdout=subprocess.DEVNULL)
+        print("wrote", name + ".scene.bin")
+
+
+def renders(collect):
+    out = os.path.join(REPO, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    for scene, iters, flags, tag in RENDERS:
+        name = f"{scene}.{tag}.{iters}it.refsum.bin"
+        if collect:
+            os.replace(os.path.join(out, name), os.path.join(HERE, name))
+            continue
+        subprocess.run([os.path.join(REF, "ref_pathtracer"), os.path.join(REPO, "scenes", scene + ".json"),
+                        "--iters", str(iters), "--out", os.path.join(out, name)] + flags + SCENES[scene], check=True)
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "scenes":
+        scenes()
+    else:
+        renders("--collect" in sys.argv)
