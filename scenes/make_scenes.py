@@ -125,7 +125,7 @@ def synthetic(n_prims, res, iters, depth, name, seed=565):
 
 def write(name, scene):
     with open(os.path.join(HERE, name), "w") as f:
-        json.dump(scene, f, indent=1)
+        json.dump(scene, f, indent=1 if len(scene["Objects"]) < 100 else None)
         f.write("\n")
 
 
@@ -134,6 +134,7 @@ def main():
     write("cornell_mirror.json", cornell((800, 800), 5000, 8, "cornell_mirror", True))
     write("cornell_small.json", cornell((160, 120), 64, 8, "cornell_small", False))
     write("cornell_small_mirror.json", cornell((160, 120), 64, 8, "cornell_small_mirror", True))
+    write("cornell_tiny.json", cornell((64, 48), 16, 8, "cornell_tiny", True))
     write("cornell_glass_1080p.json", cornell_glass((1920, 1080), 2000, 12, "cornell_glass_1080p"))
     write("cornell_glass_small.json", cornell_glass((192, 108), 64, 12, "cornell_glass_small"))
     write("synthetic_4096.json", synthetic(4096, (3840, 2160), 256, 8, "synthetic_4096"))

@@ -23,6 +23,7 @@ SCENES = {
     "cornell_mirror": [],
     "cornell_small": [],
     "cornell_small_mirror": [],
+    "cornell_tiny": [],
     "cornell_glass_small": ["--refract", "4", "1.5"],
     "cornell_glass_1080p": ["--refract", "4", "1.5"],
     "synthetic_600_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),

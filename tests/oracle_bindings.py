@@ -76,3 +76,64 @@ def gen_array(n_pot, maxval, seed=565):
     if n_pot > 1:
         lib.oracle_gen_array(ctypes.c_int(n_pot - 1), _iptr(a), ctypes.c_int(maxval), ctypes.c_uint(seed))
     return a
+
+
+class PtOracle:
+    """oracle/pt_oracle.cpp: CPU restatement of the reference's path-tracing loop (device arithmetic
+    order, bit-identical to the reference's CUDA build).  `scene` is a
+    cuda_pathtracer_b200.pathtracer.Scene (POD arrays in the reference's layouts)."""
+
+    def __init__(self):
+        self.lib = ctypes.CDLL(_ensure_built("_build/liboracle_pt.so"))
+        self.lib.pt_oracle_render.restype = ctypes.c_ulonglong
+
+    @staticmethod
+    def _opts(gui):
+        o5 = (ctypes.c_int * 5)(int(gui.russianRoulette), int(gui.sortbyMaterial), int(gui.SSAA), int(gui.DoF), 0)
+        o2 = (ctypes.c_float * 2)(float(gui.aperture), float(gui.focal_len))
+        return o5, o2
+
+    def rng(self, iteration, index, depth, n):
+        out = np.zeros(n, dtype=np.float32)
+        self.lib.pt_oracle_rng(iteration, index, depth, n, out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def sincos(self, a):
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        s, c = np.zeros_like(a), np.zeros_like(a)
+        self.lib.pt_oracle_sincos(a.size, a.ctypes.data_as(ctypes.c_void_p), s.ctypes.data_as(ctypes.c_void_p),
+                                  c.ctypes.data_as(ctypes.c_void_p))
+        return s, c
+
+    def raygen(self, scene, gui, iteration):
+        o5, o2 = self._opts(gui)
+        seg = np.zeros((scene.width * scene.height, 12), dtype=np.float32)
+        self.lib.pt_oracle_raygen(ctypes.byref(scene.camera), o5, o2, int(iteration), scene.traceDepth,
+                                  seg.ctypes.data_as(ctypes.c_void_p))
+        return seg
+
+    def intersect(self, scene, segments):
+        segments = np.ascontiguousarray(segments, dtype=np.float32)
+        out = np.zeros((len(segments), 7), dtype=np.float32)
+        self.lib.pt_oracle_intersect(scene.geoms, len(scene.geoms), len(segments),
+                                     segments.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def shade(self, scene, gui, iteration, isects, segments):
+        seg = np.ascontiguousarray(segments, dtype=np.float32).copy()
+        isects = np.ascontiguousarray(isects, dtype=np.float32)
+        self.lib.pt_oracle_shade(scene.materials, int(gui.russianRoulette), int(iteration), len(seg),
+                                 isects.ctypes.data_as(ctypes.c_void_p), seg.ctypes.data_as(ctypes.c_void_p))
+        return seg
+
+    def render(self, scene, gui, first_iter, n_iters, stride=1, threads=None, out=None):
+        """returns (sum image H x W x 3 float32, path segments)"""
+        o5, o2 = self._opts(gui)
+        if out is None:
+            out = np.zeros((scene.height, scene.width, 3), dtype=np.float32)
+        if threads is None:
+            threads = os.cpu_count() or 1
+        seg = self.lib.pt_oracle_render(ctypes.byref(scene.camera), scene.traceDepth, scene.geoms, len(scene.geoms),
+                                        scene.materials, o5, o2, int(first_iter), int(n_iters), int(stride),
+                                        out.ctypes.data_as(ctypes.c_void_p), int(threads))
+        return out, int(seg)

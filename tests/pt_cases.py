@@ -1,0 +1,59 @@
+"""Shared case tables of the path-tracer tests."""
+import os
+
+import numpy as np
+
+from cuda_pathtracer_b200 import pathtracer as pt
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+# (scene, iterations, reference-renderer flags, tag) -> tests/golden/<scene>.<tag>.<it>it.refsum.bin,
+# float SUM images written by the reference's own CUDA build (tests/golden/make_pt_golden.py)
+RENDERS = [
+    ("cornell_small", 16, [], "default"),
+    ("cornell_small", 16, ["--no-ssaa", "--no-dof", "--no-rr"], "plain"),
+    ("cornell_small_mirror", 16, [], "default"),
+    ("cornell_glass_small", 16, [], "default"),
+    ("synthetic_600_small", 4, [], "default"),
+]
+# per-stage vectors from the reference's own kernels (tests/golden/make_pt_stage_golden.py)
+STAGES = [("cornell_tiny", "default", []), ("cornell_tiny", "plain", ["--no-ssaa", "--no-dof", "--no-rr"]),
+          ("cornell_glass_small", "default", [])]
+
+
+def load_scene(name):
+    return pt.Scene.from_pod_file(os.path.join(GOLD, name + ".scene.bin"))
+
+
+def gui_from_flags(flags, batch=0):
+    g = pt.GuiDataContainer()
+    g.SSAA = "--no-ssaa" not in flags
+    g.DoF = "--no-dof" not in flags
+    g.russianRoulette = "--no-rr" not in flags
+    g.batch = batch
+    return g
+
+
+def ref_sum(scene, iters, tag, shape):
+    return np.fromfile(os.path.join(GOLD, f"{scene}.{tag}.{iters}it.refsum.bin"), dtype=np.float32).reshape(shape)
+
+
+def bits_equal(a, b):
+    """Bitwise equality of float32 arrays; a NaN matches a NaN whatever its payload (the GPU's
+    canonical NaN is 0x7fffffff, x86's 0xffc00000: total internal reflection in glm::refract
+    yields a NaN direction in the reference, interactions.cu:68)."""
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    b = np.ascontiguousarray(b, dtype=np.float32)
+    if a.shape != b.shape:
+        return False
+    same = a.view(np.uint32) == b.view(np.uint32)
+    return bool(np.all(same | (np.isnan(a) & np.isnan(b))))
+
+
+def image_metrics(mine_sum, ref_sum_img, iters):
+    """north_star's tolerance is stated on the per-pixel MEAN image (sum / iterations), peak 1.0."""
+    d = (mine_sum.astype(np.float64) - ref_sum_img.astype(np.float64)) / iters
+    mae = float(np.abs(d).mean())
+    mse = float((d ** 2).mean())
+    psnr = float("inf") if mse == 0 else 10.0 * np.log10(1.0 / mse)
+    return mae, psnr
