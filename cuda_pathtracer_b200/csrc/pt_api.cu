@@ -38,6 +38,14 @@ struct b200pt {
     uint64_t iterations = 0, launches = 0;
     float last_ms = 0.f;
     int last_batch = 0;
+    std::vector<PrimRec> host_prims;   // staging for b200pt_update_scene
+    // optional per-kernel timing of k_bounce (b200pt_set_profiling): one event pair brackets the
+    // `depth` back-to-back bounce launches of a batch
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;
+    size_t prof_used = 0;              // events in use (2 per batch)
+    double bounce_ms = 0.0;
+    uint64_t bounce_launches = 0;
 };
 
 namespace {
@@ -95,6 +103,60 @@ int ensure_batch(b200pt* h, int batch)
     return 0;
 }
 
+// fold the recorded event pairs into bounce_ms (synchronises on the last one)
+int collect_profile(b200pt* h)
+{
+    if (!h->prof_used) return 0;
+    CK(cudaEventSynchronize(h->prof_events[h->prof_used - 1]));
+    for (size_t i = 0; i + 1 < h->prof_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->prof_events[i], h->prof_events[i + 1]));
+        h->bounce_ms += ms;
+        h->bounce_launches += (uint64_t)h->depth;
+    }
+    h->prof_used = 0;
+    return 0;
+}
+
+int prof_event(b200pt* h, cudaEvent_t* e)
+{
+    if (h->prof_used == h->prof_events.size()) {
+        cudaEvent_t ne;
+        CK(cudaEventCreate(&ne));
+        h->prof_events.push_back(ne);
+    }
+    *e = h->prof_events[h->prof_used++];
+    return 0;
+}
+
+void pack_camera(const b200pt_camera& c, CamRec& cam)
+{
+    cam.W = c.resolution[0];
+    cam.H = c.resolution[1];
+    for (int k = 0; k < 3; ++k) {
+        cam.pos[k] = c.position[k];
+        cam.view[k] = c.view[k];
+        cam.up[k] = c.up[k];
+        cam.right[k] = c.right[k];
+    }
+    cam.plx = c.pixelLength[0];
+    cam.ply = c.pixelLength[1];
+}
+
+int validate_scene(const b200pt_scene* sc)
+{
+    if (!sc || !sc->geoms || !sc->materials || sc->n_geoms <= 0 || sc->n_materials <= 0) return B200_E_BADARG;
+    if (sc->camera.resolution[0] <= 0 || sc->camera.resolution[1] <= 0 || sc->trace_depth <= 0 || sc->trace_depth > 511)
+        return B200_E_BADARG;
+    for (int i = 0; i < sc->n_geoms; ++i) {
+        if (sc->geoms[i].type != B200PT_SPHERE && sc->geoms[i].type != B200PT_CUBE) return B200_E_UNSUPPORTED;
+        if (sc->geoms[i].materialid < 0 || sc->geoms[i].materialid >= sc->n_materials) return B200_E_BADARG;
+    }
+    for (int i = 0; i < sc->n_materials; ++i)
+        if (sc->materials[i].texture_id != -1) return B200_E_UNSUPPORTED;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -114,15 +176,9 @@ void b200pt_default_options(b200pt_options* o)
 
 int b200pt_create(const b200pt_scene* sc, b200pt** out)
 {
-    if (!sc || !out || !sc->geoms || !sc->materials || sc->n_geoms <= 0 || sc->n_materials <= 0) return B200_E_BADARG;
-    if (sc->camera.resolution[0] <= 0 || sc->camera.resolution[1] <= 0 || sc->trace_depth <= 0 || sc->trace_depth > 511)
-        return B200_E_BADARG;
-    for (int i = 0; i < sc->n_geoms; ++i) {
-        if (sc->geoms[i].type != B200PT_SPHERE && sc->geoms[i].type != B200PT_CUBE) return B200_E_UNSUPPORTED;
-        if (sc->geoms[i].materialid < 0 || sc->geoms[i].materialid >= sc->n_materials) return B200_E_BADARG;
-    }
-    for (int i = 0; i < sc->n_materials; ++i)
-        if (sc->materials[i].texture_id != -1) return B200_E_UNSUPPORTED;
+    if (!out) return B200_E_BADARG;
+    const int bad = validate_scene(sc);
+    if (bad) return bad;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { cudaGetLastError(); return B200_E_NODEVICE; }
 
@@ -137,16 +193,7 @@ int b200pt_create(const b200pt_scene* sc, b200pt** out)
     h->tiles = (h->P + PT_THREADS - 1) / PT_THREADS;
     h->n_prims = sc->n_geoms;
     h->n_mats = sc->n_materials;
-    h->cam.W = h->W;
-    h->cam.H = h->H;
-    for (int k = 0; k < 3; ++k) {
-        h->cam.pos[k] = sc->camera.position[k];
-        h->cam.view[k] = sc->camera.view[k];
-        h->cam.up[k] = sc->camera.up[k];
-        h->cam.right[k] = sc->camera.right[k];
-    }
-    h->cam.plx = sc->camera.pixelLength[0];
-    h->cam.ply = sc->camera.pixelLength[1];
+    pack_camera(sc->camera, h->cam);
     b200pt_default_options(&h->opt);
 
     std::vector<PrimRec> prims(sc->n_geoms);
@@ -174,6 +221,7 @@ int b200pt_destroy(b200pt* h)
     cudaFree(h->d_desc); cudaFree(h->d_segments); cudaFree(h->d_image);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
     delete h;
     return 0;
 }
@@ -193,6 +241,39 @@ int b200pt_reset(b200pt* h)
     CK(cudaMemset(h->d_segments, 0, sizeof(unsigned long long)));
     h->iterations = 0;
     h->launches = 0;
+    h->prof_used = 0;
+    h->bounce_ms = 0.0;
+    h->bounce_launches = 0;
+    return 0;
+}
+
+// Re-upload geometry, materials and camera (same counts, resolution and depth): what the
+// reference does through pathtraceFree + pathtraceInit whenever the camera or a visual setting
+// changes (main.cpp:142-146), without re-allocating.  The accumulation image is NOT cleared.
+int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
+{
+    if (!h) return B200_E_BADARG;
+    const int bad = validate_scene(sc);
+    if (bad) return bad;
+    if (sc->n_geoms != h->n_prims || sc->n_materials != h->n_mats || sc->camera.resolution[0] != h->W ||
+        sc->camera.resolution[1] != h->H || sc->trace_depth != h->depth)
+        return B200_E_BADARG;
+    h->host_prims.resize((size_t)sc->n_geoms);
+    for (int i = 0; i < sc->n_geoms; ++i) pack_prim(sc->geoms[i], h->host_prims[i]);
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaMemcpyAsync(h->d_prims, h->host_prims.data(), sizeof(PrimRec) * h->host_prims.size(), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));      // host_prims / caller memory may be reused on return
+    pack_camera(sc->camera, h->cam);
+    return 0;
+}
+
+int b200pt_set_profiling(b200pt* h, int enable)
+{
+    if (!h) return B200_E_BADARG;
+    int r = collect_profile(h);
+    if (r) return r;
+    h->profiling = enable != 0;
     return 0;
 }
 
@@ -239,6 +320,13 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
         p.in = pools[0];
         p.out = pools[1];
         CK(launch_raygen(p, s));
+        if (h->profiling) {
+            if (h->prof_used >= 8192) { r = collect_profile(h); if (r) return r; }
+            cudaEvent_t e;
+            r = prof_event(h, &e);
+            if (r) return r;
+            CK(cudaEventRecord(e, s));
+        }
         for (int b = 0; b < h->depth; ++b) {
             p.bounce = b;
             if (++h->epoch >= (1u << 30)) {
@@ -248,6 +336,12 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             p.epoch = h->epoch;
             CK(launch_bounce(p, s));
             const Pool t = p.in; p.in = p.out; p.out = t;
+        }
+        if (h->profiling) {
+            cudaEvent_t e;
+            r = prof_event(h, &e);
+            if (r) return r;
+            CK(cudaEventRecord(e, s));
         }
         h->launches += 1 + (uint64_t)h->depth;
         h->last_batch = nb;
@@ -297,6 +391,9 @@ int b200pt_get_stats(b200pt* h, b200pt_stats* st)
     if (h->ev1 && cudaEventQuery(h->ev1) == cudaSuccess && h->iterations) cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
     cudaGetLastError();
     st->last_render_ms = h->last_ms;
+    { int r = collect_profile(h); if (r) return r; }
+    st->bounce_kernel_ms = h->bounce_ms;
+    st->bounce_kernel_launches = h->bounce_launches;
     st->traced_depth = 0;
     if (h->batch_cap && h->last_batch) {
         // TracedDepth (pathtrace.cu:510): bounces the last iteration ran before its pool emptied

@@ -53,7 +53,8 @@ class _OptionsC(ctypes.Structure):
 class _StatsC(ctypes.Structure):
     _fields_ = [("path_segments", ctypes.c_uint64), ("iterations", ctypes.c_uint64),
                 ("kernel_launches", ctypes.c_uint64), ("last_render_ms", ctypes.c_float),
-                ("traced_depth", ctypes.c_int32)]
+                ("traced_depth", ctypes.c_int32), ("bounce_kernel_ms", ctypes.c_double),
+                ("bounce_kernel_launches", ctypes.c_uint64)]
 
 
 assert ctypes.sizeof(Geom) == 272 and ctypes.sizeof(Material) == 48 and ctypes.sizeof(Camera) == 84
@@ -124,6 +125,8 @@ def _lib():
         lib.b200pt_destroy.argtypes = [vp]
         lib.b200pt_set_options.argtypes = [vp, ctypes.POINTER(_OptionsC)]
         lib.b200pt_reset.argtypes = [vp]
+        lib.b200pt_update_scene.argtypes = [vp, ctypes.POINTER(_SceneC), vp]
+        lib.b200pt_set_profiling.argtypes = [vp, ci]
         lib.b200pt_render.argtypes = [vp, ci, ci, ci, vp, ci]
         lib.b200pt_tonemap_u8.argtypes = [vp, ci, vp, vp]
         lib.b200pt_read_sum.argtypes = [vp, vp]
@@ -173,6 +176,16 @@ class Renderer:
     def reset(self):
         check(_lib().b200pt_reset(self._h))
 
+    def update_scene(self, scene, stream=0):
+        """re-upload geoms / materials / camera (same counts and resolution)"""
+        sc = _SceneC(scene.camera, scene.traceDepth, len(scene.geoms), scene.geoms,
+                     len(scene.materials), scene.materials)
+        check(_lib().b200pt_update_scene(self._h, ctypes.byref(sc), stream))
+        self.scene = scene
+
+    def set_profiling(self, enable):
+        check(_lib().b200pt_set_profiling(self._h, int(bool(enable))))
+
     def render(self, first_iter, n_iters, stride=1, stream=0, sync=True):
         check(_lib().b200pt_render(self._h, int(first_iter), int(n_iters), int(stride), stream, int(sync)))
 
@@ -196,7 +209,8 @@ class Renderer:
         check(_lib().b200pt_get_stats(self._h, ctypes.byref(s)))
         return {"path_segments": s.path_segments, "iterations": s.iterations,
                 "kernel_launches": s.kernel_launches, "last_render_ms": s.last_render_ms,
-                "traced_depth": s.traced_depth}
+                "traced_depth": s.traced_depth, "bounce_kernel_ms": s.bounce_kernel_ms,
+                "bounce_kernel_launches": s.bounce_kernel_launches}
 
     # per-stage probes (device pointers, reference AoS layouts; see include/b200_pt.h)
     def debug_raygen(self, iteration, d_segments, stream=0):

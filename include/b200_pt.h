@@ -109,6 +109,8 @@ typedef struct b200pt_stats {
     uint64_t kernel_launches; /* kernels launched since the last reset                           */
     float last_render_ms;     /* CUDA-event time of the most recent b200pt_render call           */
     int32_t traced_depth;     /* GuiDataContainer::TracedDepth of the last iteration             */
+    double bounce_kernel_ms;  /* with profiling on: summed device time of the k_bounce launches  */
+    uint64_t bounce_kernel_launches; /* ... and how many launches that covers                    */
 } b200pt_stats;
 
 void b200pt_default_options(b200pt_options* o);
@@ -119,6 +121,13 @@ int b200pt_destroy(b200pt* h);
 int b200pt_set_options(b200pt* h, const b200pt_options* o);
 /* Zero the accumulation image and the statistics (what pathtraceInit does, pathtrace.cu:121-122). */
 int b200pt_reset(b200pt* h);
+
+/* Re-upload geometry, materials and camera of a scene with the same counts / resolution / depth
+ * (the reference re-runs pathtraceInit on every camera change, main.cpp:142-146).  Host pointers;
+ * synchronises `stream`.  The accumulation image is kept. */
+int b200pt_update_scene(b200pt* h, const b200pt_scene* scene, void* stream);
+/* Per-kernel CUDA-event timing of the bounce kernel (read back through b200pt_get_stats). */
+int b200pt_set_profiling(b200pt* h, int enable);
 
 /* Trace iterations first_iter .. first_iter + (n_iters-1)*iter_stride (1-based, stride >= 1) and
  * add them to the accumulation image.  Asynchronous on `stream` unless `sync` != 0. */

@@ -1,0 +1,253 @@
+"""GPU parity tests of the wavefront path tracer, through the C ABI (include/b200_pt.h).
+
+Tiers:
+  T1  every stage (camera rays, closest hit, shading) on identical inputs, BIT FOR BIT against
+      vectors produced by the reference's own kernels (tests/golden/*.stage.npz) and against the
+      CPU oracle;
+  T3  whole renders against float SUM images written by the reference's own CUDA build
+      (tests/golden/*.refsum.bin): bit-identical with batch = 1 (the reference's accumulation
+      order), and within north_star's tolerance -- mean absolute error <= 1e-3 and PSNR >= 45 dB
+      on the mean image -- with the default batched wavefront;
+  full-size properties at BASELINE's Cornell 800x800: iteration-split additivity, batch
+      invariance, segment accounting, against the oracle on a sample of pixels' worth of work.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle_bindings import PtOracle
+from pt_cases import GOLD, RENDERS, STAGES, bits_equal, gui_from_flags, image_metrics, load_scene, ref_sum
+
+pytestmark = pytest.mark.gpu
+
+MAE_TOL = 1e-3      # north_star: mean absolute error of the mean image
+PSNR_TOL = 45.0     # north_star: PSNR in dB, peak 1.0
+
+
+@pytest.fixture(scope="module")
+def pt():
+    from cuda_pathtracer_b200 import pathtracer as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+    return t
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    return PtOracle()
+
+
+def dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda().reshape(-1)
+
+
+# ---- T1: per-stage ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("scene,tag,flags", STAGES)
+def test_stages_vs_reference_kernels(pt, torch, scene, tag, flags):
+    d = np.load(os.path.join(GOLD, f"{scene}.{tag}.stage.npz"))
+    sc, it = load_scene(scene), int(d["iteration"])
+    r = pt.Renderer(sc)
+    r.set_options(gui_from_flags(flags))
+    P = sc.width * sc.height
+    seg = torch.zeros(P * 12, dtype=torch.float32, device="cuda")
+    r.debug_raygen(it, seg.data_ptr())
+    torch.cuda.synchronize()
+    n = len(d["raygen"])
+    assert bits_equal(seg.cpu().numpy().reshape(P, 12)[:n], d["raygen"])
+    b = 0
+    while f"b{b}_in" in d.files:
+        seg_in, isect, seg_out = d[f"b{b}_in"], d[f"b{b}_isect"], d[f"b{b}_out"]
+        m = len(seg_in)
+        d_seg, d_is = dev(torch, seg_in), torch.zeros(m * 7, dtype=torch.float32, device="cuda")
+        r.debug_intersect(m, d_seg.data_ptr(), d_is.data_ptr())
+        torch.cuda.synchronize()
+        assert bits_equal(d_is.cpu().numpy().reshape(m, 7), isect), f"intersect, bounce {b}"
+        d_is = dev(torch, isect)
+        r.debug_shade(it, m, d_is.data_ptr(), d_seg.data_ptr())
+        torch.cuda.synchronize()
+        assert bits_equal(d_seg.cpu().numpy().reshape(m, 12), seg_out), f"shade, bounce {b}"
+        b += 1
+    r.close()
+
+
+@pytest.mark.parametrize("scene,flags", [("cornell_small", []), ("synthetic_600_small", []),
+                                          ("cornell_glass_small", ["--no-ssaa", "--no-dof"])])
+def test_stages_vs_oracle_all_bounces(pt, torch, oracle, scene, flags):
+    """lock-step wavefront: each stage of every bounce against the CPU oracle on the same inputs"""
+    sc, gui, it = load_scene(scene), gui_from_flags(flags), 7
+    r = pt.Renderer(sc)
+    r.set_options(gui)
+    P = sc.width * sc.height
+    seg = torch.zeros(P * 12, dtype=torch.float32, device="cuda")
+    r.debug_raygen(it, seg.data_ptr())
+    torch.cuda.synchronize()
+    segs = oracle.raygen(sc, gui, it)
+    assert bits_equal(seg.cpu().numpy().reshape(P, 12), segs)
+    for bounce in range(sc.traceDepth):
+        n = len(segs)
+        if n == 0:
+            break
+        want_is = oracle.intersect(sc, segs)
+        d_seg, d_is = dev(torch, segs), torch.zeros(n * 7, dtype=torch.float32, device="cuda")
+        r.debug_intersect(n, d_seg.data_ptr(), d_is.data_ptr())
+        torch.cuda.synchronize()
+        assert bits_equal(d_is.cpu().numpy().reshape(n, 7), want_is), f"intersect, bounce {bounce}"
+        want_out = oracle.shade(sc, gui, it, want_is, segs)
+        r.debug_shade(it, n, d_is.data_ptr(), d_seg.data_ptr())
+        torch.cuda.synchronize()
+        assert bits_equal(d_seg.cpu().numpy().reshape(n, 12), want_out), f"shade, bounce {bounce}"
+        segs = np.ascontiguousarray(want_out[want_out[:, 10].view(np.int32) != 0])
+    r.close()
+
+
+# ---- T3: whole renders ------------------------------------------------------------------------------
+@pytest.mark.parametrize("scene,iters,flags,tag", RENDERS)
+def test_render_bit_exact_vs_reference_cuda(pt, scene, iters, flags, tag):
+    sc = load_scene(scene)
+    r = pt.Renderer(sc)
+    r.set_options(gui_from_flags(flags, batch=1))       # the reference's accumulation order
+    r.render(1, iters)
+    img = r.read_sum()
+    assert bits_equal(img, ref_sum(scene, iters, tag, img.shape))
+    st = r.stats()
+    assert st["iterations"] == iters and st["kernel_launches"] == iters * (1 + sc.traceDepth)
+    r.close()
+
+
+@pytest.mark.parametrize("scene,iters,flags,tag", RENDERS)
+@pytest.mark.parametrize("batch", [0, 3])
+def test_render_batched_within_north_star_tolerance(pt, scene, iters, flags, tag, batch):
+    sc = load_scene(scene)
+    r = pt.Renderer(sc)
+    r.set_options(gui_from_flags(flags, batch=batch))
+    r.render(1, iters)
+    img = r.read_sum()
+    ref = ref_sum(scene, iters, tag, img.shape)
+    mae, psnr = image_metrics(img, ref, iters)
+    assert mae <= MAE_TOL and psnr >= PSNR_TOL
+    # in fact only the order of the per-pixel float additions differs
+    assert np.allclose(img, ref, rtol=2e-6, atol=1e-6)
+    r.close()
+
+
+def test_segments_and_traced_depth_vs_oracle(pt, oracle):
+    sc, gui = load_scene("cornell_small"), gui_from_flags([], batch=4)
+    r = pt.Renderer(sc)
+    r.set_options(gui)
+    r.render(3, 6, 2)                                    # iterations 3, 5, ..., 13
+    img = r.read_sum()
+    want, segments = oracle.render(sc, gui, 3, 6, stride=2)
+    st = r.stats()
+    assert st["path_segments"] == segments
+    assert 1 <= st["traced_depth"] <= sc.traceDepth
+    assert np.allclose(img, want, rtol=2e-6, atol=1e-6)
+    r.reset()
+    assert r.stats()["path_segments"] == 0 and not r.read_sum().any()
+    r.close()
+
+
+def test_reference_shaped_api(pt, torch):
+    """InitDataContainer / pathtraceInit / pathtrace / pathtraceFree (pathtrace.h:6-9): one call per
+    iteration, the SUM image left in scene.state_image, the 8-bit preview in the caller's buffer."""
+    scene, iters, flags, tag = RENDERS[0]
+    sc = load_scene(scene)
+    gui = pt.GuiDataContainer()
+    pt.InitDataContainer(gui)
+    pt.pathtraceFree()                                   # main.cpp:144 calls Free before the first Init
+    pt.pathtraceInit(sc)
+    pbo = torch.zeros(sc.width * sc.height * 4, dtype=torch.uint8, device="cuda")
+    for it in range(1, iters + 1):
+        pt.pathtrace(pbo.data_ptr(), 0, it)
+    assert bits_equal(sc.state_image, ref_sum(scene, iters, tag, sc.state_image.shape))
+    assert 1 <= gui.TracedDepth <= sc.traceDepth
+    # sendImageToPBO (pathtrace.cu:65-86): clamp(int(pix / iter * 255.0), 0, 255), w = 0
+    mean = sc.state_image.astype(np.float32) / np.float32(iters)
+    want = np.clip((mean.astype(np.float64) * 255.0).astype(np.int64), 0, 255).astype(np.uint8)
+    got = pbo.cpu().numpy().reshape(sc.height, sc.width, 4)
+    assert np.array_equal(got[..., :3], want) and not got[..., 3].any()
+    pt.pathtraceFree()
+    with pytest.raises(RuntimeError):
+        pt.pathtrace(None, 0, 1)
+
+
+def test_errors_are_returned_not_fatal(pt):
+    from cuda_pathtracer_b200 import B200Error
+    sc = load_scene("cornell_tiny")
+    sc.geoms[0].type = 2                                 # MESH: not supported yet -> error code
+    with pytest.raises(B200Error):
+        pt.Renderer(sc)
+    sc = load_scene("cornell_tiny")
+    sc.materials[0].texture_id = 0
+    with pytest.raises(B200Error):
+        pt.Renderer(sc)
+    sc = load_scene("cornell_tiny")
+    r = pt.Renderer(sc)
+    gui = pt.GuiDataContainer()
+    gui.batch = -1
+    with pytest.raises(B200Error):
+        r.set_options(gui)
+    r.close()
+
+
+# ---- full size: BASELINE config 2 (Cornell 800x800, depth 8) -------------------------------------------
+def test_full_size_cornell_properties(pt, oracle):
+    sc = load_scene("cornell")
+    assert (sc.width, sc.height, sc.traceDepth) == (800, 800, 8)
+    r = pt.Renderer(sc)
+    g1 = gui_from_flags([], batch=1)
+    r.set_options(g1)
+    r.render(1, 8)
+    a = r.read_sum()
+    seg_a = r.stats()["path_segments"]
+    # (1) batch invariance: same paths, only the float addition order may differ
+    r.reset()
+    r.set_options(gui_from_flags([], batch=0))
+    r.render(1, 8)
+    b = r.read_sum()
+    assert r.stats()["path_segments"] == seg_a
+    assert np.allclose(a, b, rtol=2e-6, atol=1e-6)
+    # (2) iteration-split additivity (what the multi-GPU split relies on): odd + even == all
+    r.reset()
+    r.render(1, 4, 2)
+    r.render(2, 4, 2)
+    c = r.read_sum()
+    assert r.stats()["path_segments"] == seg_a
+    assert np.allclose(a, c, rtol=2e-6, atol=1e-6)
+    # (3) about three segments per camera path on this scene, image mean ~0.14
+    assert 2.5 < seg_a / (8 * 640000) < 3.6
+    assert 0.10 < a.mean() / 8 < 0.18
+    # (4) one full-size iteration against the CPU oracle, bit for bit
+    r.reset()
+    r.set_options(g1)
+    r.render(5, 1)
+    want, seg = oracle.render(sc, g1, 5, 1)
+    assert r.stats()["path_segments"] == seg
+    assert bits_equal(r.read_sum(), want)
+    r.close()
+
+
+def test_live_reference_cuda_build_if_present(pt):
+    """When the reference's own CUDA build travelled with the snapshot (oracle/_ref/ref_pathtracer,
+    built in the build container), run it on a case that has no committed golden."""
+    exe = os.path.join(os.path.dirname(GOLD), "..", "oracle", "_ref", "ref_pathtracer")
+    scene_json = os.path.join(os.path.dirname(GOLD), "..", "scenes", "cornell_tiny.json")
+    if not os.path.exists(exe):
+        pytest.skip("reference CUDA build not present on this box")
+    out = os.path.join("/tmp", "ref_tiny.bin")
+    subprocess.run([exe, scene_json, "--iters", "24", "--out", out, "--aperture", "0.3", "--focal", "8"],
+                   check=True, stdout=subprocess.DEVNULL)
+    sc = load_scene("cornell_tiny")
+    r = pt.Renderer(sc)
+    g = gui_from_flags([], batch=1)
+    g.aperture, g.focal_len = 0.3, 8.0
+    r.set_options(g)
+    r.render(1, 24)
+    img = r.read_sum()
+    assert bits_equal(img, np.fromfile(out, dtype=np.float32).reshape(img.shape))
+    r.close()
