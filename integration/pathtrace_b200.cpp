@@ -1,0 +1,83 @@
+// integration/pathtrace_b200.cpp -- the reference-side binding for the render driver.
+//
+// This is the file a maintainer of the reference adds INSTEAD OF pathtrace.cu, intersections.cu,
+// interactions.cu and stream_compaction/*.cu (path_tracer/src/): it defines the four functions of
+// pathtrace.h:6-9 against the reference's own Scene / GuiDataContainer types and forwards to the
+// C ABI of include/b200_pt.h.  Geom, Material and Camera are passed as they lie in memory (the ABI's
+// POD structs have the same byte layout, sceneStructs.h:24-72).  Conventions kept
+// (pathtrace.cu:108-177,423-528): file-static state, Free tolerates being called before Init, the
+// toggles are read from the GuiDataContainer on every call, the float SUM image is copied back to
+// scene->state.image on every call, the 8-bit preview goes to the caller's DEVICE buffer.
+//
+// oracle/Makefile compiles it against /root/reference together with the reference's unmodified
+// scene.cpp / BVH_tree.cpp / utilities.cpp and the headless main into oracle/_ref/dropin_pathtracer;
+// tests/test_dropin_gpu.py checks its output is bit-identical to the reference build's.
+#include <cstdio>
+#include <cstdlib>
+
+#include <cuda_runtime.h>
+
+#include "pathtrace.h"
+#include "scene.h"
+#include "utilities.h"
+
+#include "b200_pt.h"
+
+static_assert(sizeof(Geom) == sizeof(b200pt_geom) && sizeof(Material) == sizeof(b200pt_material) &&
+                  sizeof(Camera) == sizeof(b200pt_camera), "POD layouts must agree");
+
+static Scene* hst_scene = NULL;
+static GuiDataContainer* guiData = NULL;
+static b200pt* renderer = NULL;
+
+static void check(int code, const char* what)
+{
+    if (code == 0) return;
+    fprintf(stderr, "b200pt (%s): %s\n", what, b200pt_error_string(code));
+    exit(EXIT_FAILURE);                  // the reference's own error convention (checkCUDAErrorFn)
+}
+
+void InitDataContainer(GuiDataContainer* imGuiData) { guiData = imGuiData; }
+
+void pathtraceInit(Scene* scene)
+{
+    hst_scene = scene;
+    b200pt_scene s;
+    s.camera = *reinterpret_cast<const b200pt_camera*>(&scene->state.camera);
+    s.trace_depth = scene->state.traceDepth;
+    s.n_geoms = (int)scene->geoms.size();
+    s.geoms = reinterpret_cast<const b200pt_geom*>(scene->geoms.data());
+    s.n_materials = (int)scene->materials.size();
+    s.materials = reinterpret_cast<const b200pt_material*>(scene->materials.data());
+    check(b200pt_create(&s, &renderer), "pathtraceInit");
+}
+
+void pathtraceFree()
+{
+    b200pt_destroy(renderer);            // no-op on NULL, like cudaFree(NULL) in the reference
+    renderer = NULL;
+}
+
+void pathtrace(uchar4* pbo, int /*frame*/, int iter)
+{
+    b200pt_options o;
+    b200pt_default_options(&o);
+    if (guiData) {
+        o.russian_roulette = guiData->russianRoulette;
+        o.sort_by_material = guiData->sortbyMaterial;
+        o.ssaa = guiData->SSAA;
+        o.dof = guiData->DoF;
+        o.aperture = guiData->aperture;
+        o.focal_len = guiData->focal_len;
+    }
+    o.batch = 1;                          // one iteration per call, the reference's accumulation order
+    check(b200pt_set_options(renderer, &o), "options");
+    check(b200pt_render(renderer, iter, 1, 1, NULL, 0), "pathtrace");
+    if (pbo) check(b200pt_tonemap_u8(renderer, iter, pbo, NULL), "sendImageToPBO");
+    check(b200pt_read_sum(renderer, reinterpret_cast<float*>(hst_scene->state.image.data())), "image copy");
+    if (guiData) {
+        b200pt_stats st;
+        check(b200pt_get_stats(renderer, &st), "stats");
+        guiData->TracedDepth = st.traced_depth;
+    }
+}
