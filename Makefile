@@ -8,7 +8,7 @@ PKG   := cuda_pathtracer_b200
 CSRC  := $(PKG)/csrc
 
 SC_SRCS := $(CSRC)/sc_kernels.cu $(CSRC)/sc_api.cu
-SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/lookback.cuh include/b200_sc.h
+SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/sc_tmpl.cuh $(CSRC)/lookback.cuh include/b200_sc.h
 
 .PHONY: all lib oracle clean
 all: lib oracle
@@ -21,8 +21,11 @@ lib: $(PKG)/libb200sc.so $(PKG)/libb200pt.so
 $(PKG)/libb200sc.so: $(SC_SRCS) $(SC_HDRS)
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(SC_SRCS)
 
-$(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS)
-	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(PT_SRCS)
+# the renderer's material sort scans its histograms with the scan library (as the reference's
+# renderer calls StreamCompaction::Efficient::scan): libb200pt.so NEEDs libb200sc.so ($ORIGIN rpath)
+$(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS) $(PKG)/libb200sc.so include/b200_sc.h
+	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(PT_SRCS) -L$(PKG) -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN'
+
 
 oracle:
 	$(MAKE) -C oracle all

@@ -13,11 +13,12 @@
 #include <vector>
 
 #include "../../include/b200_pt.h"
+#include "../../include/b200_sc.h"
 #include "pt_kernels.cuh"
 
 using namespace ptk;
 
-enum { B200_OK = 0, B200_E_BADARG = 10001, B200_E_NODEVICE = 10002, B200_E_NOMEM = 10003, B200_E_UNSUPPORTED = 10004 };
+enum { B200_E_UNSUPPORTED = 10004 };   // B200_OK / BADARG / NODEVICE / NOMEM come from b200_sc.h
 
 struct b200pt {
     int device = 0;
@@ -33,6 +34,18 @@ struct b200pt {
     unsigned long long* d_desc = nullptr;
     unsigned long long* d_segments = nullptr;
     float* d_image = nullptr;
+    // split pipeline (material sort): hit records, radix-sort permutation ping-pong, digit histograms
+    b200_sc_ctx* sc = nullptr;         // the scan library's workspace (exclusive scan of the histograms)
+    float4* d_hit_n = nullptr;
+    int* d_hit_k = nullptr;
+    int* d_perm[2] = {nullptr, nullptr};
+    int* d_hist = nullptr;
+    int* d_hist_scanned = nullptr;
+    int sort_batch_cap = 0;
+    // first-bounce cache (valid while camera, geometry and the SSAA / DoF toggles stay put)
+    float4* d_cache_n = nullptr;
+    int* d_cache_k = nullptr;
+    bool cache_valid = false;
     unsigned epoch = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     uint64_t iterations = 0, launches = 0;
@@ -94,13 +107,52 @@ int ensure_batch(b200pt* h, int batch)
     if (r) return r;
     r = dev_alloc((void**)&h->d_counts, sizeof(int) * (size_t)(h->depth + 1) * batch);
     if (r) return r;
-    r = dev_alloc((void**)&h->d_desc, sizeof(unsigned long long) * (size_t)batch * h->tiles);
+    r = dev_alloc((void**)&h->d_desc, sizeof(unsigned long long) * (size_t)batch * h->tiles * PT_DESC_STRIDE);
     if (r) return r;
     CK(cudaMemset(h->d_counts, 0, sizeof(int) * (size_t)(h->depth + 1) * batch));
-    CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->tiles));
+    CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->tiles * PT_DESC_STRIDE));
     h->epoch = 0;
     h->batch_cap = batch;
     return 0;
+}
+
+int sort_bins(const b200pt* h) { return h->n_mats < 256 ? h->n_mats : 256; }
+int sort_passes(const b200pt* h)
+{
+    int passes = 1;
+    while (passes < 4 && (h->n_mats - 1) >> (8 * passes)) ++passes;
+    return passes;
+}
+
+// buffers of the split (material-sorted) pipeline, allocated on first use
+int ensure_sort(b200pt* h, int batch)
+{
+    if (batch <= h->sort_batch_cap) return 0;
+    cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
+    cudaFree(h->d_hist); cudaFree(h->d_hist_scanned);
+    h->d_hit_n = nullptr; h->d_hit_k = nullptr; h->d_perm[0] = h->d_perm[1] = nullptr;
+    h->d_hist = h->d_hist_scanned = nullptr; h->sort_batch_cap = 0;
+    const size_t paths = (size_t)batch * h->P;
+    const size_t hist = (size_t)batch * sort_bins(h) * h->tiles + 4;
+    int r = dev_alloc((void**)&h->d_hit_n, sizeof(float4) * paths);
+    if (!r) r = dev_alloc((void**)&h->d_hit_k, sizeof(int) * paths);
+    if (!r) r = dev_alloc((void**)&h->d_perm[0], sizeof(int) * paths);
+    if (!r && sort_passes(h) > 1) r = dev_alloc((void**)&h->d_perm[1], sizeof(int) * paths);
+    if (!r) r = dev_alloc((void**)&h->d_hist, sizeof(int) * hist);
+    if (!r) r = dev_alloc((void**)&h->d_hist_scanned, sizeof(int) * hist);
+    if (r) return r;
+    if (!h->sc) { r = b200_sc_ctx_create(&h->sc); if (r) return r; }
+    h->sort_batch_cap = batch;
+    return 0;
+}
+
+int ensure_cache(b200pt* h)
+{
+    if (h->d_cache_n) return 0;
+    int r = dev_alloc((void**)&h->d_cache_n, sizeof(float4) * (size_t)h->P);
+    if (!r) r = dev_alloc((void**)&h->d_cache_k, sizeof(int) * (size_t)h->P);
+    h->cache_valid = false;
+    return r;
 }
 
 // fold the recorded event pairs into bounce_ms (synchronises on the last one)
@@ -219,6 +271,9 @@ int b200pt_destroy(b200pt* h)
     if (!h) return 0;
     cudaFree(h->d_prims); cudaFree(h->d_mats); cudaFree(h->d_pool); cudaFree(h->d_counts);
     cudaFree(h->d_desc); cudaFree(h->d_segments); cudaFree(h->d_image);
+    cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
+    cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
+    b200_sc_ctx_destroy(h->sc);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
@@ -229,7 +284,9 @@ int b200pt_destroy(b200pt* h)
 int b200pt_set_options(b200pt* h, const b200pt_options* o)
 {
     if (!h || !o || o->batch < 0 || o->batch > 64) return B200_E_BADARG;
-    if (o->sort_by_material || o->first_bounce_cache) return B200_E_UNSUPPORTED;
+    // the cached first-bounce hits depend on the camera rays: any change of what shapes them drops the cache
+    if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache)
+        h->cache_valid = false;
     h->opt = *o;
     return 0;
 }
@@ -265,6 +322,7 @@ int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
     CK(cudaMemcpyAsync(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice, s));
     CK(cudaStreamSynchronize(s));      // host_prims / caller memory may be reused on return
     pack_camera(sc->camera, h->cam);
+    h->cache_valid = false;
     return 0;
 }
 
@@ -312,6 +370,17 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.tiles = h->tiles;
     p.stride = iter_stride;
 
+    const bool sort_on = h->opt.sort_by_material != 0;
+    const bool cache_on = h->opt.first_bounce_cache && !h->opt.ssaa && !h->opt.dof;
+    if (sort_on) { r = ensure_sort(h, batch); if (r) return r; }
+    if (cache_on) { r = ensure_cache(h); if (r) return r; }
+    p.hit_n = h->d_hit_n;
+    p.hit_k = h->d_hit_k;
+    p.hist = h->d_hist;
+    p.hist_scanned = h->d_hist_scanned;
+    p.cache_n = h->d_cache_n;
+    p.cache_k = h->d_cache_k;
+
     CK(cudaEventRecord(h->ev0, s));
     for (int done = 0; done < n_iters; done += batch) {
         const int nb = n_iters - done < batch ? n_iters - done : batch;
@@ -330,11 +399,33 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
         for (int b = 0; b < h->depth; ++b) {
             p.bounce = b;
             if (++h->epoch >= (1u << 30)) {
-                CK(cudaMemsetAsync(h->d_desc, 0, sizeof(unsigned long long) * (size_t)h->batch_cap * h->tiles, s));
+                CK(cudaMemsetAsync(h->d_desc, 0, sizeof(unsigned long long) * (size_t)h->batch_cap * h->tiles * PT_DESC_STRIDE, s));
                 h->epoch = 1;
             }
             p.epoch = h->epoch;
-            CK(launch_bounce(p, s));
+            p.cache_mode = (b == 0 && cache_on) ? (h->cache_valid ? 2 : 1) : 0;
+            if (!sort_on) {
+                CK(launch_bounce(p, s));
+                h->launches += 1;
+            } else {
+                // computeIntersections -> sort_by_key(materialId) -> shadeMaterials (pathtrace.cu:470-497)
+                if (p.cache_mode != 2) { CK(launch_isect(p, s)); h->launches += 1; }
+                const int bins = sort_bins(h), passes = sort_passes(h);
+                for (int pass = 0; pass < passes; ++pass) {
+                    p.perm_in = pass == 0 ? nullptr : h->d_perm[(pass - 1) & 1];
+                    p.perm_out = h->d_perm[pass & 1];
+                    CK(launch_sort_hist(p, pass, bins, s));
+                    r = b200_scan_i32_dev(h->sc, nb * bins * h->tiles, h->d_hist_scanned, h->d_hist, B200_SCAN_LOOKBACK,
+                                          nullptr, nullptr, s);
+                    if (r) return r;
+                    CK(launch_sort_scatter(p, pass, bins, s));
+                    h->launches += 2 + (uint64_t)b200_sc_last_launches(h->sc);
+                }
+                p.perm_in = h->d_perm[(passes - 1) & 1];
+                CK(launch_shade(p, s));
+                h->launches += 1;
+            }
+            if (p.cache_mode == 1) h->cache_valid = true;   // later launches are stream-ordered behind the fill
             const Pool t = p.in; p.in = p.out; p.out = t;
         }
         if (h->profiling) {
@@ -343,7 +434,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             if (r) return r;
             CK(cudaEventRecord(e, s));
         }
-        h->launches += 1 + (uint64_t)h->depth;
+        h->launches += 1;
         h->last_batch = nb;
     }
     CK(cudaEventRecord(h->ev1, s));

@@ -103,6 +103,150 @@ __global__ void __launch_bounds__(PT_THREADS) k_raygen(const __grid_constant__ R
 }
 
 // ------------------------------------------------------------------------------------------------
+// Pieces shared by the fused bounce kernel and the split (material-sorted) pipeline.
+
+struct HitRec {       // ShadeableIntersection without the texture coordinate (sceneStructs.h:92-97)
+    float t;          // -1 = miss
+    V3 n;
+    int mat;          // 0 on a miss: the reference memsets the record (pathtrace.cu:466)
+};
+
+__device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
+{
+    if (threadIdx.x == 0) {
+        mbar_init(&sh.bar[0], 1);
+        mbar_init(&sh.bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+}
+
+// producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
+__device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared& sh, MatRec* smats, int n_smem_mats,
+                                            PrimRec* sprims, bool want_prims)
+{
+    if (threadIdx.x != 0) return;
+    const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
+    const int chunk_cap = n_chunks > 1 ? PT_CHUNK : p.n_prims;
+    const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
+    const int n0 = want_prims ? min(chunk_cap, p.n_prims) : 0;
+    mbar_expect_tx(&sh.bar[0], mat_bytes + (unsigned)(n0 * sizeof(PrimRec)));
+    if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
+    if (n0) bulk_g2s(sprims, p.prims, (unsigned)(n0 * sizeof(PrimRec)), &sh.bar[0]);
+    if (want_prims && n_chunks > 1) {
+        const int n1 = min(PT_CHUNK, p.n_prims - PT_CHUNK);
+        mbar_expect_tx(&sh.bar[1], (unsigned)(n1 * sizeof(PrimRec)));
+        bulk_g2s(sprims + PT_CHUNK, p.prims + PT_CHUNK, (unsigned)(n1 * sizeof(PrimRec)), &sh.bar[1]);
+    }
+}
+
+// computeIntersections (pathtrace.cu:230-298) over the TMA-staged primitive chunks.  Every thread of
+// the CTA must call it (it contains the chunk barriers); inactive threads only take part in those.
+__device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, BounceShared& sh, const PrimRec* sprims,
+                                                     bool active, const V3& o, const V3& d)
+{
+    const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
+    float t_min = 3.402823466e+38f;
+    int hit = -1;
+    Cand best;
+    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+    for (int ch = 0; ch < n_chunks; ++ch) {
+        mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
+        const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
+        const PrimRec* sp = sprims + (n_chunks > 1 ? (ch & 1) * PT_CHUNK : 0);
+        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, t_min, hit, best);
+        if (ch + 2 < n_chunks) {                     // refill this buffer with chunk ch + 2
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const int n2 = min(PT_CHUNK, p.n_prims - (ch + 2) * PT_CHUNK);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(&sh.bar[ch & 1], (unsigned)(n2 * sizeof(PrimRec)));
+                bulk_g2s(const_cast<PrimRec*>(sprims) + (ch & 1) * PT_CHUNK, p.prims + (size_t)(ch + 2) * PT_CHUNK,
+                         (unsigned)(n2 * sizeof(PrimRec)), &sh.bar[ch & 1]);
+            }
+        }
+    }
+    HitRec h;
+    h.t = -1.0f;
+    h.n = v3(0.f, 0.f, 0.f);
+    h.mat = 0;
+    if (hit >= 0) {
+        const PrimRec& g = n_chunks > 1 ? p.prims[hit] : sprims[hit];
+        h.n = prim_normal(g, best);
+        h.t = t_min;
+        h.mat = g.material;
+    }
+    return h;
+}
+
+__device__ __forceinline__ PathState load_path(const Pool& pool, size_t at)
+{
+    const float4 a = pool.a[at], b = pool.b[at], c = pool.c[at];
+    PathState s;
+    s.o = v3(a.x, a.y, a.z);  s.pixel = __float_as_int(a.w);
+    s.d = v3(b.x, b.y, b.z);  s.remaining = __float_as_int(b.w);
+    s.c = v3(c.x, c.y, c.z);  s.bounces = __float_as_int(c.w);
+    return s;
+}
+
+// shadeMaterials + scatterRay for the path at compacted slot `idx`, finalGather for a path that
+// ends here, and the stable single-pass compaction of the survivors into the other pool.
+// Every thread of the CTA must call it.
+__device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceShared& sh, const MatRec* smats,
+                                                  int n_smem_mats, PathState& s, const HitRec& h, bool active,
+                                                  int slot, int tile, int idx, int n_live, int* count_out)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    bool live = false;
+    if (active) {
+        const MatRec& m = n_smem_mats ? smats[h.mat] : p.mats[h.mat];
+        const int iter = p.iter0 + slot * p.stride;
+        live = shade_exact(s, h.t, h.n, m, iter, idx, p.opt.rr);
+        if (!live && (s.c.x != 0.0f || s.c.y != 0.0f || s.c.z != 0.0f)) {
+            // finalGather (pathtrace.cu:347-356) for this path, at termination: one add per pixel
+            // per iteration, issued in iteration order when batch == 1
+            float* px = p.image + 3 * (size_t)s.pixel;
+            atomicAdd(px + 0, s.c.x);
+            atomicAdd(px + 1, s.c.y);
+            atomicAdd(px + 2, s.c.z);
+        }
+    }
+    // ---- stable compaction of the survivors (mark_valid + scan + keep, pathtrace.cu:359-407) ---
+    const unsigned bal = __ballot_sync(FULL_MASK, live);
+    const int wrank = __popc(bal & ((1u << lane) - 1u));
+    if (lane == 0) sh.warp_cnt[warp] = __popc(bal);
+    __syncthreads();
+    int warp_prefix = 0, aggregate = 0;
+#pragma unroll
+    for (int w = 0; w < PT_THREADS / 32; ++w) {
+        const int c = sh.warp_cnt[w];
+        if (w < warp) warp_prefix += c;
+        aggregate += c;
+    }
+    if (warp == 0) {
+        unsigned long long* desc = p.desc + (size_t)slot * p.tiles * PT_DESC_STRIDE;
+        const int e = b200::lb_exclusive_prefix_cfg<1, b200::LB_DEFAULT_BACKOFF_NS, PT_DESC_STRIDE>(
+            desc, (unsigned)tile, p.epoch, aggregate, 0, lane);
+        if (lane == 0) {
+            sh.tile_exclusive = e;
+            if (tile == (n_live - 1) / PT_THREADS) *count_out = e + aggregate;
+        }
+    }
+    __syncthreads();
+    if (live) {
+        const size_t at = (size_t)slot * p.P + (size_t)(sh.tile_exclusive + warp_prefix + wrank);
+        p.out.a[at] = make_float4(s.o.x, s.o.y, s.o.z, __int_as_float(s.pixel));
+        p.out.b[at] = make_float4(s.d.x, s.d.y, s.d.z, __int_as_float(s.remaining));
+        p.out.c[at] = make_float4(s.c.x, s.c.y, s.c.z, __int_as_float(s.bounces));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_bounce: the fused bounce.  CACHE (first-bounce cache, bounce 0 only, valid when the camera rays
+// do not change between iterations, i.e. SSAA and DoF off): 0 = off, 1 = trace and fill the cache
+// (slot 0 writes it), 2 = replace the closest-hit search by one 20-byte cache read per path.
+template <int CACHE>
 __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -119,117 +263,172 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         if (tile == 0 && threadIdx.x == 0) *count_out = 0;
         return;
     }
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
-    const int chunk_cap = n_chunks > 1 ? PT_CHUNK : p.n_prims;
-
-    if (threadIdx.x == 0) {
-        mbar_init(&sh.bar[0], 1);
-        mbar_init(&sh.bar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        if (tile == 0) atomicAdd(p.segments, (unsigned long long)n_live);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {                          // producer: stage materials + first chunks
-        const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
-        const int n0 = min(chunk_cap, p.n_prims);
-        mbar_expect_tx(&sh.bar[0], mat_bytes + (unsigned)(n0 * sizeof(PrimRec)));
-        if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
-        bulk_g2s(sprims, p.prims, (unsigned)(n0 * sizeof(PrimRec)), &sh.bar[0]);
-        if (n_chunks > 1) {
-            const int n1 = min(PT_CHUNK, p.n_prims - PT_CHUNK);
-            mbar_expect_tx(&sh.bar[1], (unsigned)(n1 * sizeof(PrimRec)));
-            bulk_g2s(sprims + PT_CHUNK, p.prims + PT_CHUNK, (unsigned)(n1 * sizeof(PrimRec)), &sh.bar[1]);
-        }
-    }
+    if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
+    bounce_barriers_init(sh);
+    stage_begin(p, sh, smats, n_smem_mats, sprims, CACHE != 2);
 
     // this thread's path (overlaps the bulk copies)
     const int idx = tile * PT_THREADS + threadIdx.x;
     const bool active = idx < n_live;
-    PathState s;
-    {
-        const size_t at = (size_t)slot * p.P + (active ? idx : 0);
-        const float4 a = p.in.a[at], b = p.in.b[at], c = p.in.c[at];
-        s.o = v3(a.x, a.y, a.z);  s.pixel = __float_as_int(a.w);
-        s.d = v3(b.x, b.y, b.z);  s.remaining = __float_as_int(b.w);
-        s.c = v3(c.x, c.y, c.z);  s.bounces = __float_as_int(c.w);
-    }
+    PathState s = load_path(p.in, (size_t)slot * p.P + (active ? idx : 0));
 
-    // ---- closest hit (computeIntersections, pathtrace.cu:230-298) ------------------------------
-    float t_min = 3.402823466e+38f;
-    int hit = -1;
-    Cand best;
-    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-    for (int ch = 0; ch < n_chunks; ++ch) {
-        mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
-        const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
-        const PrimRec* sp = sprims + (n_chunks > 1 ? (ch & 1) * PT_CHUNK : 0);
-        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, s.o, s.d, t_min, hit, best);
-        if (ch + 2 < n_chunks) {                     // refill this buffer with chunk ch + 2
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                const int n2 = min(PT_CHUNK, p.n_prims - (ch + 2) * PT_CHUNK);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_expect_tx(&sh.bar[ch & 1], (unsigned)(n2 * sizeof(PrimRec)));
-                bulk_g2s(sprims + (ch & 1) * PT_CHUNK, p.prims + (size_t)(ch + 2) * PT_CHUNK,
-                         (unsigned)(n2 * sizeof(PrimRec)), &sh.bar[ch & 1]);
-            }
+    HitRec h;
+    if (CACHE == 2) {
+        const float4 cn = p.cache_n[active ? idx : 0];
+        h.t = cn.x; h.n = v3(cn.y, cn.z, cn.w);
+        h.mat = p.cache_k[active ? idx : 0];
+        mbar_wait(&sh.bar[0], 0u);                  // the materials
+    } else {
+        h = closest_hit_staged(p, sh, sprims, active, s.o, s.d);
+        if (CACHE == 1 && slot == 0 && active) {
+            p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+            p.cache_k[idx] = h.mat;
         }
     }
+    shade_and_compact(p, sh, smats, n_smem_mats, s, h, active, slot, tile, idx, n_live, count_out);
+}
 
-    // ---- shade (shadeMaterials + scatterRay) ---------------------------------------------------
-    bool live = false;
+// ------------------------------------------------------------------------------------------------
+// The split pipeline used when paths are bucketed by material between intersection and shading
+// (thrust::sort_by_key on materialId, pathtrace.cu:410-414,479-491): k_isect writes the hit
+// records, k_sort_hist / (scan) / k_sort_scatter build the stable sorted order as a permutation
+// (LSD radix, 8 bits per pass, one pass for up to 256 materials), k_shade gathers through it.
+__global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(smem_raw + sizeof(BounceShared));
+    const int slot = blockIdx.y;
+    const int tile = blockIdx.x;
+    const int n_live = p.counts[p.bounce * p.batch + slot];
+    if (tile * PT_THREADS >= n_live) return;
+    if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
+    bounce_barriers_init(sh);
+    stage_begin(p, sh, nullptr, 0, sprims, true);
+    const int idx = tile * PT_THREADS + threadIdx.x;
+    const bool active = idx < n_live;
+    const size_t at = (size_t)slot * p.P + (active ? idx : 0);
+    const float4 a = p.in.a[at], b = p.in.b[at];
+    const HitRec h = closest_hit_staged(p, sh, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
     if (active) {
-        V3 n = v3(0.f, 0.f, 0.f);
-        float t = -1.0f;
-        int mat_id = 0;
-        if (hit >= 0) {
-            const PrimRec& g = n_chunks > 1 ? p.prims[hit] : sprims[hit];
-            n = prim_normal(g, best);
-            t = t_min;
-            mat_id = g.material;
-        }
-        const MatRec& m = n_smem_mats ? smats[mat_id] : p.mats[mat_id];
-        const int iter = p.iter0 + slot * p.stride;
-        live = shade_exact(s, t, n, m, iter, idx, p.opt.rr);
-        if (!live && (s.c.x != 0.0f || s.c.y != 0.0f || s.c.z != 0.0f)) {
-            // finalGather (pathtrace.cu:347-356) for this path, at termination: one add per pixel
-            // per iteration, issued in iteration order when batch == 1
-            float* px = p.image + 3 * (size_t)s.pixel;
-            atomicAdd(px + 0, s.c.x);
-            atomicAdd(px + 1, s.c.y);
-            atomicAdd(px + 2, s.c.z);
+        p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+        p.hit_k[at] = h.mat;
+        if (p.cache_mode == 1 && slot == 0) {
+            p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+            p.cache_k[idx] = h.mat;
         }
     }
+}
 
-    // ---- stable compaction of the survivors (mark_valid + scan + keep, pathtrace.cu:359-407) ---
-    const unsigned bal = __ballot_sync(FULL_MASK, live);
-    const int wrank = __popc(bal & ((1u << lane) - 1u));
-    if (lane == 0) sh.warp_cnt[warp] = __popc(bal);
+// digit of the sort key of the element at sorted position j of this pass
+__device__ __forceinline__ int sort_digit(const RenderParams& p, int slot, int j, int pass, int& src)
+{
+    src = pass == 0 ? j : p.perm_in[(size_t)slot * p.P + j];
+    const int* keys = p.cache_mode == 2 ? p.cache_k : p.hit_k + (size_t)slot * p.P;
+    return (keys[src] >> (8 * pass)) & 255;
+}
+
+struct SortShared {
+    int cnt[PT_THREADS / 32][256];      // per-warp digit counts
+};
+
+// per-warp counts of each digit and this thread's stable rank among the equal digits of its warp
+__device__ __forceinline__ int warp_digit_rank(SortShared& sh, bool active, int digit, int bins)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int b = lane; b < bins; b += 32) sh.cnt[warp][b] = 0;
+    __syncwarp();
+    const unsigned act = __ballot_sync(FULL_MASK, active);
+    int rank = 0;
+    if (active) {
+        const unsigned peers = __match_any_sync(act, digit);
+        rank = __popc(peers & ((1u << lane) - 1u));
+        if (rank == 0) sh.cnt[warp][digit] = __popc(peers);
+    }
+    return rank;
+}
+
+// hist[(slot * bins + bin) * tiles + tile] = number of elements of `tile` whose digit is `bin`
+__global__ void __launch_bounds__(PT_THREADS) k_sort_hist(const __grid_constant__ RenderParams p, int pass, int bins)
+{
+    __shared__ SortShared sh;
+    const int slot = blockIdx.y, tile = blockIdx.x;
+    const int n_live = p.counts[p.bounce * p.batch + slot];
+    int* hist = p.hist + (size_t)slot * bins * p.tiles;
+    if (tile * PT_THREADS >= n_live) {               // every tile writes its column: no memset
+        for (int b = threadIdx.x; b < bins; b += PT_THREADS) hist[(size_t)b * p.tiles + tile] = 0;
+        return;
+    }
+    const int j = tile * PT_THREADS + threadIdx.x;
+    const bool active = j < n_live;
+    int src = 0;
+    const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
+    warp_digit_rank(sh, active, digit, bins);
     __syncthreads();
-    int warp_prefix = 0, aggregate = 0;
+    for (int b = threadIdx.x; b < bins; b += PT_THREADS) {
+        int t = 0;
 #pragma unroll
-    for (int w = 0; w < PT_THREADS / 32; ++w) {
-        const int c = sh.warp_cnt[w];
-        if (w < warp) warp_prefix += c;
-        aggregate += c;
+        for (int w = 0; w < PT_THREADS / 32; ++w) t += sh.cnt[w][b];
+        hist[(size_t)b * p.tiles + tile] = t;
     }
-    if (warp == 0) {
-        unsigned long long* desc = p.desc + (size_t)slot * p.tiles;
-        const int e = b200::lb_exclusive_prefix(desc, (unsigned)tile, p.epoch, aggregate, 0, lane);
-        if (lane == 0) {
-            sh.tile_exclusive = e;
-            if (tile == (n_live - 1) / PT_THREADS) *count_out = e + aggregate;
-        }
-    }
+}
+
+// perm_out[slot][offset(bin, tile) + rank] = source slot; offsets = exclusive scan of hist
+__global__ void __launch_bounds__(PT_THREADS) k_sort_scatter(const __grid_constant__ RenderParams p, int pass, int bins)
+{
+    __shared__ SortShared sh;
+    const int slot = blockIdx.y, tile = blockIdx.x;
+    const int n_live = p.counts[p.bounce * p.batch + slot];
+    if (tile * PT_THREADS >= n_live) return;
+    const int* offs = p.hist_scanned + (size_t)slot * bins * p.tiles;
+    const int base = offs[0];                        // everything in the slots before this one
+    const int j = tile * PT_THREADS + threadIdx.x;
+    const bool active = j < n_live;
+    int src = 0;
+    const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
+    const int rank = warp_digit_rank(sh, active, digit, bins);
     __syncthreads();
-    if (live) {
-        const size_t at = (size_t)slot * p.P + (size_t)(sh.tile_exclusive + warp_prefix + wrank);
-        p.out.a[at] = make_float4(s.o.x, s.o.y, s.o.z, __int_as_float(s.pixel));
-        p.out.b[at] = make_float4(s.d.x, s.d.y, s.d.z, __int_as_float(s.remaining));
-        p.out.c[at] = make_float4(s.c.x, s.c.y, s.c.z, __int_as_float(s.bounces));
+    if (active) {
+        const int warp = threadIdx.x >> 5;
+        int before = 0;
+        for (int w = 0; w < warp; ++w) before += sh.cnt[w][digit];
+        const int pos = offs[(size_t)digit * p.tiles + tile] - base + before + rank;
+        p.perm_out[(size_t)slot * p.P + pos] = src;
     }
+}
+
+// shadeMaterials on the sorted order: slot j of the sorted array is source slot perm[j]; the RNG
+// seed uses j, exactly as the reference's shading kernel indexes the sorted arrays.
+__global__ void __launch_bounds__(PT_THREADS) k_shade(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
+    const int n_smem_mats = p.n_mats <= PT_SMEM_MATS ? p.n_mats : 0;
+    MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(BounceShared));
+    const int slot = blockIdx.y;
+    const int tile = blockIdx.x;
+    const int n_live = p.counts[p.bounce * p.batch + slot];
+    int* count_out = p.counts + (p.bounce + 1) * p.batch + slot;
+    if (tile * PT_THREADS >= n_live) {
+        if (tile == 0 && threadIdx.x == 0) *count_out = 0;
+        return;
+    }
+    if (p.cache_mode == 2 && tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
+    bounce_barriers_init(sh);
+    stage_begin(p, sh, smats, n_smem_mats, nullptr, false);
+    const int j = tile * PT_THREADS + threadIdx.x;
+    const bool active = j < n_live;
+    const int src = active ? (p.perm_in ? p.perm_in[(size_t)slot * p.P + j] : j) : 0;
+    const size_t at = (size_t)slot * p.P + src;
+    PathState s = load_path(p.in, at);
+    HitRec h;
+    {
+        const float4 hn = p.cache_mode == 2 ? p.cache_n[src] : p.hit_n[at];
+        h.t = hn.x; h.n = v3(hn.y, hn.z, hn.w);
+        h.mat = p.cache_mode == 2 ? p.cache_k[src] : p.hit_k[at];
+    }
+    mbar_wait(&sh.bar[0], 0u);                       // the materials
+    shade_and_compact(p, sh, smats, n_smem_mats, s, h, active, slot, tile, j, n_live, count_out);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -325,8 +524,13 @@ size_t bounce_smem_bytes(int n_prims, int n_mats)
 
 cudaError_t configure_kernels()
 {
-    return cudaFuncSetAttribute(k_bounce, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS));
+    const int cap = (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS);
+    cudaError_t e = cudaFuncSetAttribute(k_bounce<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    return e;
 }
 
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
@@ -337,7 +541,35 @@ cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
 
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
 {
-    k_bounce<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(p.n_prims, p.n_mats), s>>>(p);
+    const dim3 grid(p.tiles, p.batch);
+    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats);
+    if (p.cache_mode == 1) k_bounce<1><<<grid, PT_THREADS, smem, s>>>(p);
+    else if (p.cache_mode == 2) k_bounce<2><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats), s>>>(p);
+    else k_bounce<0><<<grid, PT_THREADS, smem, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
+{
+    k_isect<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(p.n_prims, 0), s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sort_hist(const RenderParams& p, int pass, int bins, cudaStream_t s)
+{
+    k_sort_hist<<<dim3(p.tiles, p.batch), PT_THREADS, 0, s>>>(p, pass, bins);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaStream_t s)
+{
+    k_sort_scatter<<<dim3(p.tiles, p.batch), PT_THREADS, 0, s>>>(p, pass, bins);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shade(const RenderParams& p, cudaStream_t s)
+{
+    k_shade<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(0, p.n_mats), s>>>(p);
     return cudaGetLastError();
 }
 

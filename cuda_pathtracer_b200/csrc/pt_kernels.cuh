@@ -9,6 +9,9 @@ namespace ptk {
 constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
+constexpr int PT_DESC_STRIDE = 16;         // 64-bit words between look-back descriptors: one 128-B line each
+                                           // (packed descriptors make the lines around the prefix frontier an
+                                           // L2 hot spot, see lookback.cuh)
 
 // SoA path pool: three 16-byte words per path.
 //   a = origin.xyz    | pixelIndex
@@ -38,11 +41,26 @@ struct RenderParams {
     int iter0, stride;                 // slot s traces iteration iter0 + s * stride
     int bounce;                        // which bounce this launch is
     unsigned epoch;                    // look-back epoch of this launch
+    // split pipeline (material sort) and first-bounce cache
+    float4* hit_n;                     // [batch][P] hit record {t, normal}
+    int* hit_k;                        // [batch][P] hit record material id (the sort key; 0 on a miss)
+    const int* perm_in;                // [batch][P] sorted position -> source slot (nullptr = identity)
+    int* perm_out;
+    int* hist;                         // [batch][bins][tiles] digit counts per tile
+    const int* hist_scanned;           // exclusive scan of hist (flattened)
+    float4* cache_n;                   // [P] first-bounce cache
+    int* cache_k;
+    int cache_mode;                    // at bounce 0: 0 = off, 1 = fill, 2 = use
 };
 
 size_t bounce_smem_bytes(int n_prims, int n_mats);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
-cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);
+cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);           // fused (honours p.cache_mode)
+// split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
+cudaError_t launch_isect(const RenderParams& p, cudaStream_t s);
+cudaError_t launch_sort_hist(const RenderParams& p, int pass, int bins, cudaStream_t s);
+cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaStream_t s);
+cudaError_t launch_shade(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s);
 // per-stage probes on the reference's AoS layouts (PathSegment 12 words, ShadeableIntersection 7 words)
 cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments, cudaStream_t s);

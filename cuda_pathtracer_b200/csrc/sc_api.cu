@@ -54,10 +54,10 @@ int ensure(void** p, size_t* cap, size_t want_elems, size_t elem_bytes, bool zer
 
 int ensure_lookback(b200_sc_ctx* c, unsigned n)
 {
-    const size_t tiles = sc_num_tiles(n);
+    const size_t tiles = sc_desc_words(n);
     if (c->desc_cap < tiles) {
         // new array is zero => every word reads as "epoch 0, not ready"; epochs start at 1
-        size_t want = tiles < 1024 ? 1024 : tiles;
+        size_t want = tiles < 16384 ? 16384 : tiles;
         int r = ensure((void**)&c->desc, &c->desc_cap, want, sizeof(unsigned long long), true);
         if (r) return r;
     }

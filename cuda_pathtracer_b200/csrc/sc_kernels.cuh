@@ -10,7 +10,25 @@ constexpr int SC_VEC = 4;                             // int4 loads per thread
 constexpr int SC_ITEMS = SC_VEC * 4;                  // 16 ints per thread
 constexpr int SC_TILE = SC_THREADS * SC_ITEMS;        // 4096 ints = 16 KB per tile
 
-inline unsigned sc_num_tiles(unsigned n) { return (n + SC_TILE - 1) / SC_TILE; }
+inline unsigned sc_num_tiles(unsigned n) { return (unsigned)(((unsigned long long)n + SC_TILE - 1) / SC_TILE); }
+
+// single-pass (decoupled look-back) scan and compact: tuned on a B200 with benchmarks/sc_tune.cu
+// (profiles/r1_sc_tune_v3.jsonl).  At 2^28 ints: scan 128 x 8 -> 5.5 TB/s, compact 256 x 8 -> 4.7 TB/s;
+// the decisive knob is SC_LB_STRIDE (one 128-byte line per descriptor), see lookback.cuh.
+constexpr int SC_LB_THREADS = 128;                    // scan: 128 threads x 8 vectors = 4096 ints per tile
+constexpr int SC_LB_VEC = 8;
+constexpr int SC_LB_TILE = SC_LB_THREADS * SC_LB_VEC * 4;
+constexpr int SC_CP_THREADS = 256;                    // compact: 256 threads x 8 vectors = 8192 ints per tile
+constexpr int SC_CP_VEC = 8;
+constexpr int SC_CP_TILE = SC_CP_THREADS * SC_CP_VEC * 4;
+constexpr int SC_LB_WINDOW = 1;                       // look-back window = 32 * this descriptors
+constexpr int SC_LB_BACKOFF_NS = 0;                   // sleep between polls of an unpublished descriptor
+constexpr int SC_LB_STRIDE = 16;                      // 64-bit words between descriptors (128 B)
+constexpr bool SC_LB_TICKET = false;                  // tile id = blockIdx.x (see sc_tmpl.cuh)
+inline unsigned sc_lb_num_tiles(unsigned n) { return (unsigned)(((unsigned long long)n + SC_LB_TILE - 1) / SC_LB_TILE); }
+inline unsigned sc_cp_num_tiles(unsigned n) { return (unsigned)(((unsigned long long)n + SC_CP_TILE - 1) / SC_CP_TILE); }
+// descriptor words a launch over n elements needs (scan tiles are the smaller ones)
+inline size_t sc_desc_words(unsigned n) { return (size_t)sc_lb_num_tiles(n) * SC_LB_STRIDE; }
 
 // Single-pass decoupled look-back exclusive scan (B4/B6 replacement).  desc: >= num_tiles words,
 // zero at allocation; tickets: 2 unsigned, zero at allocation; epoch: bumped per launch.

@@ -36,6 +36,10 @@ RENDERS = [
     ("cornell_small_mirror", 16, [], "default"),
     ("cornell_glass_small", 16, [], "default"),
     ("synthetic_600_small", 4, [], "default"),
+    # material sort on (tests/pt_cases.py SORT_RENDERS)
+    ("cornell_glass_small", 16, ["--sort"], "sort"),
+    ("synthetic_600_small", 4, ["--sort"], "sort"),
+    ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
 ]
 
 

@@ -16,6 +16,13 @@ RENDERS = [
     ("cornell_glass_small", 16, [], "default"),
     ("synthetic_600_small", 4, [], "default"),
 ]
+# material sort on (thrust::sort_by_key in the reference, pathtrace.cu:479-491): the paths differ
+# from the unsorted ones because the shading seed is the slot index AFTER sorting
+SORT_RENDERS = [
+    ("cornell_glass_small", 16, ["--sort"], "sort"),
+    ("synthetic_600_small", 4, ["--sort"], "sort"),
+    ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
+]
 # per-stage vectors from the reference's own kernels (tests/golden/make_pt_stage_golden.py)
 STAGES = [("cornell_tiny", "default", []), ("cornell_tiny", "plain", ["--no-ssaa", "--no-dof", "--no-rr"]),
           ("cornell_glass_small", "default", [])]
@@ -30,6 +37,7 @@ def gui_from_flags(flags, batch=0):
     g.SSAA = "--no-ssaa" not in flags
     g.DoF = "--no-dof" not in flags
     g.russianRoulette = "--no-rr" not in flags
+    g.sortbyMaterial = "--sort" in flags
     g.batch = batch
     return g
 

@@ -18,7 +18,7 @@ import numpy as np
 import pytest
 
 from oracle_bindings import PtOracle
-from pt_cases import GOLD, RENDERS, STAGES, bits_equal, gui_from_flags, image_metrics, load_scene, ref_sum
+from pt_cases import GOLD, RENDERS, SORT_RENDERS, STAGES, bits_equal, gui_from_flags, image_metrics, load_scene, ref_sum
 
 pytestmark = pytest.mark.gpu
 
@@ -133,6 +133,83 @@ def test_render_batched_within_north_star_tolerance(pt, scene, iters, flags, tag
     assert mae <= MAE_TOL and psnr >= PSNR_TOL
     # in fact only the order of the per-pixel float additions differs
     assert np.allclose(img, ref, rtol=2e-6, atol=1e-6)
+    r.close()
+
+
+# ---- material sort (A9) and first-bounce cache ----------------------------------------------------------
+def have_golden(scene, iters, tag):
+    return os.path.exists(os.path.join(GOLD, f"{scene}.{tag}.{iters}it.refsum.bin"))
+
+
+@pytest.mark.parametrize("scene,iters,flags,tag", SORT_RENDERS)
+def test_sorted_render_bit_exact_vs_reference_cuda(pt, oracle, scene, iters, flags, tag):
+    """sort-by-material on: bit-identical to the reference's CUDA build (thrust::sort_by_key) and to
+    the oracle's stable sort, with batch = 1; same paths (segment count) with the default batch"""
+    sc = load_scene(scene)
+    gui = gui_from_flags(flags, batch=1)
+    r = pt.Renderer(sc)
+    r.set_options(gui)
+    r.render(1, iters)
+    img = r.read_sum()
+    want, segments = oracle.render(sc, gui, 1, iters)
+    assert bits_equal(img, want)
+    assert r.stats()["path_segments"] == segments
+    if have_golden(scene, iters, tag):
+        assert bits_equal(img, ref_sum(scene, iters, tag, img.shape))
+    r.reset()
+    r.set_options(gui_from_flags(flags, batch=0))
+    r.render(1, iters)
+    assert r.stats()["path_segments"] == segments
+    assert np.allclose(r.read_sum(), want, rtol=2e-6, atol=1e-6)
+    r.close()
+
+
+def test_sorted_golden_fixtures_present():
+    missing = [c for c in SORT_RENDERS if not have_golden(c[0], c[1], c[3])]
+    assert not missing, f"reference-CUDA goldens missing for {missing}: run tests/golden/make_pt_golden.py renders"
+
+
+@pytest.mark.parametrize("scene,flags", [("cornell_small", ["--no-ssaa", "--no-dof"]),
+                                          ("cornell_glass_small", ["--no-ssaa", "--no-dof", "--sort"]),
+                                          ("synthetic_600_small", ["--no-ssaa", "--no-dof"])])
+@pytest.mark.parametrize("batch", [1, 3])
+def test_first_bounce_cache_changes_nothing(pt, scene, flags, batch):
+    """the cache replaces bounce 0's closest-hit search by a read of the identical record: the image
+    must be bit-identical with batch = 1 (and the same paths otherwise); it is ignored (not an
+    error) while SSAA or DoF is on, because the camera rays then differ per iteration"""
+    sc = load_scene(scene)
+    r = pt.Renderer(sc)
+    gui = gui_from_flags(flags, batch=batch)
+    r.set_options(gui)
+    r.render(1, 9)
+    plain, seg = r.read_sum(), r.stats()["path_segments"]
+    r.reset()
+    gui.firstBounceCache = True
+    r.set_options(gui)
+    r.render(1, 4)                       # fills the cache in the first batch, uses it afterwards
+    r.render(5, 5)
+    cached = r.read_sum()
+    assert r.stats()["path_segments"] == seg
+    if batch == 1:
+        assert bits_equal(cached, plain)
+    else:
+        assert np.allclose(cached, plain, rtol=2e-6, atol=1e-6)
+    # a scene update drops the cache (the reference re-inits on every camera change)
+    r.update_scene(sc)
+    r.reset()
+    r.render(1, 9)
+    assert np.allclose(r.read_sum(), plain, rtol=2e-6, atol=1e-6)
+    # with SSAA on the option is ignored
+    r.reset()
+    gui.SSAA = True
+    r.set_options(gui)
+    r.render(1, 3)
+    want = pt.Renderer(sc)
+    gui.firstBounceCache = False
+    want.set_options(gui)
+    want.render(1, 3)
+    assert np.allclose(r.read_sum(), want.read_sum(), rtol=2e-6, atol=1e-6)
+    want.close()
     r.close()
 
 
