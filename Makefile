@@ -10,8 +10,8 @@ CSRC  := $(PKG)/csrc
 SC_SRCS := $(CSRC)/sc_kernels.cu $(CSRC)/sc_api.cu
 SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/sc_tmpl.cuh $(CSRC)/lookback.cuh include/b200_sc.h
 
-.PHONY: all lib oracle clean
-all: lib oracle
+.PHONY: all lib host oracle clean
+all: lib host oracle
 
 PT_SRCS := $(CSRC)/pt_kernels.cu $(CSRC)/pt_api.cu
 PT_HDRS := $(CSRC)/pt_kernels.cuh $(CSRC)/pt_math.cuh $(CSRC)/pt_shade.cuh $(CSRC)/lookback.cuh include/b200_pt.h
@@ -27,9 +27,25 @@ $(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS) $(PKG)/libb200sc.so include/b200_sc.h
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(PT_SRCS) -L$(PKG) -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 
+# ---- host side above the C ABI (C++): scene loader, image writer, headless CLI, scan harness ----
+HOST     := $(PKG)/host
+BIN      := $(PKG)/bin
+CXXFLAGS := -std=c++17 -O2 -ffp-contract=off -Wall -Iinclude -I/usr/local/cuda/include
+HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/image_io.hpp include/b200_pt.h
+
+host: $(BIN)/cuda_path_tracer
+
+$(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
+	@mkdir -p $(BIN)
+	g++ $(CXXFLAGS) -c -o $@ $<
+
+$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/image_io.o $(PKG)/libb200pt.so
+	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200pt -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN/..'
+
 oracle:
 	$(MAKE) -C oracle all
 
 clean:
 	rm -f $(PKG)/*.so
+	rm -rf $(BIN)
 	$(MAKE) -C oracle clean

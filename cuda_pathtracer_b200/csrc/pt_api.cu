@@ -462,6 +462,14 @@ int b200pt_read_sum(b200pt* h, float* host_rgb)
     return 0;
 }
 
+int b200pt_write_sum(b200pt* h, const float* host_rgb)
+{
+    if (!h || !host_rgb) return B200_E_BADARG;
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(h->d_image, host_rgb, sizeof(float) * 3 * (size_t)h->P, cudaMemcpyHostToDevice));
+    return 0;
+}
+
 int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats)
 {
     if (!h || !dev_ptr) return B200_E_BADARG;
@@ -548,7 +556,7 @@ const char* b200pt_error_string(int code)
     case B200_E_BADARG: return "b200pt: bad argument";
     case B200_E_NODEVICE: return "b200pt: no CUDA device (this library has no CPU fallback)";
     case B200_E_NOMEM: return "b200pt: out of device memory";
-    case B200_E_UNSUPPORTED: return "b200pt: scene feature not supported (meshes, textures, material sort or first-bounce cache)";
+    case B200_E_UNSUPPORTED: return "b200pt: scene feature not supported (triangle meshes, textures)";
     default: return cudaGetErrorString((cudaError_t)code);
     }
 }

@@ -130,6 +130,7 @@ def _lib():
         lib.b200pt_render.argtypes = [vp, ci, ci, ci, vp, ci]
         lib.b200pt_tonemap_u8.argtypes = [vp, ci, vp, vp]
         lib.b200pt_read_sum.argtypes = [vp, vp]
+        lib.b200pt_write_sum.argtypes = [vp, vp]
         lib.b200pt_sum_device_ptr.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         lib.b200pt_get_stats.argtypes = [vp, ctypes.POINTER(_StatsC)]
         lib.b200pt_debug_raygen.argtypes = [vp, ci, vp, vp]
@@ -198,6 +199,12 @@ class Renderer:
         assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.size == 3 * self.scene.width * self.scene.height
         check(_lib().b200pt_read_sum(self._h, out.ctypes.data))
         return out
+
+    def write_sum(self, img):
+        """replace the accumulation image (restartable rendering)"""
+        img = np.ascontiguousarray(img, dtype=np.float32)
+        assert img.size == 3 * self.scene.width * self.scene.height
+        check(_lib().b200pt_write_sum(self._h, img.ctypes.data))
 
     def sum_device_ptr(self):
         p, n = ctypes.c_void_p(), ctypes.c_size_t()

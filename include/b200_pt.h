@@ -95,7 +95,8 @@ typedef struct b200pt_options {
     int32_t dof;                /* default 1 */
     float aperture;             /* default 0.1 */
     float focal_len;            /* default 10.0 */
-    int32_t first_bounce_cache; /* NEW, default 0; only honoured when ssaa == 0 && dof == 0 */
+    int32_t first_bounce_cache; /* NEW, default 0; only honoured when ssaa == 0 && dof == 0 (the camera
+                                   rays must not change between iterations); silently off otherwise */
     int32_t batch;              /* NEW: iterations traced concurrently in one wavefront
                                    (0 = library default).  1 keeps the reference's accumulation
                                    order so the float sum image is bit-identical to it.       */
@@ -139,6 +140,9 @@ int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream
 
 /* Copy the float SUM image (3*W*H floats) to host memory; synchronises. */
 int b200pt_read_sum(b200pt* h, float* host_rgb);
+/* Replace the float SUM image by 3*W*H floats from host memory (restartable rendering: resume from a
+ * stored accumulation; the caller continues with the next iteration number).  Synchronises. */
+int b200pt_write_sum(b200pt* h, const float* host_rgb);
 /* Device pointer of the float SUM image (for NCCL all-reduce across GPUs). */
 int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats);
 

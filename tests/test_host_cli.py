@@ -1,0 +1,155 @@
+"""Host side above the C ABI: the C++ scene loader, the image writer and the headless CLI
+(cuda_pathtracer_b200/host/ -> cuda_pathtracer_b200/bin/cuda_path_tracer), the drop-in for the
+reference executable (`cuda_path_tracer SCENE.json`, path_tracer/src/main.cpp:34-112).
+
+CPU tests: the loader's PODs are BYTE-IDENTICAL to dumps written by the reference's own, unmodified
+scene.cpp (tests/golden/*.scene.bin, made by oracle/ref_scene_dump.cpp); the PNG writer decodes to
+the pixels saveImage()/Image::savePNG define (x mirrored, clamp, *255.f, truncation).
+GPU tests: the CLI's float SUM image equals the reference CUDA build's bit for bit, output naming,
+restartable rendering."""
+import glob
+import os
+import struct
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+from pt_cases import GOLD, bits_equal, ref_sum
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
+SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
+          "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096"]
+
+
+def scene_path(name):
+    return os.path.join(REPO, "scenes", name + ".json")
+
+
+def decode_png(path):
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    at, idat, w, h = 8, b"", None, None
+    while at < len(raw):
+        n, kind = struct.unpack(">I4s", raw[at:at + 8])
+        body = raw[at + 8:at + 8 + n]
+        crc, = struct.unpack(">I", raw[at + 8 + n:at + 12 + n])
+        assert crc == zlib.crc32(kind + body) & 0xFFFFFFFF
+        if kind == b"IHDR":
+            w, h, depth, ctype, comp, filt, inter = struct.unpack(">IIBBBBB", body)
+            assert (depth, ctype, comp, filt, inter) == (8, 2, 0, 0, 0)
+        elif kind == b"IDAT":
+            idat += body
+        at += 12 + n
+    rows = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, 1 + 3 * w)
+    assert not rows[:, 0].any()                              # filter type 0 on every row
+    return rows[:, 1:].reshape(h, w, 3)
+
+
+def expected_png_pixels(sum_img, samples):
+    """main.cpp:88-101 + image.cpp:22-36: mean, x mirror, clamp to [0,1], * 255.f, truncate"""
+    mean = sum_img.astype(np.float32) / np.float32(samples)
+    v = np.clip(mean, np.float32(0), np.float32(1)) * np.float32(255)
+    v = np.where(np.isnan(v), np.float32(0), v)
+    return v.astype(np.uint8)[:, ::-1, :]
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_loader_is_byte_identical_to_the_reference_loader(tmp_path, name):
+    out = str(tmp_path / "scene.bin")
+    subprocess.run([EXE, scene_path(name), "--dump-scene", out], check=True, stdout=subprocess.DEVNULL)
+    assert open(out, "rb").read() == open(os.path.join(GOLD, name + ".scene.bin"), "rb").read()
+
+
+def test_loader_against_the_reference_tree_when_present(tmp_path):
+    """the reference's own shipped cornell.json through both loaders (build container only)"""
+    ref_scene = "/root/reference/path_tracer/scenes/cornell.json"
+    dump = os.path.join(REPO, "oracle", "_ref", "ref_scene_dump")
+    if not (os.path.exists(ref_scene) and os.path.exists(dump)):
+        pytest.skip("needs /root/reference and oracle/_ref/ref_scene_dump")
+    a, b = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+    subprocess.run([dump, ref_scene, a], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run([EXE, ref_scene, "--dump-scene", b], check=True, stdout=subprocess.DEVNULL)
+    assert open(a, "rb").read() == open(b, "rb").read()
+
+
+def test_material_ids_follow_alphabetical_key_order(tmp_path):
+    """nlohmann's object is a std::map, so ids are NOT in file order"""
+    out = str(tmp_path / "s.bin")
+    subprocess.run([EXE, scene_path("cornell_tiny"), "--dump-scene", out], check=True, stdout=subprocess.DEVNULL)
+    from cuda_pathtracer_b200 import pathtracer as pt
+    sc = pt.Scene.from_pod_file(out)
+    # cornell: diffuse_green 0, diffuse_red 1, diffuse_white 2, light 3, specular_white 4
+    assert [round(m.emittance) for m in sc.materials] == [0, 0, 0, 5, 0]
+    assert tuple(round(c, 2) for c in sc.materials[0].color) == (0.35, 0.85, 0.35)
+
+
+def test_cli_exit_codes(tmp_path):
+    assert subprocess.run([EXE], capture_output=True).returncode == 1                 # usage (main.cpp:38-42)
+    assert subprocess.run([EXE, str(tmp_path / "missing.json")], capture_output=True).returncode == 255
+    assert subprocess.run([EXE, str(tmp_path / "scene.txt")], capture_output=True).returncode == 255
+    bad = tmp_path / "bad.json"
+    bad.write_text('{"Materials": {}, "Objects": [{"TYPE": "cube"}]}')
+    assert subprocess.run([EXE, str(bad)], capture_output=True).returncode == 255
+    assert subprocess.run([EXE, scene_path("cornell_tiny"), "--bogus"], capture_output=True).returncode == 1
+
+
+def test_png_writer_pixels(tmp_path):
+    rng = np.random.default_rng(565)
+    h, w, samples = 37, 53, 7
+    s = (rng.random((h, w, 3), dtype=np.float32) * np.float32(10) - np.float32(1.5)).astype(np.float32)
+    s[0, 0] = [np.nan, 7.0, 0.0]
+    s[1, 2] = [samples * 1.0, samples * 0.999999, -0.0]
+    src = str(tmp_path / "sum.bin")
+    s.tofile(src)
+    base = str(tmp_path / "img")
+    subprocess.run([EXE, "--convert", src, str(w), str(h), str(samples), base, "--hdr"], check=True,
+                   stdout=subprocess.DEVNULL)
+    assert np.array_equal(decode_png(base + ".png"), expected_png_pixels(s, samples))
+    hdr = open(base + ".hdr", "rb").read()
+    assert hdr.startswith(b"#?RADIANCE\n") and hdr.endswith(hdr[-4 * w * h:]) and len(hdr) > 4 * w * h
+
+
+# ---- on a B200 ---------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene,iters,flags,tag", [("cornell_small", 16, [], "default"),
+                                                    ("cornell_glass_small", 16, ["--sort"], "sort")])
+def test_cli_render_matches_reference_cuda_build(tmp_path, scene, iters, flags, tag):
+    sum_out, base = str(tmp_path / "sum.bin"), str(tmp_path / "out")
+    subprocess.run([EXE, scene_path(scene), "--iters", str(iters), "--batch", "1", "--sum-out", sum_out,
+                    "--out", base] + flags, check=True, stdout=subprocess.DEVNULL)
+    got = np.fromfile(sum_out, dtype=np.float32)
+    png = decode_png(base + ".png")
+    h, w = png.shape[:2]
+    got = got.reshape(h, w, 3)
+    assert bits_equal(got, ref_sum(scene, iters, tag, got.shape))
+    assert np.array_equal(png, expected_png_pixels(got, iters))
+
+
+@pytest.mark.gpu
+def test_cli_default_output_name_and_iterations(tmp_path):
+    """no flags: renders Camera.ITERATIONS samples and writes <FILE>.<time>.<N>samp.png into cwd"""
+    r = subprocess.run([EXE, scene_path("cornell_tiny")], cwd=str(tmp_path), capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    files = glob.glob(str(tmp_path / "*.png"))
+    assert len(files) == 1
+    name = os.path.basename(files[0])
+    import json
+    cam = json.load(open(scene_path("cornell_tiny")))["Camera"]
+    parts = name.split(".")
+    assert parts[0] == cam["FILE"] and parts[-2] == f"{cam['ITERATIONS']}samp" and parts[1].endswith("z")
+    assert "Reading scene from" in r.stdout and "Saved" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_restartable_rendering(tmp_path):
+    """N4: 6 iterations == 4 iterations, stop, resume with 2 more (batch 1: bit-identical)"""
+    a, b, c = (str(tmp_path / n) for n in ("a.bin", "b.bin", "c.bin"))
+    common = [EXE, scene_path("cornell_tiny"), "--batch", "1", "--no-png"]
+    subprocess.run(common + ["--iters", "6", "--sum-out", a], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run(common + ["--iters", "4", "--sum-out", b], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run(common + ["--iters", "2", "--resume-sum", b, "--samples-done", "4", "--sum-out", c], check=True,
+                   stdout=subprocess.DEVNULL)
+    assert bits_equal(np.fromfile(a, dtype=np.float32), np.fromfile(c, dtype=np.float32))
