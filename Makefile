@@ -33,7 +33,7 @@ BIN      := $(PKG)/bin
 CXXFLAGS := -std=c++17 -O2 -ffp-contract=off -Wall -Iinclude -I/usr/local/cuda/include
 HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/image_io.hpp include/b200_pt.h
 
-host: $(BIN)/cuda_path_tracer
+host: $(BIN)/cuda_path_tracer $(BIN)/stream_compaction_test
 
 $(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
 	@mkdir -p $(BIN)
@@ -41,6 +41,10 @@ $(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
 
 $(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/image_io.o $(PKG)/libb200pt.so
 	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200pt -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN/..'
+
+$(BIN)/stream_compaction_test: $(HOST)/sc_harness.cpp include/b200_stream_compaction.hpp include/b200_sc.h $(PKG)/libb200sc.so
+	@mkdir -p $(BIN)
+	g++ $(CXXFLAGS) -o $@ $< -L$(PKG) -lb200sc -Wl,-rpath,'$$ORIGIN/..'
 
 oracle:
 	$(MAKE) -C oracle all

@@ -153,3 +153,66 @@ def test_cli_restartable_rendering(tmp_path):
     subprocess.run(common + ["--iters", "2", "--resume-sum", b, "--samples-done", "4", "--sum-out", c], check=True,
                    stdout=subprocess.DEVNULL)
     assert bits_equal(np.fromfile(a, dtype=np.float32), np.fromfile(c, dtype=np.float32))
+
+
+# ---- scan / compact harness (include/b200_stream_compaction.hpp + host/sc_harness.cpp) ------------------
+SC_EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "stream_compaction_test")
+
+
+def test_sc_harness_cpu_namespace_config0():
+    """BASELINE configs[0]: StreamCompaction::CPU scan + compact on n = 2^20 (POT and NPOT) on the host"""
+    import json
+    r = subprocess.run([SC_EXE, "20", "--cpu-only", "--json"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert "FAIL" not in r.stdout and r.stdout.count("passed") == 4
+    row = json.loads(r.stdout.strip().splitlines()[-1])
+    assert row["n"] == 1 << 20 and row["failures"] == 0 and row["ms"]["cpu_scan_pot"] > 0
+
+
+def test_sc_header_cpu_namespace_matches_golden_vectors(tmp_path):
+    """the header's CPU::scan / compact* against the reference's own cpu.cu outputs (sc_golden.npz)"""
+    gold = np.load(os.path.join(GOLD, "sc_golden.npz"))
+    src = tmp_path / "t.cpp"
+    src.write_text(r'''
+#include <cstdio>
+#include <vector>
+#include "b200_stream_compaction.hpp"
+int main(int argc, char** argv) {
+    FILE* f = fopen(argv[1], "rb"); int n; if (fread(&n, 4, 1, f) != 1) return 1;
+    std::vector<int> in(n), out(n), out2(n);
+    if (fread(in.data(), 4, n, f) != (size_t)n) return 1; fclose(f);
+    int mode = argv[3][0] - '0', count = n;
+    if (mode == 0) StreamCompaction::CPU::scan(n, out.data(), in.data());
+    else if (mode == 1) count = StreamCompaction::CPU::compactWithoutScan(n, out.data(), in.data());
+    else count = StreamCompaction::CPU::compactWithScan(n, out.data(), in.data());
+    f = fopen(argv[2], "wb"); fwrite(out.data(), 4, count, f); fclose(f);
+    if (ilog2ceil(1) != 0 || ilog2ceil(5) != 3 || ilog2(8) != 3 || ilog2ceil(8) != 3) return 3;
+    return 0;
+}''')
+    exe = str(tmp_path / "t")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", os.path.join(REPO, "include"), str(src), "-o", exe,
+                    "-L", os.path.join(REPO, "cuda_pathtracer_b200"), "-lb200sc",
+                    "-Wl,-rpath," + os.path.join(REPO, "cuda_pathtracer_b200")], check=True)
+
+    def run(a, mode):
+        fin, fout = str(tmp_path / "in.bin"), str(tmp_path / "out.bin")
+        with open(fin, "wb") as f:
+            f.write(struct.pack("<i", a.size))
+            f.write(np.ascontiguousarray(a, dtype=np.int32).tobytes())
+        subprocess.run([exe, fin, fout, str(mode)], check=True)
+        return np.fromfile(fout, dtype=np.int32)
+
+    assert np.array_equal(run(gold["scan_in"], 0), gold["scan_pot"])
+    assert np.array_equal(run(gold["scan_in"][:-3], 0), gold["scan_npot"])
+    assert np.array_equal(run(gold["wrap_in"], 0), gold["wrap_scan"])
+    for mode in (1, 2):
+        assert np.array_equal(run(gold["compact_in"], mode), gold["compact_pot"])
+        assert np.array_equal(run(gold["compact_in"][:-3], mode), gold["compact_npot"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("lg", [8, 20, 26])
+def test_sc_harness_all_variants_pass(lg):
+    r = subprocess.run([SC_EXE, str(lg), "--json"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert "FAIL" not in r.stdout and r.stdout.count("passed") == 12
