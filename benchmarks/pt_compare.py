@@ -20,6 +20,7 @@ def gui_from_flags(flags, batch):
     g.SSAA = "--no-ssaa" not in flags
     g.DoF = "--no-dof" not in flags
     g.russianRoulette = "--no-rr" not in flags
+    g.sortbyMaterial = "--sort" in flags
     g.batch = batch
     return g
 

@@ -45,7 +45,16 @@ struct b200pt {
     // first-bounce cache (valid while camera, geometry and the SSAA / DoF toggles stay put)
     float4* d_cache_n = nullptr;
     int* d_cache_k = nullptr;
+    float2* d_hit_uv = nullptr;
+    float2* d_cache_uv = nullptr;
     bool cache_valid = false;
+    // triangle meshes / BVH / textures (b200pt_create_ext)
+    BvhRec* d_nodes = nullptr;
+    TriVert* d_tv = nullptr;
+    TriAttr* d_ta = nullptr;
+    TexRec* d_tex = nullptr;
+    unsigned char* d_texels = nullptr;
+    MeshScene mesh{};
     unsigned epoch = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     uint64_t iterations = 0, launches = 0;
@@ -87,7 +96,8 @@ void pack_prim(const b200pt_geom& g, PrimRec& r)
         }
     r.type = g.type;
     r.material = g.materialid;
-    r.pad0 = r.pad1 = 0;
+    r.pad0 = g.type == B200PT_MESH ? g.tri_start_idx : 0;     // a MESH owns the triangle ids [pad0, pad1)
+    r.pad1 = g.type == B200PT_MESH ? g.tri_end_idx : 0;
 }
 
 int default_batch(int P)
@@ -116,6 +126,8 @@ int ensure_batch(b200pt* h, int batch)
     return 0;
 }
 
+int upload_meshes(b200pt* h, const b200pt_scene_ext* ext);
+
 int sort_bins(const b200pt* h) { return h->n_mats < 256 ? h->n_mats : 256; }
 int sort_passes(const b200pt* h)
 {
@@ -134,8 +146,11 @@ int ensure_sort(b200pt* h, int batch)
     h->d_hist = h->d_hist_scanned = nullptr; h->sort_batch_cap = 0;
     const size_t paths = (size_t)batch * h->P;
     const size_t hist = (size_t)batch * sort_bins(h) * h->tiles + 4;
+    cudaFree(h->d_hit_uv);
+    h->d_hit_uv = nullptr;
     int r = dev_alloc((void**)&h->d_hit_n, sizeof(float4) * paths);
     if (!r) r = dev_alloc((void**)&h->d_hit_k, sizeof(int) * paths);
+    if (!r) r = dev_alloc((void**)&h->d_hit_uv, sizeof(float2) * paths);
     if (!r) r = dev_alloc((void**)&h->d_perm[0], sizeof(int) * paths);
     if (!r && sort_passes(h) > 1) r = dev_alloc((void**)&h->d_perm[1], sizeof(int) * paths);
     if (!r) r = dev_alloc((void**)&h->d_hist, sizeof(int) * hist);
@@ -151,6 +166,7 @@ int ensure_cache(b200pt* h)
     if (h->d_cache_n) return 0;
     int r = dev_alloc((void**)&h->d_cache_n, sizeof(float4) * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_cache_k, sizeof(int) * (size_t)h->P);
+    if (!r) r = dev_alloc((void**)&h->d_cache_uv, sizeof(float2) * (size_t)h->P);
     h->cache_valid = false;
     return r;
 }
@@ -195,17 +211,107 @@ void pack_camera(const b200pt_camera& c, CamRec& cam)
     cam.ply = c.pixelLength[1];
 }
 
-int validate_scene(const b200pt_scene* sc)
+// geoms / materials / camera against the triangle, BVH-node and texture counts of the scene
+int validate_scene_counts(const b200pt_scene* sc, int n_tris, int n_nodes, int n_tex)
 {
     if (!sc || !sc->geoms || !sc->materials || sc->n_geoms <= 0 || sc->n_materials <= 0) return B200_E_BADARG;
     if (sc->camera.resolution[0] <= 0 || sc->camera.resolution[1] <= 0 || sc->trace_depth <= 0 || sc->trace_depth > 511)
         return B200_E_BADARG;
     for (int i = 0; i < sc->n_geoms; ++i) {
-        if (sc->geoms[i].type != B200PT_SPHERE && sc->geoms[i].type != B200PT_CUBE) return B200_E_UNSUPPORTED;
+        const int type = sc->geoms[i].type;
+        if (type != B200PT_SPHERE && type != B200PT_CUBE && type != B200PT_MESH) return B200_E_UNSUPPORTED;
+        if (type == B200PT_MESH && n_tris && n_nodes == 0) return B200_E_UNSUPPORTED;   // meshes need the BVH
         if (sc->geoms[i].materialid < 0 || sc->geoms[i].materialid >= sc->n_materials) return B200_E_BADARG;
     }
     for (int i = 0; i < sc->n_materials; ++i)
-        if (sc->materials[i].texture_id != -1) return B200_E_UNSUPPORTED;
+        if (sc->materials[i].texture_id < -1 || sc->materials[i].texture_id >= n_tex) return B200_E_BADARG;
+    return 0;
+}
+
+int validate_scene(const b200pt_scene* sc, const b200pt_scene_ext* ext)
+{
+    const int n_tris = ext ? ext->n_triangles : 0, n_nodes = ext ? ext->n_bvh_nodes : 0, n_tex = ext ? ext->n_textures : 0;
+    if (n_tris < 0 || n_nodes < 0 || n_tex < 0) return B200_E_BADARG;
+    if ((n_tris && !ext->triangles) || (n_nodes && !ext->bvh) || (n_tex && !ext->textures)) return B200_E_BADARG;
+    for (int i = 0; i < n_nodes; ++i) {
+        const b200pt_bvh_node& nd = ext->bvh[i];
+        if (nd.sub_areas > 0) {
+            if (nd.first_area_idx < 0 || nd.first_area_idx + nd.sub_areas > n_tris) return B200_E_BADARG;
+        } else if (nd.axis < 0 || nd.axis > 2 || nd.rchild_idx <= i || nd.rchild_idx >= n_nodes || i + 1 >= n_nodes) {
+            return B200_E_BADARG;
+        }
+    }
+    for (int i = 0; i < n_tex; ++i)
+        if (ext->textures[i].width <= 0 || ext->textures[i].height <= 0 || ext->textures[i].components <= 0 ||
+            !ext->textures[i].pixels)
+            return B200_E_BADARG;
+    return validate_scene_counts(sc, n_tris, n_nodes, n_tex);
+}
+
+// class Triangle / BVHTree / Texture -> the device records (pt_math.cuh)
+int upload_meshes(b200pt* h, const b200pt_scene_ext* ext)
+{
+    const int n_tris = ext->n_triangles, n_nodes = ext->n_bvh_nodes, n_tex = ext->n_textures;
+    if (n_nodes) {
+        std::vector<BvhRec> nodes((size_t)n_nodes);
+        for (int i = 0; i < n_nodes; ++i) {
+            const b200pt_bvh_node& s = ext->bvh[i];
+            BvhRec& d = nodes[i];
+            for (int k = 0; k < 3; ++k) { d.lo[k] = s.min_corner[k]; d.hi[k] = s.max_corner[k]; }
+            d.sub_areas = s.sub_areas;
+            d.axis = s.sub_areas > 0 ? 0 : s.axis;
+            d.first = s.sub_areas > 0 ? s.first_area_idx : 0;
+            d.rchild = s.sub_areas > 0 ? 0 : s.rchild_idx;
+            d.pad0 = d.pad1 = 0;
+        }
+        int r = dev_alloc((void**)&h->d_nodes, sizeof(BvhRec) * nodes.size());
+        if (r) return r;
+        CK(cudaMemcpy(h->d_nodes, nodes.data(), sizeof(BvhRec) * nodes.size(), cudaMemcpyHostToDevice));
+    }
+    if (n_tris) {
+        std::vector<TriVert> tv((size_t)n_tris);
+        std::vector<TriAttr> ta((size_t)n_tris);
+        for (int i = 0; i < n_tris; ++i) {
+            const b200pt_triangle& s = ext->triangles[i];
+            for (int k = 0; k < 3; ++k) { tv[i].v0[k] = s.vertices[0][k]; tv[i].v1[k] = s.vertices[1][k]; tv[i].v2[k] = s.vertices[2][k]; }
+            tv[i].id = s.id;
+            tv[i].pad0 = tv[i].pad1 = 0;
+            std::memcpy(ta[i].uv, s.uv, sizeof(s.uv));
+            std::memcpy(ta[i].n, s.normals, sizeof(s.normals));
+            ta[i].pad = 0.f;
+        }
+        int r = dev_alloc((void**)&h->d_tv, sizeof(TriVert) * tv.size());
+        if (!r) r = dev_alloc((void**)&h->d_ta, sizeof(TriAttr) * ta.size());
+        if (r) return r;
+        CK(cudaMemcpy(h->d_tv, tv.data(), sizeof(TriVert) * tv.size(), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(h->d_ta, ta.data(), sizeof(TriAttr) * ta.size(), cudaMemcpyHostToDevice));
+    }
+    if (n_tex) {
+        std::vector<TexRec> recs((size_t)n_tex);
+        std::vector<unsigned char> pool;
+        for (int i = 0; i < n_tex; ++i) {
+            const b200pt_texture& t = ext->textures[i];
+            const size_t bytes = (size_t)t.width * t.height * t.components;
+            recs[i].w = t.width; recs[i].h = t.height; recs[i].comp = t.components;
+            recs[i].offset = (unsigned)pool.size();
+            pool.insert(pool.end(), t.pixels, t.pixels + bytes);
+            while (pool.size() % 16) pool.push_back(0);
+        }
+        int r = dev_alloc((void**)&h->d_tex, sizeof(TexRec) * recs.size());
+        if (!r) r = dev_alloc((void**)&h->d_texels, pool.size());
+        if (r) return r;
+        CK(cudaMemcpy(h->d_tex, recs.data(), sizeof(TexRec) * recs.size(), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(h->d_texels, pool.data(), pool.size(), cudaMemcpyHostToDevice));
+    }
+    h->mesh.nodes = h->d_nodes;
+    h->mesh.tv = h->d_tv;
+    h->mesh.ta = h->d_ta;
+    h->mesh.tex = h->d_tex;
+    h->mesh.texels = h->d_texels;
+    h->mesh.n_nodes = n_tris ? n_nodes : 0;
+    h->mesh.n_tris = n_tris;
+    h->mesh.n_tex = n_tex;
+    h->mesh.n_smem_nodes = h->mesh.n_nodes < PT_SMEM_NODES ? h->mesh.n_nodes : PT_SMEM_NODES;
     return 0;
 }
 
@@ -226,10 +332,12 @@ void b200pt_default_options(b200pt_options* o)
     o->batch = 0;
 }
 
-int b200pt_create(const b200pt_scene* sc, b200pt** out)
+int b200pt_create(const b200pt_scene* sc, b200pt** out) { return b200pt_create_ext(sc, nullptr, out); }
+
+int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200pt** out)
 {
     if (!out) return B200_E_BADARG;
-    const int bad = validate_scene(sc);
+    const int bad = validate_scene(sc, ext);
     if (bad) return bad;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { cudaGetLastError(); return B200_E_NODEVICE; }
@@ -261,6 +369,7 @@ int b200pt_create(const b200pt_scene* sc, b200pt** out)
     CK(cudaEventCreate(&h->ev0));
     CK(cudaEventCreate(&h->ev1));
     r = b200pt_reset(h);
+    if (!r && ext) r = upload_meshes(h, ext);
     if (r) { b200pt_destroy(h); return r; }
     *out = h;
     return 0;
@@ -273,6 +382,8 @@ int b200pt_destroy(b200pt* h)
     cudaFree(h->d_desc); cudaFree(h->d_segments); cudaFree(h->d_image);
     cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
     cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
+    cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv);
+    cudaFree(h->d_nodes); cudaFree(h->d_tv); cudaFree(h->d_ta); cudaFree(h->d_tex); cudaFree(h->d_texels);
     b200_sc_ctx_destroy(h->sc);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -310,8 +421,10 @@ int b200pt_reset(b200pt* h)
 int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
 {
     if (!h) return B200_E_BADARG;
-    const int bad = validate_scene(sc);
-    if (bad) return bad;
+    {   // triangles, BVH and textures stay as uploaded: validate against their counts
+        const int bad = validate_scene_counts(sc, h->mesh.n_tris, h->mesh.n_nodes, h->mesh.n_tex);
+        if (bad) return bad;
+    }
     if (sc->n_geoms != h->n_prims || sc->n_materials != h->n_mats || sc->camera.resolution[0] != h->W ||
         sc->camera.resolution[1] != h->H || sc->trace_depth != h->depth)
         return B200_E_BADARG;
@@ -380,6 +493,9 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.hist_scanned = h->d_hist_scanned;
     p.cache_n = h->d_cache_n;
     p.cache_k = h->d_cache_k;
+    p.hit_uv = h->d_hit_uv;
+    p.cache_uv = h->d_cache_uv;
+    p.mesh = h->mesh;
 
     CK(cudaEventRecord(h->ev0, s));
     for (int done = 0; done < n_iters; done += batch) {
@@ -533,7 +649,7 @@ int b200pt_debug_intersect(b200pt* h, int n, const void* d_segments, void* d_ise
 {
     if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
     if (n == 0) return 0;
-    CK(launch_debug_intersect(h->d_prims, h->n_prims, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
+    CK(launch_debug_intersect(h->d_prims, h->n_prims, h->mesh, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
     h->launches += 1;
     return 0;
 }
@@ -544,7 +660,7 @@ int b200pt_debug_shade(b200pt* h, int iter, int n, const void* d_isects, void* d
     if (n == 0) return 0;
     RenderParams p{};
     fill_params(h, p);
-    CK(launch_debug_shade(h->d_prims, h->d_mats, p.opt, iter, n, (const float*)d_isects, (float*)d_segments, (cudaStream_t)stream));
+    CK(launch_debug_shade(h->d_mats, h->mesh, p.opt, iter, n, (const float*)d_isects, (float*)d_segments, (cudaStream_t)stream));
     h->launches += 1;
     return 0;
 }

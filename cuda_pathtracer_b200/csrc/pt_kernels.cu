@@ -71,11 +71,18 @@ struct BounceShared {
 };
 
 // closest hit over the primitives [0, n) of `sp`, global indices base..base+n-1
+// A MESH primitive's candidate is the BVH hit if the hit triangle belongs to it (pathtrace.cu:262-272).
+// `owner` records the first MESH primitive that accepted the hit.
 __device__ __forceinline__ void closest_in_chunk(const PrimRec* __restrict__ sp, int n, int base, const V3& o,
-                                                 const V3& d, float& t_min, int& hit, Cand& best)
+                                                 const V3& d, const MeshHit& mh, float& t_min, int& hit, Cand& best,
+                                                 int& owner)
 {
     for (int i = 0; i < n; ++i) {
-        const Cand c = prim_test(sp[i], o, d);
+        Cand c = prim_test(sp[i], o, d);
+        if (sp[i].type == 2 && mh.any && mh.id >= sp[i].pad0 && mh.id < sp[i].pad1) {
+            c.t = mh.t;
+            if (owner < 0) owner = base + i;
+        }
         if (c.t > 0.0f && t_min > c.t) {    // strict: the lowest index wins ties (pathtrace.cu:280)
             t_min = c.t;
             hit = base + i;
@@ -105,11 +112,19 @@ __global__ void __launch_bounds__(PT_THREADS) k_raygen(const __grid_constant__ R
 // ------------------------------------------------------------------------------------------------
 // Pieces shared by the fused bounce kernel and the split (material-sorted) pipeline.
 
-struct HitRec {       // ShadeableIntersection without the texture coordinate (sceneStructs.h:92-97)
+struct HitRec {       // ShadeableIntersection (sceneStructs.h:92-97)
     float t;          // -1 = miss
     V3 n;
     int mat;          // 0 on a miss: the reference memsets the record (pathtrace.cu:466)
+    float u, v;       // texture coordinate (mesh hits; 0 otherwise)
 };
+
+__device__ __forceinline__ MeshHit no_mesh_hit()
+{
+    MeshHit h;
+    h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
+    return h;
+}
 
 __device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
 {
@@ -124,15 +139,17 @@ __device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
 
 // producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
 __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared& sh, MatRec* smats, int n_smem_mats,
-                                            PrimRec* sprims, bool want_prims)
+                                            BvhRec* snodes, PrimRec* sprims, bool want_prims)
 {
     if (threadIdx.x != 0) return;
     const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
     const int chunk_cap = n_chunks > 1 ? PT_CHUNK : p.n_prims;
     const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
+    const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
     const int n0 = want_prims ? min(chunk_cap, p.n_prims) : 0;
-    mbar_expect_tx(&sh.bar[0], mat_bytes + (unsigned)(n0 * sizeof(PrimRec)));
+    mbar_expect_tx(&sh.bar[0], mat_bytes + node_bytes + (unsigned)(n0 * sizeof(PrimRec)));
     if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
+    if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &sh.bar[0]);
     if (n0) bulk_g2s(sprims, p.prims, (unsigned)(n0 * sizeof(PrimRec)), &sh.bar[0]);
     if (want_prims && n_chunks > 1) {
         const int n1 = min(PT_CHUNK, p.n_prims - PT_CHUNK);
@@ -143,19 +160,25 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared&
 
 // computeIntersections (pathtrace.cu:230-298) over the TMA-staged primitive chunks.  Every thread of
 // the CTA must call it (it contains the chunk barriers); inactive threads only take part in those.
-__device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, BounceShared& sh, const PrimRec* sprims,
-                                                     bool active, const V3& o, const V3& d)
+__device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, BounceShared& sh, const BvhRec* snodes,
+                                                     const PrimRec* sprims, bool active, const V3& o, const V3& d)
 {
     const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
     float t_min = 3.402823466e+38f;
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+    MeshHit mh = no_mesh_hit();
+    int owner = -1;
+    if (p.mesh.n_nodes > 0) {                        // one BVH traversal serves every MESH primitive
+        mbar_wait(&sh.bar[0], 0u);                   // the staged top of the tree
+        if (active) mh = bvh_traverse(p.mesh, snodes, o, d);
+    }
     for (int ch = 0; ch < n_chunks; ++ch) {
         mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
         const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
         const PrimRec* sp = sprims + (n_chunks > 1 ? (ch & 1) * PT_CHUNK : 0);
-        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, t_min, hit, best);
+        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, mh, t_min, hit, best, owner);
         if (ch + 2 < n_chunks) {                     // refill this buffer with chunk ch + 2
             __syncthreads();
             if (threadIdx.x == 0) {
@@ -171,9 +194,17 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
     h.t = -1.0f;
     h.n = v3(0.f, 0.f, 0.f);
     h.mat = 0;
+    h.u = h.v = 0.0f;
     if (hit >= 0) {
         const PrimRec& g = n_chunks > 1 ? p.prims[hit] : sprims[hit];
-        h.n = prim_normal(g, best);
+        if (g.type == 2) {
+            tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, h.n, h.u, h.v);
+        } else {
+            h.n = prim_normal(g, best);
+            // (sic) a sphere / cube winning AFTER a mesh primitive accepted the BVH hit carries that
+            // hit's stale texture coordinate (pathtrace.cu:267,283)
+            if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, unused, h.u, h.v); }
+        }
         h.t = t_min;
         h.mat = g.material;
     }
@@ -202,7 +233,9 @@ __device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceS
     if (active) {
         const MatRec& m = n_smem_mats ? smats[h.mat] : p.mats[h.mat];
         const int iter = p.iter0 + slot * p.stride;
-        live = shade_exact(s, h.t, h.n, m, iter, idx, p.opt.rr);
+        const V3 base = (m.texture_id != -1 && h.t > 0.0f) ? tex_color(p.mesh, m.texture_id, h.u, h.v)
+                                                           : v3(m.color[0], m.color[1], m.color[2]);
+        live = shade_exact(s, h.t, h.n, m, base, iter, idx, p.opt.rr);
         if (!live && (s.c.x != 0.0f || s.c.y != 0.0f || s.c.z != 0.0f)) {
             // finalGather (pathtrace.cu:347-356) for this path, at termination: one add per pixel
             // per iteration, issued in iteration order when batch == 1
@@ -253,7 +286,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
     const int n_smem_mats = p.n_mats <= PT_SMEM_MATS ? p.n_mats : 0;
     MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(BounceShared));
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(smem_raw + sizeof(BounceShared) + (size_t)n_smem_mats * sizeof(MatRec));
+    BvhRec* snodes = reinterpret_cast<BvhRec*>(smats + n_smem_mats);
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE != 2 ? p.mesh.n_smem_nodes : 0));
 
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
@@ -265,7 +299,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     }
     if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
     bounce_barriers_init(sh);
-    stage_begin(p, sh, smats, n_smem_mats, sprims, CACHE != 2);
+    stage_begin(p, sh, smats, n_smem_mats, snodes, sprims, CACHE != 2);
 
     // this thread's path (overlaps the bulk copies)
     const int idx = tile * PT_THREADS + threadIdx.x;
@@ -275,14 +309,17 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     HitRec h;
     if (CACHE == 2) {
         const float4 cn = p.cache_n[active ? idx : 0];
+        const float2 cuv = p.cache_uv[active ? idx : 0];
         h.t = cn.x; h.n = v3(cn.y, cn.z, cn.w);
         h.mat = p.cache_k[active ? idx : 0];
+        h.u = cuv.x; h.v = cuv.y;
         mbar_wait(&sh.bar[0], 0u);                  // the materials
     } else {
-        h = closest_hit_staged(p, sh, sprims, active, s.o, s.d);
+        h = closest_hit_staged(p, sh, snodes, sprims, active, s.o, s.d);
         if (CACHE == 1 && slot == 0 && active) {
             p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             p.cache_k[idx] = h.mat;
+            p.cache_uv[idx] = make_float2(h.u, h.v);
         }
     }
     shade_and_compact(p, sh, smats, n_smem_mats, s, h, active, slot, tile, idx, n_live, count_out);
@@ -297,25 +334,28 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(smem_raw + sizeof(BounceShared));
+    BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(BounceShared));
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
     const int n_live = p.counts[p.bounce * p.batch + slot];
     if (tile * PT_THREADS >= n_live) return;
     if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
     bounce_barriers_init(sh);
-    stage_begin(p, sh, nullptr, 0, sprims, true);
+    stage_begin(p, sh, nullptr, 0, snodes, sprims, true);
     const int idx = tile * PT_THREADS + threadIdx.x;
     const bool active = idx < n_live;
     const size_t at = (size_t)slot * p.P + (active ? idx : 0);
     const float4 a = p.in.a[at], b = p.in.b[at];
-    const HitRec h = closest_hit_staged(p, sh, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
+    const HitRec h = closest_hit_staged(p, sh, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
     if (active) {
         p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
         p.hit_k[at] = h.mat;
+        p.hit_uv[at] = make_float2(h.u, h.v);
         if (p.cache_mode == 1 && slot == 0) {
             p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             p.cache_k[idx] = h.mat;
+            p.cache_uv[idx] = make_float2(h.u, h.v);
         }
     }
 }
@@ -415,7 +455,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_shade(const __grid_constant__ Re
     }
     if (p.cache_mode == 2 && tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
     bounce_barriers_init(sh);
-    stage_begin(p, sh, smats, n_smem_mats, nullptr, false);
+    stage_begin(p, sh, smats, n_smem_mats, nullptr, nullptr, false);
     const int j = tile * PT_THREADS + threadIdx.x;
     const bool active = j < n_live;
     const int src = active ? (p.perm_in ? p.perm_in[(size_t)slot * p.P + j] : j) : 0;
@@ -424,8 +464,10 @@ __global__ void __launch_bounds__(PT_THREADS) k_shade(const __grid_constant__ Re
     HitRec h;
     {
         const float4 hn = p.cache_mode == 2 ? p.cache_n[src] : p.hit_n[at];
+        const float2 huv = p.cache_mode == 2 ? p.cache_uv[src] : p.hit_uv[at];
         h.t = hn.x; h.n = v3(hn.y, hn.z, hn.w);
         h.mat = p.cache_mode == 2 ? p.cache_k[src] : p.hit_k[at];
+        h.u = huv.x; h.v = huv.y;
     }
     mbar_wait(&sh.bar[0], 0u);                       // the materials
     shade_and_compact(p, sh, smats, n_smem_mats, s, h, active, slot, tile, j, n_live, count_out);
@@ -479,8 +521,8 @@ __global__ void __launch_bounds__(256) k_debug_raygen(const __grid_constant__ Re
     store_segment(segments + 12 * (size_t)idx, make_camera_path(p.cam, p.opt, iter, p.depth, x, y));
 }
 
-__global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restrict__ prims, int n_prims, int n,
-                                                         const float* __restrict__ segments,
+__global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restrict__ prims, int n_prims, MeshScene mesh,
+                                                         int n, const float* __restrict__ segments,
                                                          float* __restrict__ isects)
 {
     const int i = blockIdx.x * 256 + threadIdx.x;
@@ -490,41 +532,56 @@ __global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restri
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-    closest_in_chunk(prims, n_prims, 0, s.o, s.d, t_min, hit, best);
+    mesh.n_smem_nodes = 0;
+    const MeshHit mh = mesh.n_nodes > 0 ? bvh_traverse(mesh, nullptr, s.o, s.d) : no_mesh_hit();
+    int owner = -1;
+    closest_in_chunk(prims, n_prims, 0, s.o, s.d, mh, t_min, hit, best, owner);
     float* o = isects + 7 * (size_t)i;           // the reference memsets the record to 0 first
     V3 nn = v3(0.f, 0.f, 0.f);
     int mat = 0;
-    if (hit >= 0) { nn = prim_normal(prims[hit], best); mat = prims[hit].material; }
+    float u = 0.f, v = 0.f;
+    if (hit >= 0) {
+        if (prims[hit].type == 2) {
+            tri_attributes(mesh.ta[mh.tri], mh.bx, mh.by, nn, u, v);
+        } else {
+            nn = prim_normal(prims[hit], best);
+            if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(mesh.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
+        }
+        mat = prims[hit].material;
+    }
     o[0] = hit >= 0 ? t_min : -1.0f;
     o[1] = nn.x; o[2] = nn.y; o[3] = nn.z;
     o[4] = __int_as_float(mat);
-    o[5] = 0.f; o[6] = 0.f;
+    o[5] = u; o[6] = v;
 }
 
-__global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ mats, OptRec opt, int iter, int n,
-                                                     const float* __restrict__ isects, float* __restrict__ segments)
+__global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ mats, MeshScene mesh, OptRec opt, int iter,
+                                                     int n, const float* __restrict__ isects, float* __restrict__ segments)
 {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
     PathState s = load_segment(segments + 12 * (size_t)i);
     const float* is = isects + 7 * (size_t)i;
     const MatRec m = mats[__float_as_int(is[4])];
-    shade_exact(s, is[0], v3(is[1], is[2], is[3]), m, iter, i, opt.rr);
+    const V3 base = (m.texture_id != -1 && is[0] > 0.0f) ? tex_color(mesh, m.texture_id, is[5], is[6])
+                                                         : v3(m.color[0], m.color[1], m.color[2]);
+    shade_exact(s, is[0], v3(is[1], is[2], is[3]), m, base, iter, i, opt.rr);
     store_segment(segments + 12 * (size_t)i, s);
 }
 
 // ------------------------------------------------------------------------------------------------
-size_t bounce_smem_bytes(int n_prims, int n_mats)
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes)
 {
     const int n_chunks = (n_prims + PT_CHUNK - 1) / PT_CHUNK;
     const size_t prim_bytes = (size_t)(n_chunks > 1 ? 2 * PT_CHUNK : n_prims) * sizeof(PrimRec);
     const size_t mat_bytes = (size_t)(n_mats <= PT_SMEM_MATS ? n_mats : 0) * sizeof(MatRec);
-    return sizeof(BounceShared) + mat_bytes + prim_bytes;
+    const size_t node_bytes = (size_t)(n_nodes < PT_SMEM_NODES ? n_nodes : PT_SMEM_NODES) * sizeof(BvhRec);
+    return sizeof(BounceShared) + mat_bytes + node_bytes + prim_bytes;
 }
 
 cudaError_t configure_kernels()
 {
-    const int cap = (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS);
+    const int cap = (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS, PT_SMEM_NODES);
     cudaError_t e = cudaFuncSetAttribute(k_bounce<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
@@ -542,16 +599,16 @@ cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
 {
     const dim3 grid(p.tiles, p.batch);
-    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats);
+    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes);
     if (p.cache_mode == 1) k_bounce<1><<<grid, PT_THREADS, smem, s>>>(p);
-    else if (p.cache_mode == 2) k_bounce<2><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats), s>>>(p);
+    else if (p.cache_mode == 2) k_bounce<2><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
     else k_bounce<0><<<grid, PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
 {
-    k_isect<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(p.n_prims, 0), s>>>(p);
+    k_isect<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes), s>>>(p);
     return cudaGetLastError();
 }
 
@@ -569,7 +626,7 @@ cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaS
 
 cudaError_t launch_shade(const RenderParams& p, cudaStream_t s)
 {
-    k_shade<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(0, p.n_mats), s>>>(p);
+    k_shade<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
     return cudaGetLastError();
 }
 
@@ -585,17 +642,17 @@ cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments
     return cudaGetLastError();
 }
 
-cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* segments, float* isects,
-                                   cudaStream_t s)
+cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, MeshScene mesh, int n, const float* segments,
+                                   float* isects, cudaStream_t s)
 {
-    k_debug_intersect<<<(n + 255) / 256, 256, 0, s>>>(prims, n_prims, n, segments, isects);
+    k_debug_intersect<<<(n + 255) / 256, 256, 0, s>>>(prims, n_prims, mesh, n, segments, isects);
     return cudaGetLastError();
 }
 
-cudaError_t launch_debug_shade(const PrimRec*, const MatRec* mats, OptRec opt, int iter, int n, const float* isects,
+cudaError_t launch_debug_shade(const MatRec* mats, MeshScene mesh, OptRec opt, int iter, int n, const float* isects,
                                float* segments, cudaStream_t s)
 {
-    k_debug_shade<<<(n + 255) / 256, 256, 0, s>>>(mats, opt, iter, n, isects, segments);
+    k_debug_shade<<<(n + 255) / 256, 256, 0, s>>>(mats, mesh, opt, iter, n, isects, segments);
     return cudaGetLastError();
 }
 

@@ -9,6 +9,7 @@ namespace ptk {
 constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
+constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
 constexpr int PT_DESC_STRIDE = 16;         // 64-bit words between look-back descriptors: one 128-B line each
                                            // (packed descriptors make the lines around the prefix frontier an
                                            // L2 hot spot, see lookback.cuh)
@@ -51,9 +52,12 @@ struct RenderParams {
     float4* cache_n;                   // [P] first-bounce cache
     int* cache_k;
     int cache_mode;                    // at bounce 0: 0 = off, 1 = fill, 2 = use
+    float2* hit_uv;                    // [batch][P] hit record texture coordinate (mesh hits)
+    float2* cache_uv;                  // [P]
+    MeshScene mesh;                    // triangle meshes / BVH / textures (n_nodes == 0: none)
 };
 
-size_t bounce_smem_bytes(int n_prims, int n_mats);
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);           // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
@@ -64,9 +68,9 @@ cudaError_t launch_shade(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s);
 // per-stage probes on the reference's AoS layouts (PathSegment 12 words, ShadeableIntersection 7 words)
 cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments, cudaStream_t s);
-cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, int n, const float* segments, float* isects,
-                                   cudaStream_t s);
-cudaError_t launch_debug_shade(const PrimRec* prims, const MatRec* mats, OptRec opt, int iter, int n, const float* isects,
+cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, MeshScene mesh, int n, const float* segments,
+                                   float* isects, cudaStream_t s);
+cudaError_t launch_debug_shade(const MatRec* mats, MeshScene mesh, OptRec opt, int iter, int n, const float* isects,
                                float* segments, cudaStream_t s);
 cudaError_t configure_kernels();
 

@@ -226,4 +226,172 @@ __device__ __forceinline__ V3 prim_normal(const PrimRec& g, const Cand& c)
     return n;
 }
 
+
+// ---- triangle meshes: BVH traversal and ray / triangle test ---------------------------------------
+// BVHIntersectionTest (intersections.cu:170-224), BoundingBox::intersect (boundingbox.h:74-92),
+// Triangle::intersect (sceneStructs.h:146-160) and glm::intersectRayTriangle (GLM 0.9.6
+// gtx/intersect.inl), in the operation order of the reference build's SASS
+// (_Z19BVHIntersectionTest...): cross products as FMUL + FFMA(a, b, -t), dot products as
+// fma(z, z', fma(x, x', y*y')), 1/x as rcp.rn, every bounding-box slab as FADD then FMUL.
+
+struct BvhRec {          // class BVHTree (40 B) padded to three 16-byte words
+    float lo[3]; int sub_areas;          // min corner | leaf triangle count (0 = inner node)
+    float hi[3]; int axis;               // max corner | split axis of an inner node
+    int first; int rchild; int pad0, pad1;
+};
+static_assert(sizeof(BvhRec) == 48, "BvhRec must stay 48 bytes");
+
+struct TriVert {         // what the intersection test reads: 48 B
+    float v0[3]; int id;                 // id = index before the BVH build reordered the triangles
+    float v1[3]; int pad0;
+    float v2[3]; int pad1;
+};
+static_assert(sizeof(TriVert) == 48, "TriVert must stay 48 bytes");
+
+struct TriAttr {         // what only the closest hit reads: 64 B
+    float uv[3][2];
+    float n[3][3];
+    float pad;
+};
+static_assert(sizeof(TriAttr) == 64, "TriAttr must stay 64 bytes");
+
+struct TexRec {          // class Texture: size, channel count, byte offset into the texel pool
+    int w, h, comp;
+    unsigned offset;
+};
+
+struct MeshScene {
+    const BvhRec* nodes;
+    const TriVert* tv;
+    const TriAttr* ta;
+    const TexRec* tex;
+    const unsigned char* texels;
+    int n_nodes, n_tris, n_tex, n_smem_nodes;
+};
+
+struct MeshHit {
+    bool any;            // some triangle was intersected (what BVHIntersectionTest returns)
+    float t;             // parametric distance of the closest one (ShadeableIntersection::t)
+    int tri;             // its position in the reordered triangle array (-1: none recorded)
+    int id;              // its Triangle::id
+    float bx, by;        // barycentric coordinates of the hit
+};
+
+// glm::min / glm::max: x < y ? x : y  /  x > y ? x : y (func_common.inl:413,434)
+__device__ __forceinline__ float gmin(float x, float y) { return x < y ? x : y; }
+__device__ __forceinline__ float gmax(float x, float y) { return x > y ? x : y; }
+
+__device__ __forceinline__ bool bbox_hit(const float* __restrict__ lo, const float* __restrict__ hi, const V3& o,
+                                         const V3& inv)
+{
+    const float mx = __fmul_rn(__fsub_rn(lo[0], o.x), inv.x), Mx = __fmul_rn(__fsub_rn(hi[0], o.x), inv.x);
+    const float my = __fmul_rn(__fsub_rn(lo[1], o.y), inv.y), My = __fmul_rn(__fsub_rn(hi[1], o.y), inv.y);
+    const float mz = __fmul_rn(__fsub_rn(lo[2], o.z), inv.z), Mz = __fmul_rn(__fsub_rn(hi[2], o.z), inv.z);
+    const float tmin = gmax(gmax(gmin(mx, Mx), gmin(my, My)), gmin(mz, Mz));
+    const float tmax = gmin(gmin(gmax(mx, Mx), gmax(my, My)), gmax(mz, Mz));
+    if (tmax < 0.0f) return false;
+    if (tmin > tmax) return false;
+    return true;
+}
+
+// glm::intersectRayTriangle: back-face culled (a < epsilon -> miss); bary = (x, y, t)
+__device__ __forceinline__ bool tri_test(const TriVert& T, const V3& o, const V3& d, float& bx, float& by, float& bt)
+{
+    const V3 v0 = v3(T.v0[0], T.v0[1], T.v0[2]);
+    const V3 e1 = v3(__fsub_rn(T.v1[0], v0.x), __fsub_rn(T.v1[1], v0.y), __fsub_rn(T.v1[2], v0.z));
+    const V3 e2 = v3(__fsub_rn(T.v2[0], v0.x), __fsub_rn(T.v2[1], v0.y), __fsub_rn(T.v2[2], v0.z));
+    const V3 p = cross_exact(d, e2);
+    const float a = dot_exact(e1, p);
+    if (a < 1.1920928955078125e-07f) return false;
+    const float f = __frcp_rn(a);
+    const V3 s = v3(__fsub_rn(o.x, v0.x), __fsub_rn(o.y, v0.y), __fsub_rn(o.z, v0.z));
+    bx = __fmul_rn(dot_exact(s, p), f);
+    if (bx < 0.0f) return false;
+    if (bx > 1.0f) return false;
+    const V3 q = cross_exact(s, e1);
+    by = __fmul_rn(dot_exact(d, q), f);
+    if (by < 0.0f) return false;
+    if (__fadd_rn(bx, by) > 1.0f) return false;
+    bt = __fmul_rn(dot_exact(e2, q), f);
+    return bt >= 0.0f;
+}
+
+constexpr int BVH_MAX_SEARCH_DEPTH = 64;     // intersections.cu:177
+
+// One traversal of the BVH over ALL meshes' triangles.  The reference runs this once per MESH geom
+// and accepts the result only for the geom whose id range holds the hit triangle
+// (pathtrace.cu:262-272); the traversal itself does not depend on the geom, so it is done once.
+// snodes: the first M.n_smem_nodes nodes staged in shared memory (DFS order keeps the top of the
+// tree there).
+__device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec* __restrict__ snodes, const V3& o,
+                                                const V3& d)
+{
+    MeshHit h;
+    h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
+    if (M.n_nodes == 0) return h;
+    int to_visit[BVH_MAX_SEARCH_DEPTH];
+    int sp = 0, cur = 0;
+    const bool neg[3] = {d.x < 0.0f, d.y < 0.0f, d.z < 0.0f};
+    const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    while (true) {
+        const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
+        if (bbox_hit(nd.lo, nd.hi, o, inv)) {
+            const int n_leaf = nd.sub_areas;
+            if (n_leaf > 0) {
+                const int first = nd.first;
+                for (int i = 0; i < n_leaf; ++i) {
+                    float bx, by, bt;
+                    if (tri_test(M.tv[first + i], o, d, bx, by, bt)) {
+                        h.any = true;
+                        if (h.t == -1.0f || bt < h.t) {
+                            h.t = bt; h.tri = first + i; h.bx = bx; h.by = by;
+                        }
+                    }
+                }
+                if (sp == 0) break;
+                cur = to_visit[--sp];
+            } else {
+                if (sp == BVH_MAX_SEARCH_DEPTH) { cur = to_visit[--sp]; continue; }
+                if (neg[nd.axis]) { to_visit[sp++] = cur + 1; cur = nd.rchild; }
+                else { to_visit[sp++] = nd.rchild; cur = cur + 1; }
+            }
+        } else {
+            if (sp == 0) break;
+            cur = to_visit[--sp];
+        }
+    }
+    if (h.tri >= 0) h.id = M.tv[h.tri].id;
+    return h;
+}
+
+// Triangle::intersect's attribute interpolation for the closest hit (sceneStructs.h:152-154):
+// uv = uv0*(1-x-y) + uv1*x + uv2*y; normal = normalize(n0*x + n1*y + n2*(1-x-y)) -- the weights of
+// the normal are permuted with respect to the uv's (sic).
+__device__ __forceinline__ void tri_attributes(const TriAttr& A, float bx, float by, V3& n, float& u, float& v)
+{
+    const float w = __fsub_rn(__fsub_rn(1.0f, bx), by);
+    u = __fmaf_rn(by, A.uv[2][0], __fmaf_rn(w, A.uv[0][0], __fmul_rn(bx, A.uv[1][0])));
+    v = __fmaf_rn(by, A.uv[2][1], __fmaf_rn(w, A.uv[0][1], __fmul_rn(bx, A.uv[1][1])));
+    const V3 m = v3(__fmaf_rn(w, A.n[2][0], __fmaf_rn(bx, A.n[0][0], __fmul_rn(by, A.n[1][0]))),
+                    __fmaf_rn(w, A.n[2][1], __fmaf_rn(bx, A.n[0][1], __fmul_rn(by, A.n[1][1]))),
+                    __fmaf_rn(w, A.n[2][2], __fmaf_rn(bx, A.n[0][2], __fmul_rn(by, A.n[1][2]))));
+    n = normalize_exact(m);
+}
+
+// Texture::get_color (sceneStructs.h:175-188): nearest texel, v flipped; only 3-channel textures
+// yield a colour.  (The reference reads out of bounds for uv outside [0, 1]; the index is clamped here.)
+__device__ __forceinline__ V3 tex_color(const MeshScene& M, int texture_id, float u, float v)
+{
+    const TexRec T = M.tex[texture_id];
+    const float fw = (float)T.w, fh = (float)T.h;
+    const int X = (int)gmin(__fmul_rn(fw, u), __fadd_rn(fw, -1.0f));
+    const int Y = (int)gmin(__fmul_rn(fh, __fsub_rn(1.0f, v)), __fadd_rn(fh, -1.0f));
+    if (T.comp != 3) return v3(0.f, 0.f, 0.f);
+    int texid = Y * T.w + X;
+    texid = texid < 0 ? 0 : (texid >= T.w * T.h ? T.w * T.h - 1 : texid);
+    const unsigned char* px = M.texels + T.offset + 3u * (unsigned)texid;
+    return v3(__fmul_rn((float)px[0], 0.003921568627f), __fmul_rn((float)px[1], 0.003921568627f),
+              __fmul_rn((float)px[2], 0.003921568627f));
+}
+
 }  // namespace ptk

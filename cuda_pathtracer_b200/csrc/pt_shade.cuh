@@ -92,13 +92,14 @@ __device__ __forceinline__ V3 cosine_hemisphere(const V3& n, uint32_t& rng)
               __fmaf_rn(p2.z, os, __fmaf_rn(p1.z, oc, __fmul_rn(up, n.z))));
 }
 
-// scatterRay (interactions.cu:43-85), texture-less materials.
+// scatterRay (interactions.cu:43-85).  `base` is the first colour factor (interactions.cu:60): the
+// texel of a textured material, m.color otherwise.
 __device__ __forceinline__ void scatter_exact(PathState& p, const V3& hit, const V3& n, const MatRec& m,
-                                              uint32_t& rng)
+                                              const V3& base, uint32_t& rng)
 {
     const V3 I = p.d;
     p.o = v3(__fmaf_rn(n.x, 1.0e-4f, hit.x), __fmaf_rn(n.y, 1.0e-4f, hit.y), __fmaf_rn(n.z, 1.0e-4f, hit.z));
-    p.c = v3(__fmul_rn(m.color[0], p.c.x), __fmul_rn(m.color[1], p.c.y), __fmul_rn(m.color[2], p.c.z));
+    p.c = v3(__fmul_rn(base.x, p.c.x), __fmul_rn(base.y, p.c.y), __fmul_rn(base.z, p.c.z));
     if (m.has_refractive != 0.0f) {
         const float ior = m.ior;
         const float a = __fadd_rn(ior, -1.0f), b = __fadd_rn(ior, 1.0f);
@@ -130,11 +131,14 @@ __device__ __forceinline__ void scatter_exact(PathState& p, const V3& hit, const
     p.c = v3(__fmul_rn(m.color[0], p.c.x), __fmul_rn(m.color[1], p.c.y), __fmul_rn(m.color[2], p.c.z));
 }
 
+__device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, const MatRec& m, int iter,
+                                            int idx, int rr);
+
 // shadeMaterials (pathtrace.cu:301-344) for one path at compacted slot `idx`.
 // Returns true when the path stays alive; on return p.c is the colour finalGather would add
 // for a terminated path (0 unless it ended on a light).
-__device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, const MatRec& m, int iter,
-                                            int idx, int rr)
+__device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, const MatRec& m, const V3& base,
+                                            int iter, int idx, int rr)
 {
     if (!(t > 0.0f)) {
         p.c = v3(0.f, 0.f, 0.f);
@@ -150,7 +154,7 @@ __device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, 
         return false;
     }
     const V3 hit = point_on_ray(p.o, p.d, t);
-    scatter_exact(p, hit, n, m, rng);
+    scatter_exact(p, hit, n, m, base, rng);
     const int old_bounces = p.bounces;
     p.bounces = old_bounces + 1;
     p.remaining -= 1;
@@ -172,6 +176,13 @@ __device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, 
         p.c = v3(__fdiv_rn(p.c.x, inv), __fdiv_rn(p.c.y, inv), __fdiv_rn(p.c.z, inv));
     }
     return true;
+}
+
+// texture-less convenience form
+__device__ __forceinline__ bool shade_exact(PathState& p, float t, const V3& n, const MatRec& m, int iter,
+                                            int idx, int rr)
+{
+    return shade_exact(p, t, n, m, v3(m.color[0], m.color[1], m.color[2]), iter, idx, rr);
 }
 
 }  // namespace ptk

@@ -37,6 +37,36 @@ class Camera(ctypes.Structure):          # == struct Camera, sceneStructs.h:58-6
                 ("fov", ctypes.c_float * 2), ("pixelLength", ctypes.c_float * 2)]
 
 
+class Triangle(ctypes.Structure):        # == class Triangle, sceneStructs.h:103-160 (124 B)
+    _fields_ = [("id", ctypes.c_int32), ("vertices", (ctypes.c_float * 3) * 3), ("uv", (ctypes.c_float * 2) * 3),
+                ("normals", (ctypes.c_float * 3) * 3), ("bbox_min", ctypes.c_float * 3), ("bbox_max", ctypes.c_float * 3)]
+
+
+class BVHNode(ctypes.Structure):         # == class BVHTree, BVH_tree.h:57-64 (40 B)
+    _fields_ = [("min_corner", ctypes.c_float * 3), ("max_corner", ctypes.c_float * 3), ("sub_areas", ctypes.c_int32),
+                ("axis", ctypes.c_int32), ("first_area_idx", ctypes.c_int32), ("rchild_idx", ctypes.c_int32)]
+
+
+class _TextureC(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_int32), ("height", ctypes.c_int32), ("components", ctypes.c_int32),
+                ("pixels", ctypes.c_void_p)]
+
+
+class _SceneExtC(ctypes.Structure):
+    _fields_ = [("n_triangles", ctypes.c_int32), ("triangles", ctypes.POINTER(Triangle)),
+                ("n_bvh_nodes", ctypes.c_int32), ("bvh", ctypes.POINTER(BVHNode)),
+                ("n_textures", ctypes.c_int32), ("textures", ctypes.POINTER(_TextureC))]
+
+
+class Texture:
+    """class Texture (sceneStructs.h:162-189): width x height x components bytes, top row first"""
+
+    def __init__(self, width, height, components, pixels):
+        self.width, self.height, self.components = int(width), int(height), int(components)
+        self.pixels = np.ascontiguousarray(pixels, dtype=np.uint8).reshape(-1)
+        assert self.pixels.size == self.width * self.height * self.components
+
+
 class _SceneC(ctypes.Structure):
     _fields_ = [("camera", Camera), ("trace_depth", ctypes.c_int32), ("n_geoms", ctypes.c_int32),
                 ("geoms", ctypes.POINTER(Geom)), ("n_materials", ctypes.c_int32),
@@ -58,6 +88,7 @@ class _StatsC(ctypes.Structure):
 
 
 assert ctypes.sizeof(Geom) == 272 and ctypes.sizeof(Material) == 48 and ctypes.sizeof(Camera) == 84
+assert ctypes.sizeof(Triangle) == 124 and ctypes.sizeof(BVHNode) == 40
 
 
 class GuiDataContainer:
@@ -81,12 +112,15 @@ class GuiDataContainer:
 class Scene:
     """The POD part of the reference's ``Scene`` (scene.h:17-36): geoms, materials, state."""
 
-    def __init__(self, camera, trace_depth, iterations, geoms, materials):
+    def __init__(self, camera, trace_depth, iterations, geoms, materials, triangles=None, bvh=None, textures=None):
         self.camera = camera
         self.traceDepth = int(trace_depth)
         self.iterations = int(iterations)
         self.geoms = geoms
         self.materials = materials
+        self.triangles = triangles if triangles is not None else (Triangle * 0)()
+        self.bvh = bvh if bvh is not None else (BVHNode * 0)()
+        self.textures = list(textures or [])
         w, h = camera.resolution[0], camera.resolution[1]
         self.state_image = np.zeros((h, w, 3), dtype=np.float32)   # RenderState::image (SUM)
 
@@ -103,8 +137,8 @@ class Scene:
         """Read a "B2PTSCN1" dump: header, Camera, Geom[], Material[] (see oracle/ref_scene_dump.cpp
         and the repo's own loader, which writes the same layout)."""
         raw = open(path, "rb").read()
-        if raw[:8] != b"B2PTSCN1":
-            raise ValueError(f"{path}: not a B2PTSCN1 scene dump")
+        if raw[:8] not in (b"B2PTSCN1", b"B2PTSCN2"):
+            raise ValueError(f"{path}: not a B2PTSCN1 / B2PTSCN2 scene dump")
         n_geoms, n_mats, depth, iters = struct.unpack_from("<4i", raw, 8)
         off = 24
         cam = Camera.from_buffer_copy(raw, off)
@@ -112,7 +146,22 @@ class Scene:
         geoms = (Geom * n_geoms).from_buffer_copy(raw, off)
         off += ctypes.sizeof(Geom) * n_geoms
         mats = (Material * n_mats).from_buffer_copy(raw, off)
-        return Scene(cam, depth, iters, geoms, mats)
+        off += ctypes.sizeof(Material) * n_mats
+        if raw[:8] == b"B2PTSCN1":
+            return Scene(cam, depth, iters, geoms, mats)
+        n_tris, n_nodes, n_tex, _ = struct.unpack_from("<4i", raw, off)
+        off += 16
+        tris = (Triangle * n_tris).from_buffer_copy(raw, off)
+        off += ctypes.sizeof(Triangle) * n_tris
+        bvh = (BVHNode * n_nodes).from_buffer_copy(raw, off)
+        off += ctypes.sizeof(BVHNode) * n_nodes
+        textures = []
+        for _ in range(n_tex):
+            w, h, comp, _pad = struct.unpack_from("<4i", raw, off)
+            off += 16
+            textures.append(Texture(w, h, comp, np.frombuffer(raw, dtype=np.uint8, count=w * h * comp, offset=off)))
+            off += w * h * comp
+        return Scene(cam, depth, iters, geoms, mats, tris, bvh, textures)
 
 
 def _lib():
@@ -122,6 +171,7 @@ def _lib():
         lib.b200pt_default_options.argtypes = [ctypes.POINTER(_OptionsC)]
         lib.b200pt_default_options.restype = None
         lib.b200pt_create.argtypes = [ctypes.POINTER(_SceneC), ctypes.POINTER(vp)]
+        lib.b200pt_create_ext.argtypes = [ctypes.POINTER(_SceneC), ctypes.POINTER(_SceneExtC), ctypes.POINTER(vp)]
         lib.b200pt_destroy.argtypes = [vp]
         lib.b200pt_set_options.argtypes = [vp, ctypes.POINTER(_OptionsC)]
         lib.b200pt_reset.argtypes = [vp]
@@ -156,7 +206,10 @@ class Renderer:
         sc = _SceneC(scene.camera, scene.traceDepth, len(scene.geoms), scene.geoms,
                      len(scene.materials), scene.materials)
         self._h = ctypes.c_void_p()
-        check(_lib().b200pt_create(ctypes.byref(sc), ctypes.byref(self._h)))
+        tex = (_TextureC * len(scene.textures))(*[_TextureC(t.width, t.height, t.components, t.pixels.ctypes.data)
+                                                  for t in scene.textures])
+        ext = _SceneExtC(len(scene.triangles), scene.triangles, len(scene.bvh), scene.bvh, len(scene.textures), tex)
+        check(_lib().b200pt_create_ext(ctypes.byref(sc), ctypes.byref(ext), ctypes.byref(self._h)))
 
     def close(self):
         if self._h:

@@ -62,7 +62,7 @@ typedef struct b200pt_material {
     float hasRefractive;
     float indexOfRefraction;
     float emittance;
-    int32_t texture_id; /* -1 = none; textures are not supported yet: create() rejects others */
+    int32_t texture_id; /* -1 = none, else an index into b200pt_scene_ext::textures */
 } b200pt_material;
 
 /* == struct Camera (84 bytes) */
@@ -85,6 +85,49 @@ typedef struct b200pt_scene {
     int32_t n_materials;
     const b200pt_material* materials;
 } b200pt_scene;
+
+/* ---- triangle meshes, BVH and textures (the room.json path of the reference) -----------------
+ * Same byte layouts as the reference's host structures, so a shim passes scene->triangles.data()
+ * and scene->bvh_tree as they are:
+ *   b200pt_triangle == class Triangle (124 B, sceneStructs.h:103-160): WORLD-space vertices, per-vertex
+ *     texture coordinates and normals, `id` = index of the triangle before the BVH build reordered
+ *     the array (Geom::tri_start_idx/tri_end_idx are ranges of ids);
+ *   b200pt_bvh_node == class BVHTree (40 B, BVH_tree.h:57-64): flattened in DFS order, the left child
+ *     of node i is node i+1, `sub_areas` > 0 marks a leaf holding triangles
+ *     [first_area_idx, first_area_idx + sub_areas).
+ * A texture is width x height x components bytes, row-major, top row first (class Texture,
+ * sceneStructs.h:162-189; only components == 3 yields a colour, anything else reads as black). */
+typedef struct b200pt_triangle {
+    int32_t id;
+    float vertices[3][3];
+    float uv[3][2];
+    float normals[3][3];
+    float bbox_min[3];            /* unused (never assigned by the reference's loader) */
+    float bbox_max[3];
+} b200pt_triangle;
+
+typedef struct b200pt_bvh_node {
+    float min_corner[3];
+    float max_corner[3];
+    int32_t sub_areas;
+    int32_t axis;
+    int32_t first_area_idx;
+    int32_t rchild_idx;
+} b200pt_bvh_node;
+
+typedef struct b200pt_texture {
+    int32_t width, height, components;
+    const unsigned char* pixels;  /* host memory */
+} b200pt_texture;
+
+typedef struct b200pt_scene_ext {
+    int32_t n_triangles;
+    const b200pt_triangle* triangles;
+    int32_t n_bvh_nodes;
+    const b200pt_bvh_node* bvh;
+    int32_t n_textures;
+    const b200pt_texture* textures;
+} b200pt_scene_ext;
 
 /* The run-time toggles of GuiDataContainer (utilities.h:17-34) with the reference's defaults,
  * plus the knobs that are new here. */
@@ -118,6 +161,8 @@ void b200pt_default_options(b200pt_options* o);
 
 /* Allocate device state for `scene` on the current device and zero the accumulation image. */
 int b200pt_create(const b200pt_scene* scene, b200pt** out);
+/* The same for a scene with MESH geoms and / or textured materials (`ext` may be NULL). */
+int b200pt_create_ext(const b200pt_scene* scene, const b200pt_scene_ext* ext, b200pt** out);
 int b200pt_destroy(b200pt* h);
 int b200pt_set_options(b200pt* h, const b200pt_options* o);
 /* Zero the accumulation image and the statistics (what pathtraceInit does, pathtrace.cu:121-122). */

@@ -9,7 +9,10 @@
 // (tests/golden/make_pt_golden.py) which pin the repo's own scene loader and feed the C ABI.
 //
 // File layout (little endian): "B2PTSCN1", int32 n_geoms, n_materials, trace_depth, iterations,
-// then Camera, Geom[n_geoms], Material[n_materials].
+// then Camera, Geom[n_geoms], Material[n_materials].  Scenes with triangle meshes are written as
+// "B2PTSCN2": the same, followed by int32 n_triangles, n_bvh_nodes, n_textures, 0, then
+// Triangle[n_triangles] (124 B each, in the order the BVH build left them), BVHTree[n_bvh_nodes]
+// (40 B each, DFS order), and per texture int32 width, height, components, 0 + the raw pixel bytes.
 //
 //   ref_scene_dump SCENE.json OUT.bin [--refract MATERIAL_ID IOR]...
 #include <cstdio>
@@ -57,11 +60,13 @@ int main(int argc, char** argv)
     cam.position = cameraPosition;
 
     static_assert(sizeof(Camera) == 84 && sizeof(Geom) == 272 && sizeof(Material) == 48, "layout");
+    static_assert(sizeof(Triangle) == 124 && sizeof(BVHTree) == 40, "layout");
+    const bool v2 = !scene->triangles.empty() || !scene->textures.empty();
     FILE* f = fopen(argv[2], "wb");
     if (!f) { perror("fopen"); return 1; }
     int hdr[4] = {(int)scene->geoms.size(), (int)scene->materials.size(), scene->state.traceDepth,
                   (int)scene->state.iterations};
-    fwrite("B2PTSCN1", 1, 8, f);
+    fwrite(v2 ? "B2PTSCN2" : "B2PTSCN1", 1, 8, f);
     fwrite(hdr, sizeof(int), 4, f);
     fwrite(&cam, sizeof(Camera), 1, f);
     for (Geom g : scene->geoms) {
@@ -72,6 +77,26 @@ int main(int argc, char** argv)
         fwrite(&g, sizeof(Geom), 1, f);
     }
     fwrite(scene->materials.data(), sizeof(Material), scene->materials.size(), f);
+    if (v2) {
+        int ext[4] = {(int)scene->triangles.size(), scene->triangles.empty() ? 0 : scene->n_bvh_nodes,
+                      (int)scene->textures.size(), 0};
+        fwrite(ext, sizeof(int), 4, f);
+        for (Triangle t : scene->triangles) {
+            memset(&t.BoundBox, 0, sizeof(t.BoundBox));     // never assigned by the reference's loader
+            fwrite(&t, sizeof(Triangle), 1, f);
+        }
+        for (int i = 0; i < ext[1]; ++i) {
+            BVHTree node = scene->bvh_tree[i];
+            if (node.sub_areas > 0) { node.Axis = 0; node.RChild_idx = 0; }        // uninitialised in leaves
+            else node.first_area_idx = 0;                                          // ... and in inner nodes
+            fwrite(&node, sizeof(BVHTree), 1, f);
+        }
+        for (const Texture& t : scene->textures) {
+            int th[4] = {t.width, t.height, t.components, 0};
+            fwrite(th, sizeof(int), 4, f);
+            fwrite(t.image, 1, (size_t)t.width * t.height * t.components, f);
+        }
+    }
     fclose(f);
     printf("wrote %s: %d geoms, %d materials, %dx%d, depth %d, %d iterations\n", argv[2], hdr[0], hdr[1],
            cam.resolution.x, cam.resolution.y, hdr[2], hdr[3]);

@@ -86,7 +86,8 @@ int main(int argc, char** argv)
     if (argc < 4) { fprintf(stderr, "usage: see the header of oracle/ref_stage_probe.cu\n"); return 1; }
     const std::string mode = argv[1];
     std::vector<char> raw = read_file<char>(argv[2]);
-    if (memcmp(raw.data(), "B2PTSCN1", 8) != 0) { fprintf(stderr, "bad scene dump\n"); return 1; }
+    const bool v2 = memcmp(raw.data(), "B2PTSCN2", 8) == 0;
+    if (!v2 && memcmp(raw.data(), "B2PTSCN1", 8) != 0) { fprintf(stderr, "bad scene dump\n"); return 1; }
     int hdr[4];
     memcpy(hdr, raw.data() + 8, 16);
     Camera cam;
@@ -96,6 +97,36 @@ int main(int argc, char** argv)
     std::vector<Material> mats(hdr[1]);
     memcpy(mats.data(), raw.data() + 24 + sizeof(Camera) + sizeof(Geom) * hdr[0], sizeof(Material) * hdr[1]);
     const int depth = hdr[2];
+    // triangle meshes / BVH / textures (B2PTSCN2), uploaded as pathtraceInit does (pathtrace.cu:137-166)
+    Triangle* d_tris = nullptr;
+    BVHTree* d_bvh = nullptr;
+    Texture* d_textures = nullptr;
+    if (v2) {
+        const char* at = raw.data() + 24 + sizeof(Camera) + sizeof(Geom) * hdr[0] + sizeof(Material) * hdr[1];
+        int ext[4];
+        memcpy(ext, at, 16);
+        at += 16;
+        std::vector<Triangle> tris(ext[0]);
+        memcpy((void*)tris.data(), at, sizeof(Triangle) * ext[0]);
+        at += sizeof(Triangle) * ext[0];
+        std::vector<BVHTree> nodes(ext[1]);
+        memcpy((void*)nodes.data(), at, sizeof(BVHTree) * ext[1]);
+        at += sizeof(BVHTree) * ext[1];
+        std::vector<Texture> texs(ext[2]);
+        for (int i = 0; i < ext[2]; ++i) {
+            int th[4];
+            memcpy(th, at, 16);
+            at += 16;
+            texs[i].id = i; texs[i].width = th[0]; texs[i].height = th[1]; texs[i].components = th[2];
+            const size_t bytes = (size_t)th[0] * th[1] * th[2];
+            cudaMalloc(&texs[i].dev_image, bytes);
+            cudaMemcpy(texs[i].dev_image, at, bytes, cudaMemcpyHostToDevice);
+            at += bytes;
+        }
+        if (ext[0]) { cudaMalloc(&d_tris, sizeof(Triangle) * ext[0]); cudaMemcpy(d_tris, tris.data(), sizeof(Triangle) * ext[0], cudaMemcpyHostToDevice); }
+        if (ext[0] && ext[1]) { cudaMalloc(&d_bvh, sizeof(BVHTree) * ext[1]); cudaMemcpy(d_bvh, nodes.data(), sizeof(BVHTree) * ext[1], cudaMemcpyHostToDevice); }
+        if (ext[2]) { cudaMalloc(&d_textures, sizeof(Texture) * ext[2]); cudaMemcpy(d_textures, texs.data(), sizeof(Texture) * ext[2], cudaMemcpyHostToDevice); }
+    }
 
     Settings st{};
     st.enable_RussianRoulette = true; st.use_BoundingBoxTest = true; st.use_BVHtree = true;
@@ -132,8 +163,8 @@ int main(int argc, char** argv)
         ShadeableIntersection* d_is = nullptr;
         cudaMalloc(&d_is, sizeof(ShadeableIntersection) * n);
         cudaMemset(d_is, 0, sizeof(ShadeableIntersection) * n);                              // pathtrace.cu:466
-        computeIntersections<<<(n + 63) / 64, 64>>>(0, n, d_paths, d_geoms, (int)geoms.size(), d_is, nullptr, nullptr,
-                                                    nullptr, d_st);
+        computeIntersections<<<(n + 63) / 64, 64>>>(0, n, d_paths, d_geoms, (int)geoms.size(), d_is, d_tris, nullptr,
+                                                    d_bvh, d_st);
         cudaDeviceSynchronize();
         write_file(argv[4], d_is, (size_t)n);
     } else if (mode == "shade") {
@@ -143,7 +174,7 @@ int main(int argc, char** argv)
         const int n = (int)segs.size();
         PathSegment* d_paths = upload(segs);
         ShadeableIntersection* d_is = upload(is);
-        shadeMaterials<<<(n + 63) / 64, 64>>>(iter, n, d_st, d_is, d_paths, d_mats, nullptr);
+        shadeMaterials<<<(n + 63) / 64, 64>>>(iter, n, d_st, d_is, d_paths, d_mats, d_textures);
         cudaDeviceSynchronize();
         write_file(argv[6], d_paths, (size_t)n);
     } else {

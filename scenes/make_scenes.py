@@ -13,6 +13,10 @@ cornell_glass_1080p.json   config 4: 1920x1080, depth 12, mirror + glass + diffu
                     reference loader ignores: the reference baseline patches material id
                     `glass` after load (oracle/ref_headless_main.cpp --refract).
 synthetic_4096.json config 5: 4096 random spheres/cubes, 64 materials, 3840x2160, depth 8.
+mesh_room*.json     triangle meshes + textures in the layout of the reference's scenes/room.json
+                    (cube walls, "mesh" objects with OBJ_FILE under Models/, materials with
+                    TEXTURE_FILE under Textures/).  The OBJ models (grid quad, icosphere, torus) and the
+                    binary PPM textures are generated here as well.
 """
 import json
 import os
@@ -123,6 +127,143 @@ def synthetic(n_prims, res, iters, depth, name, seed=565):
     return {"Materials": mats, "Camera": cam, "Objects": objs}
 
 
+# ---- triangle meshes and textures (the room.json analogue) -----------------------------------------
+import math
+
+
+def fmt(x):
+    return "%.6f" % x
+
+
+def write_obj(name, verts, uvs, normals, faces):
+    """faces: tuples of (v, vt, vn) 0-based index triples, counter-clockwise seen from outside"""
+    os.makedirs(os.path.join(HERE, "Models"), exist_ok=True)
+    with open(os.path.join(HERE, "Models", name), "w") as f:
+        f.write("# generated by scenes/make_scenes.py\n")
+        for v in verts:
+            f.write("v " + " ".join(fmt(c) for c in v) + "\n")
+        for t in uvs:
+            f.write("vt " + " ".join(fmt(c) for c in t) + "\n")
+        for n in normals:
+            f.write("vn " + " ".join(fmt(c) for c in n) + "\n")
+        for face in faces:
+            f.write("f " + " ".join("%d/%d/%d" % (a + 1, b + 1, c + 1) for a, b, c in face) + "\n")
+
+
+def grid_quad(n):
+    """unit square in the xy plane facing +z, n x n cells, QUAD faces (the loader fans them)"""
+    verts, uvs = [], []
+    for j in range(n + 1):
+        for i in range(n + 1):
+            verts.append((i / n - 0.5, j / n - 0.5, 0.0))
+            uvs.append((i / n, j / n))
+    faces = []
+    for j in range(n):
+        for i in range(n):
+            a, b, c, d = j * (n + 1) + i, j * (n + 1) + i + 1, (j + 1) * (n + 1) + i + 1, (j + 1) * (n + 1) + i
+            faces.append([(a, a, 0), (b, b, 0), (c, c, 0), (d, d, 0)])
+    return verts, uvs, [(0.0, 0.0, 1.0)], faces
+
+
+def icosphere(levels):
+    t = (1.0 + math.sqrt(5.0)) / 2.0
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t),
+         (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    f = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6),
+         (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10),
+         (8, 6, 7), (9, 8, 1)]
+
+    def norm(p):
+        l = math.sqrt(sum(c * c for c in p))
+        return tuple(c / l for c in p)
+
+    v = [norm(p) for p in v]
+    for _ in range(levels):
+        cache, nf = {}, []
+
+        def mid(a, b):
+            key = (min(a, b), max(a, b))
+            if key not in cache:
+                cache[key] = len(v)
+                v.append(norm(tuple((v[a][k] + v[b][k]) / 2 for k in range(3))))
+            return cache[key]
+
+        for a, b, c in f:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        f = nf
+    verts = [tuple(0.5 * c for c in p) for p in v]
+    uvs = [(0.5 + math.atan2(p[2], p[0]) / (2 * math.pi), 0.5 - math.asin(max(-1.0, min(1.0, p[1]))) / math.pi) for p in v]
+    faces = [[(a, a, a), (b, b, b), (c, c, c)] for a, b, c in f]
+    return verts, uvs, v, faces
+
+
+def torus(nu, nv, R=0.35, r=0.15):
+    verts, uvs, normals = [], [], []
+    for i in range(nu):
+        for j in range(nv):
+            u, w = 2 * math.pi * i / nu, 2 * math.pi * j / nv
+            verts.append(((R + r * math.cos(w)) * math.cos(u), r * math.sin(w), (R + r * math.cos(w)) * math.sin(u)))
+            normals.append((math.cos(w) * math.cos(u), math.sin(w), math.cos(w) * math.sin(u)))
+            uvs.append((i / nu, j / nv))
+    faces = []
+    for i in range(nu):
+        for j in range(nv):
+            a, b = i * nv + j, ((i + 1) % nu) * nv + j
+            c, d = ((i + 1) % nu) * nv + (j + 1) % nv, i * nv + (j + 1) % nv
+            faces.append([(a, a, a), (d, d, d), (c, c, c)])
+            faces.append([(a, a, a), (c, c, c), (b, b, b)])
+    return verts, uvs, normals, faces
+
+
+def write_ppm(name, w, h, pixel):
+    os.makedirs(os.path.join(HERE, "Textures"), exist_ok=True)
+    with open(os.path.join(HERE, "Textures", name), "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(bytes(c for y in range(h) for x in range(w) for c in pixel(x, y)))
+
+
+def mesh_assets():
+    write_obj("grid_quad.obj", *grid_quad(4))
+    write_obj("icosphere.obj", *icosphere(2))
+    write_obj("torus.obj", *torus(16, 12))
+    write_ppm("checker.ppm", 64, 64,
+              lambda x, y: (230, 230, 60) if ((x // 8) + (y // 8)) % 2 else (40, 60, 200))
+    write_ppm("gradient.ppm", 48, 32, lambda x, y: (5 * x + 10, 7 * y + 20, (x * y) % 256))
+
+
+def mesh_room(res, iters, depth, name):
+    mats = {
+        "light": {"TYPE": "Emitting", "RGB": [1.0, 1.0, 1.0], "EMITTANCE": 12.0},
+        "diffuse_white": {"TYPE": "Diffuse", "RGB": [0.98, 0.98, 0.98]},
+        "diffuse_red": {"TYPE": "Diffuse", "RGB": [0.85, 0.65, 0.65], "SPECRGB": [0.98, 0.98, 0.98], "REFL": 1.0},
+        "diffuse_blue": {"TYPE": "Diffuse", "RGB": [0.65, 0.65, 0.85]},
+        "checker_wall": {"TYPE": "Diffuse", "RGB": [0.88, 0.88, 0.88], "TEXTURE_FILE": "checker.ppm"},
+        "gradient_skin": {"TYPE": "Diffuse", "RGB": [0.98, 0.98, 0.98], "SPECRGB": [0.5, 0.58, 0.9],
+                          "TEXTURE_FILE": "gradient.ppm"},
+        "mirror": {"TYPE": "Specular", "RGB": [0.98, 0.98, 0.98], "REFLECTIVE": 1.0},
+        "plain_green": {"TYPE": "Diffuse", "RGB": [0.35, 0.85, 0.35]},
+    }
+
+    def mesh(mat, obj, t, r, s):
+        return {"TYPE": "mesh", "MATERIAL": mat, "TRANS": t, "ROTAT": r, "SCALE": s, "OBJ_FILE": obj}
+
+    objs = [
+        cube("light", [0.0, 10.0, 0.0], [0.0, 0.0, 0.0], [3.0, 0.1, 3.0]),
+        cube("diffuse_white", [0.0, 0.0, 0.0], [0.0, 0.0, 0.0], [15.0, 0.01, 15.0]),
+        cube("diffuse_white", [0.0, 10.0, 0.0], [0.0, 0.0, 90.0], [0.01, 15.0, 15.0]),
+        cube("diffuse_white", [0.0, 5.0, -5.0], [0.0, 90.0, 0.0], [0.01, 10.0, 15.0]),
+        cube("diffuse_red", [-7.0, 5.0, 0.0], [0.0, 0.0, 0.0], [0.01, 10.0, 15.0]),
+        cube("diffuse_blue", [7.0, 5.0, 0.0], [0.0, 0.0, 0.0], [0.01, 10.0, 15.0]),
+        mesh("checker_wall", "grid_quad.obj", [0.0, 5.0, -4.8], [0.0, 0.0, 0.0], [9.0, 7.0, 1.0]),
+        mesh("gradient_skin", "icosphere.obj", [-2.5, 2.0, -1.0], [0.0, 30.0, 0.0], [3.6, 3.6, 3.6]),
+        mesh("plain_green", "torus.obj", [2.6, 2.2, 0.5], [35.0, 20.0, 10.0], [5.0, 5.0, 5.0]),
+        sphere("mirror", [0.3, 1.2, 2.0], [0.0, 0.0, 0.0], [2.4, 2.4, 2.4]),
+        mesh("gradient_skin", "torus.obj", [-3.5, 6.5, -2.0], [80.0, 0.0, 25.0], [4.0, 4.0, 4.0]),
+    ]
+    return {"Materials": mats, "Camera": camera(res, iters, depth, name), "Objects": objs}
+
+
 def write(name, scene):
     with open(os.path.join(HERE, name), "w") as f:
         json.dump(scene, f, indent=1 if len(scene["Objects"]) < 100 else None)
@@ -139,6 +280,9 @@ def main():
     write("cornell_glass_small.json", cornell_glass((192, 108), 64, 12, "cornell_glass_small"))
     write("synthetic_4096.json", synthetic(4096, (3840, 2160), 256, 8, "synthetic_4096"))
     write("synthetic_600_small.json", synthetic(600, (128, 72), 16, 8, "synthetic_600_small"))
+    mesh_assets()
+    write("mesh_room.json", mesh_room((1200, 1200), 2000, 8, "mesh_room"))
+    write("mesh_room_small.json", mesh_room((160, 160), 32, 8, "mesh_room_small"))
 
 
 if __name__ == "__main__":

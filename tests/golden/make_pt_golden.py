@@ -27,6 +27,8 @@ SCENES = {
     "cornell_glass_small": ["--refract", "4", "1.5"],
     "cornell_glass_1080p": ["--refract", "4", "1.5"],
     "synthetic_600_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
+    "mesh_room_small": [],
+    "mesh_room": [],
     "synthetic_4096": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
 }
 # (scene, iterations, extra renderer flags, tag)
@@ -40,6 +42,9 @@ RENDERS = [
     ("cornell_glass_small", 16, ["--sort"], "sort"),
     ("synthetic_600_small", 4, ["--sort"], "sort"),
     ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
+    # triangle meshes + BVH + textures (the room.json path)
+    ("mesh_room_small", 8, [], "default"),
+    ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
 ]
 
 

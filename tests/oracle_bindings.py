@@ -87,6 +87,15 @@ class PtOracle:
         self.lib = ctypes.CDLL(_ensure_built("_build/liboracle_pt.so"))
         self.lib.pt_oracle_render.restype = ctypes.c_ulonglong
 
+    def _set_mesh(self, scene):
+        """hand the scene's triangles / BVH / textures to the oracle (kept alive on self)"""
+        tris, bvh, texs = getattr(scene, "triangles", ()), getattr(scene, "bvh", ()), getattr(scene, "textures", [])
+        dims = (ctypes.c_int * max(1, 3 * len(texs)))(*[v for t in texs for v in (t.width, t.height, t.components)])
+        ptrs = (ctypes.c_void_p * max(1, len(texs)))(*[t.pixels.ctypes.data for t in texs])
+        self._keep = (scene, dims, ptrs)
+        self.lib.pt_oracle_set_mesh(tris if len(tris) else None, len(tris), bvh if len(bvh) else None, len(bvh),
+                                    len(texs), dims, ptrs)
+
     @staticmethod
     def _opts(gui):
         o5 = (ctypes.c_int * 5)(int(gui.russianRoulette), int(gui.sortbyMaterial), int(gui.SSAA), int(gui.DoF), 0)
@@ -115,6 +124,7 @@ class PtOracle:
     def intersect(self, scene, segments):
         segments = np.ascontiguousarray(segments, dtype=np.float32)
         out = np.zeros((len(segments), 7), dtype=np.float32)
+        self._set_mesh(scene)
         self.lib.pt_oracle_intersect(scene.geoms, len(scene.geoms), len(segments),
                                      segments.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
         return out
@@ -122,6 +132,7 @@ class PtOracle:
     def shade(self, scene, gui, iteration, isects, segments):
         seg = np.ascontiguousarray(segments, dtype=np.float32).copy()
         isects = np.ascontiguousarray(isects, dtype=np.float32)
+        self._set_mesh(scene)
         self.lib.pt_oracle_shade(scene.materials, int(gui.russianRoulette), int(iteration), len(seg),
                                  isects.ctypes.data_as(ctypes.c_void_p), seg.ctypes.data_as(ctypes.c_void_p))
         return seg
@@ -133,6 +144,7 @@ class PtOracle:
             out = np.zeros((scene.height, scene.width, 3), dtype=np.float32)
         if threads is None:
             threads = os.cpu_count() or 1
+        self._set_mesh(scene)
         seg = self.lib.pt_oracle_render(ctypes.byref(scene.camera), scene.traceDepth, scene.geoms, len(scene.geoms),
                                         scene.materials, o5, o2, int(first_iter), int(n_iters), int(stride),
                                         out.ctypes.data_as(ctypes.c_void_p), int(threads))

@@ -15,6 +15,7 @@ RENDERS = [
     ("cornell_small_mirror", 16, [], "default"),
     ("cornell_glass_small", 16, [], "default"),
     ("synthetic_600_small", 4, [], "default"),
+    ("mesh_room_small", 8, [], "default"),                # triangle meshes, BVH, textures
 ]
 # material sort on (thrust::sort_by_key in the reference, pathtrace.cu:479-491): the paths differ
 # from the unsorted ones because the shading seed is the slot index AFTER sorting
@@ -22,10 +23,11 @@ SORT_RENDERS = [
     ("cornell_glass_small", 16, ["--sort"], "sort"),
     ("synthetic_600_small", 4, ["--sort"], "sort"),
     ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
+    ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
 ]
 # per-stage vectors from the reference's own kernels (tests/golden/make_pt_stage_golden.py)
 STAGES = [("cornell_tiny", "default", []), ("cornell_tiny", "plain", ["--no-ssaa", "--no-dof", "--no-rr"]),
-          ("cornell_glass_small", "default", [])]
+          ("cornell_glass_small", "default", []), ("mesh_room_small", "default", [])]
 
 
 def load_scene(name):
