@@ -31,7 +31,7 @@ $(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS) $(PKG)/libb200sc.so include/b200_sc.h
 HOST     := $(PKG)/host
 BIN      := $(PKG)/bin
 CXXFLAGS := -std=c++17 -O2 -ffp-contract=off -Wall -Iinclude -I/usr/local/cuda/include
-HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/image_io.hpp include/b200_pt.h
+HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/mesh.hpp $(HOST)/image_io.hpp include/b200_pt.h
 
 host: $(BIN)/cuda_path_tracer $(BIN)/stream_compaction_test
 
@@ -39,7 +39,7 @@ $(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
 	@mkdir -p $(BIN)
 	g++ $(CXXFLAGS) -c -o $@ $<
 
-$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/image_io.o $(PKG)/libb200pt.so
+$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/mesh.o $(BIN)/image_io.o $(PKG)/libb200pt.so
 	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200pt -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN/..'
 
 $(BIN)/stream_compaction_test: $(HOST)/sc_harness.cpp include/b200_stream_compaction.hpp include/b200_sc.h $(PKG)/libb200sc.so

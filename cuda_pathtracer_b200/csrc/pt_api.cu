@@ -220,7 +220,11 @@ int validate_scene_counts(const b200pt_scene* sc, int n_tris, int n_nodes, int n
     for (int i = 0; i < sc->n_geoms; ++i) {
         const int type = sc->geoms[i].type;
         if (type != B200PT_SPHERE && type != B200PT_CUBE && type != B200PT_MESH) return B200_E_UNSUPPORTED;
-        if (type == B200PT_MESH && n_tris && n_nodes == 0) return B200_E_UNSUPPORTED;   // meshes need the BVH
+        if (type == B200PT_MESH) {
+            const int b = sc->geoms[i].tri_start_idx, e = sc->geoms[i].tri_end_idx;    // a range of triangle ids
+            if (b < 0 || e < b || e > n_tris) return B200_E_BADARG;
+            if (e > b && n_nodes == 0) return B200_E_UNSUPPORTED;                        // meshes are traced through the BVH
+        }
         if (sc->geoms[i].materialid < 0 || sc->geoms[i].materialid >= sc->n_materials) return B200_E_BADARG;
     }
     for (int i = 0; i < sc->n_materials; ++i)

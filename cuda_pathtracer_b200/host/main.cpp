@@ -22,7 +22,7 @@
 //   --hdr                also write BASE.hdr              --no-png      skip the PNG
 //   --sum-out FILE       raw float SUM image (3*W*H floats, index x + y*W)
 //   --pbo-out FILE       raw uchar4 preview buffer (sendImageToPBO, pathtrace.cu:65-86)
-//   --dump-scene FILE    write the loaded scene as a "B2PTSCN1" POD dump and exit (no GPU needed)
+//   --dump-scene FILE    write the loaded scene as a "B2PTSCN1"/"B2PTSCN2" POD dump and exit (no GPU needed)
 //   --device D           CUDA device ordinal
 //   --resume-sum FILE --samples-done K   restartable rendering: start from a float SUM image that
 //                        already holds K samples (a --sum-out of an earlier run); iterations
@@ -161,7 +161,8 @@ int main(int argc, char** argv)
     }
     b200pt* renderer = nullptr;
     const b200pt_scene pod = scene->pod();
-    check(b200pt_create(&pod, &renderer), "pathtraceInit");
+    const b200pt_scene_ext ext = scene->pod_ext();
+    check(b200pt_create_ext(&pod, &ext, &renderer), "pathtraceInit");
     check(b200pt_set_options(renderer, &opt), "options");
 
     if (!resume_sum.empty()) {

@@ -1,0 +1,466 @@
+// mesh.cpp -- see mesh.hpp.
+#include "mesh.hpp"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+namespace b200host {
+
+// =====================================================================================================
+// OBJ
+// =====================================================================================================
+namespace {
+
+inline bool is_digit(char c) { return c >= '0' && c <= '9'; }
+
+// tinyobjloader 1.0.6 tryParseDouble (tiny_obj_loader.h:474-587), restated: integer digits are
+// accumulated in a double, each fractional digit adds digit * 10^-k (a small table for k < 8,
+// pow(10, -k) beyond), a decimal exponent e is applied as ldexp(m * 5^e, e).  The result can differ
+// from strtod in the last place, and the cast to float then (rarely) differs too -- hence this
+// restatement instead of strtod.
+bool parse_double(const char* s, const char* s_end, double* result)
+{
+    if (s >= s_end) return false;
+    double mantissa = 0.0;
+    int exponent = 0;
+    char sign = '+', exp_sign = '+';
+    const char* curr = s;
+    int read = 0;
+    bool more;
+    if (*curr == '+' || *curr == '-') { sign = *curr; curr++; }
+    else if (!is_digit(*curr)) return false;
+    more = curr != s_end;
+    while (more && is_digit(*curr)) {
+        mantissa *= 10;
+        mantissa += (int)(*curr - '0');
+        curr++; read++;
+        more = curr != s_end;
+    }
+    if (read == 0) return false;
+    bool assemble = !more;
+    if (!assemble) {
+        if (*curr == '.') {
+            static const double lut[] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
+            curr++;
+            read = 1;
+            more = curr != s_end;
+            while (more && is_digit(*curr)) {
+                mantissa += (int)(*curr - '0') * (read < 8 ? lut[read] : std::pow(10.0, -read));
+                read++; curr++;
+                more = curr != s_end;
+            }
+        } else if (*curr != 'e' && *curr != 'E') {
+            assemble = true;
+        }
+        if (!assemble && more && (*curr == 'e' || *curr == 'E')) {
+            curr++;
+            more = curr != s_end;
+            if (more && (*curr == '+' || *curr == '-')) { exp_sign = *curr; curr++; }
+            else if (!is_digit(*curr)) return false;
+            read = 0;
+            more = curr != s_end;
+            while (more && is_digit(*curr)) {
+                exponent *= 10;
+                exponent += (int)(*curr - '0');
+                curr++; read++;
+                more = curr != s_end;
+            }
+            exponent *= (exp_sign == '+' ? 1 : -1);
+            if (read == 0) return false;
+        }
+    }
+    *result = (sign == '+' ? 1 : -1) * (exponent ? std::ldexp(mantissa * std::pow(5.0, exponent), exponent) : mantissa);
+    return true;
+}
+
+// parseReal (tiny_obj_loader.h:589-597): next blank-delimited token, default when unparsable
+float parse_real(const char** token, double dflt = 0.0)
+{
+    *token += std::strspn(*token, " \t");
+    const char* end = *token + std::strcspn(*token, " \t\r");
+    double val = dflt;
+    parse_double(*token, end, &val);
+    *token = end;
+    return (float)val;
+}
+
+struct VertexIndex { int v, vt, vn; };
+
+// fixIndex: positive -> zero based, zero -> 0, negative -> relative to the end
+bool fix_index(int idx, int n, int* out)
+{
+    if (idx > 0) { *out = idx - 1; return true; }
+    if (idx == 0) return false;
+    *out = n + idx;
+    return true;
+}
+
+// "i", "i/j", "i//k", "i/j/k"
+bool parse_triple(const char** token, int vsize, int vnsize, int vtsize, VertexIndex* ret)
+{
+    VertexIndex vi{-1, -1, -1};
+    if (!fix_index(std::atoi(*token), vsize, &vi.v)) return false;
+    *token += std::strcspn(*token, "/ \t\r");
+    if ((*token)[0] != '/') { *ret = vi; return true; }
+    (*token)++;
+    if ((*token)[0] == '/') {                              // i//k
+        (*token)++;
+        if (!fix_index(std::atoi(*token), vnsize, &vi.vn)) return false;
+        *token += std::strcspn(*token, "/ \t\r");
+        *ret = vi;
+        return true;
+    }
+    if (!fix_index(std::atoi(*token), vtsize, &vi.vt)) return false;
+    *token += std::strcspn(*token, "/ \t\r");
+    if ((*token)[0] != '/') { *ret = vi; return true; }
+    (*token)++;
+    if (!fix_index(std::atoi(*token), vnsize, &vi.vn)) return false;
+    *token += std::strcspn(*token, "/ \t\r");
+    *ret = vi;
+    return true;
+}
+
+inline float fmin_glm(float x, float y) { return x < y ? x : y; }     // glm::min
+inline float fmax_glm(float x, float y) { return x > y ? x : y; }     // glm::max
+
+}  // namespace
+
+void load_obj_mesh(const std::string& path, const Mat4& transform, const Mat4& inv_transpose,
+                   std::vector<b200pt_triangle>& triangles, float min_bound[3], float max_bound[3])
+{
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("Cannot open file [" + path + "]");
+    std::vector<float> v, vn, vt;
+    std::vector<std::vector<VertexIndex>> faces;
+    std::string line;
+    while (std::getline(in, line)) {
+        if (!line.empty() && line.back() == '\n') line.pop_back();
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        if (line.empty()) continue;
+        const char* token = line.c_str();
+        token += std::strspn(token, " \t");
+        if (token[0] == '\0' || token[0] == '#') continue;
+        if (token[0] == 'v' && (token[1] == ' ' || token[1] == '\t')) {
+            token += 2;
+            const float x = parse_real(&token), y = parse_real(&token), z = parse_real(&token);
+            v.push_back(x); v.push_back(y); v.push_back(z);
+        } else if (token[0] == 'v' && token[1] == 'n' && (token[2] == ' ' || token[2] == '\t')) {
+            token += 3;
+            const float x = parse_real(&token), y = parse_real(&token), z = parse_real(&token);
+            vn.push_back(x); vn.push_back(y); vn.push_back(z);
+        } else if (token[0] == 'v' && token[1] == 't' && (token[2] == ' ' || token[2] == '\t')) {
+            token += 3;
+            const float x = parse_real(&token), y = parse_real(&token);
+            vt.push_back(x); vt.push_back(y);
+        } else if (token[0] == 'f' && (token[1] == ' ' || token[1] == '\t')) {
+            token += 2;
+            token += std::strspn(token, " \t");
+            std::vector<VertexIndex> face;
+            while (token[0] != '\0' && token[0] != '\r' && token[0] != '\n') {
+                VertexIndex vi;
+                if (!parse_triple(&token, (int)(v.size() / 3), (int)(vn.size() / 3), (int)(vt.size() / 2), &vi))
+                    throw std::runtime_error("Failed parse `f' line(e.g. zero value for face index)");
+                face.push_back(vi);
+                token += std::strspn(token, " \t\r");
+            }
+            faces.push_back(face);
+        }
+        // everything else (o, g, s, usemtl, mtllib, ...) does not change the order of the faces
+    }
+
+    // scene.cpp:113-170: one Triangle per (fan-triangulated) face, world space, bounds with the
+    // reference's initial values (min = FLT_MAX, max = FLT_MIN -- the smallest POSITIVE float, sic)
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {FLT_MIN, FLT_MIN, FLT_MIN};
+    for (const std::vector<VertexIndex>& face : faces) {
+        for (size_t k = 2; k < face.size(); ++k) {
+            const VertexIndex corner[3] = {face[0], face[k - 1], face[k]};
+            b200pt_triangle tri;
+            std::memset(&tri, 0, sizeof(tri));
+            for (int c = 0; c < 3; ++c) {
+                const VertexIndex& id = corner[c];
+                if (id.v < 0 || (size_t)(3 * id.v + 2) >= v.size()) throw std::runtime_error("vertex index out of range in " + path);
+                const Vec4 w = mul(transform, Vec4{v[3 * id.v], v[3 * id.v + 1], v[3 * id.v + 2], 1.0f});
+                tri.vertices[c][0] = w.x; tri.vertices[c][1] = w.y; tri.vertices[c][2] = w.z;
+                if (id.vn >= 0 && (size_t)(3 * id.vn + 2) < vn.size()) {
+                    const Vec4 n = mul(inv_transpose, Vec4{vn[3 * id.vn], vn[3 * id.vn + 1], vn[3 * id.vn + 2], 0.0f});
+                    tri.normals[c][0] = n.x; tri.normals[c][1] = n.y; tri.normals[c][2] = n.z;
+                }
+                if (id.vt >= 0 && (size_t)(2 * id.vt + 1) < vt.size()) {
+                    tri.uv[c][0] = vt[2 * id.vt];
+                    tri.uv[c][1] = vt[2 * id.vt + 1];
+                }
+            }
+            for (int a = 0; a < 3; ++a) {
+                const float lo = fmin_glm(fmin_glm(tri.vertices[0][a], tri.vertices[1][a]), tri.vertices[2][a]);
+                const float hi = fmax_glm(fmax_glm(tri.vertices[0][a], tri.vertices[1][a]), tri.vertices[2][a]);
+                mn[a] = std::min(lo, mn[a]);
+                mx[a] = std::max(hi, mx[a]);
+            }
+            tri.id = (int)triangles.size();
+            triangles.push_back(tri);
+        }
+    }
+    for (int a = 0; a < 3; ++a) { min_bound[a] = mn[a]; max_bound[a] = mx[a]; }
+}
+
+// =====================================================================================================
+// BVH (BVH_tree.cpp)
+// =====================================================================================================
+namespace {
+
+struct Box {
+    Vec3 lo{0.f, 0.f, 0.f}, hi{0.f, 0.f, 0.f};
+
+    bool all_zero() const { return lo.x == 0.0f && lo.y == 0.0f && lo.z == 0.0f && hi.x == 0.0f && hi.y == 0.0f && hi.z == 0.0f; }
+    // BoundingBox::operator||(BoundingBox&): an all-zero box counts as "empty" (boundingbox.h:48-66)
+    Box join(const Box& b) const
+    {
+        if (all_zero()) return b;
+        Box r;
+        r.lo = {fmin_glm(b.lo.x, lo.x), fmin_glm(b.lo.y, lo.y), fmin_glm(b.lo.z, lo.z)};
+        r.hi = {fmax_glm(b.hi.x, hi.x), fmax_glm(b.hi.y, hi.y), fmax_glm(b.hi.z, hi.z)};
+        return r;
+    }
+    // BoundingBox::operator||(const vec3&): no emptiness test
+    Box join(const Vec3& p) const
+    {
+        Box r;
+        r.lo = {fmin_glm(p.x, lo.x), fmin_glm(p.y, lo.y), fmin_glm(p.z, lo.z)};
+        r.hi = {fmax_glm(p.x, hi.x), fmax_glm(p.y, hi.y), fmax_glm(p.z, hi.z)};
+        return r;
+    }
+    int longest_axis() const
+    {
+        const Vec3 d = hi - lo;
+        return (d.x > d.y && d.x > d.z) ? 0 : (d.y > d.z) ? 1 : 2;
+    }
+    float area() const
+    {
+        const Vec3 d = hi - lo;
+        return 2.0f * (d.x * d.y + d.x * d.z + d.y * d.z);
+    }
+    Vec3 offset_of(const Vec3& p) const              // getOffsetBoxes
+    {
+        Vec3 o = p - lo;
+        if (hi.x > lo.x) o.x /= (hi.x - lo.x);
+        if (hi.y > lo.y) o.y /= (hi.y - lo.y);
+        if (hi.z > lo.z) o.z /= (hi.z - lo.z);
+        return o;
+    }
+};
+
+inline float axis_of(const Vec3& v, int a) { return a == 0 ? v.x : (a == 1 ? v.y : v.z); }
+
+struct BoxRef {            // BVH_BBox
+    int index;
+    Box bounds;
+    Vec3 center;
+};
+
+struct Node {              // BVHTreeNode
+    Box bbox;
+    Node* l = nullptr;
+    Node* r = nullptr;
+    int axis = 0, sub_areas = 0, first = 0;
+};
+
+constexpr int kMaxAreas = 8;                         // MAX_AREAS
+constexpr int kRegions = kMaxAreas - 1;
+
+int bucket_of(const Box& central, const Vec3& center, int axis)
+{
+    int idx = (int)(kRegions * axis_of(central.offset_of(center), axis));
+    if (idx == kRegions) idx = kRegions - 1;
+    return idx;
+}
+
+Node* make_leaf(std::vector<BoxRef>& bb, std::vector<b200pt_triangle>& ordered, const std::vector<b200pt_triangle>& tris,
+                int start, int end, const Box& bounds, Node* node)
+{
+    node->first = (int)ordered.size();
+    for (int i = start; i < end; ++i) ordered.push_back(tris[bb[i].index]);
+    node->sub_areas = end - start;
+    node->bbox = bounds;
+    node->axis = -1;
+    return node;
+}
+
+Node* build(std::vector<BoxRef>& bb, std::vector<b200pt_triangle>& ordered, const std::vector<b200pt_triangle>& tris,
+            int start, int end, int& n_nodes)
+{
+    Node* node = new Node();
+    n_nodes += 1;
+    Box bounds = bb[start].bounds;
+    for (int i = start; i < end; ++i) bounds = bounds.join(bb[i].bounds);
+    const int n_tris = end - start;
+    if (n_tris == 1) return make_leaf(bb, ordered, tris, start, end, bounds, node);
+
+    Box central;
+    central.lo = central.hi = bb[start].center;
+    for (int i = start; i < end; ++i) central = central.join(bb[i].center);
+    const int axis = central.longest_axis();
+    if (axis_of(central.lo, axis) == axis_of(central.hi, axis)) return make_leaf(bb, ordered, tris, start, end, bounds, node);
+
+    int mid;
+    if (n_tris == 2) {
+        mid = (int)(1.0f * (start + end) / 2.0f);
+        // std::nth_element on two elements is an insertion sort: swap iff the second compares less
+        if (axis_of(bb[start + 1].center, axis) < axis_of(bb[start].center, axis)) std::swap(bb[start], bb[start + 1]);
+    } else {
+        struct Region { int count = 0; Box bounds; } regions[kRegions];
+        for (int i = start; i < end; ++i) {
+            const int idx = bucket_of(central, bb[i].center, axis);
+            regions[idx].count += 1;
+            regions[idx].bounds = regions[idx].bounds.join(bb[i].bounds);
+        }
+        float cost[kRegions - 1];
+        for (int i = 0; i < kRegions - 1; ++i) {
+            int c0 = 0, c1 = 0;
+            Box a0, a1;
+            for (int j = 0; j < i; ++j) { c0 += regions[j].count; a0 = a0.join(regions[j].bounds); }
+            for (int j = i + 1; j < kRegions; ++j) { c1 += regions[j].count; a1 = a1.join(regions[j].bounds); }   // bucket i is in neither (sic)
+            cost[i] = 1.0f * (c0 * a0.area() + c1 * a1.area()) / bounds.area();
+        }
+        float min_cost = FLT_MAX;
+        int split = 0;
+        for (int i = 0; i < kRegions - 1; ++i)
+            if (cost[i] < min_cost) { min_cost = cost[i]; split = i; }
+        if (min_cost >= n_tris && n_tris <= kMaxAreas) return make_leaf(bb, ordered, tris, start, end, bounds, node);
+
+        // std::partition (libstdc++, bidirectional algorithm) with the predicate bucket <= split
+        auto pred = [&](const BoxRef& b) { return bucket_of(central, b.center, axis) <= split; };
+        int first = start, last = end;
+        while (true) {
+            while (true) {
+                if (first == last) goto done;
+                if (pred(bb[first])) ++first; else break;
+            }
+            --last;
+            while (true) {
+                if (first == last) goto done;
+                if (!pred(bb[last])) --last; else break;
+            }
+            std::swap(bb[first], bb[last]);
+            ++first;
+        }
+    done:
+        mid = first;
+        if (mid == start || mid == end)
+            throw std::runtime_error("BVH build: degenerate split (the reference recurses without end here)");
+    }
+    node->axis = axis;
+    // BVH_tree.cpp:68-71,130-133 makes both recursive calls as arguments of one function call; the
+    // order is unspecified in C++ and g++ (the compiler of the reference build the goldens come
+    // from) evaluates the RIGHT one first.  It only affects the order of the leaf triangles.
+    node->r = build(bb, ordered, tris, mid, end, n_nodes);
+    node->l = build(bb, ordered, tris, start, mid, n_nodes);
+    node->bbox = node->l->bbox.join(node->r->bbox);
+    node->sub_areas = 0;
+    return node;
+}
+
+int flatten(const Node* node, std::vector<b200pt_bvh_node>& out, int& offset)
+{
+    b200pt_bvh_node& t = out[(size_t)offset];
+    t.min_corner[0] = node->bbox.lo.x; t.min_corner[1] = node->bbox.lo.y; t.min_corner[2] = node->bbox.lo.z;
+    t.max_corner[0] = node->bbox.hi.x; t.max_corner[1] = node->bbox.hi.y; t.max_corner[2] = node->bbox.hi.z;
+    const int mine = offset++;
+    if (node->sub_areas > 0) {
+        t.first_area_idx = node->first;
+        t.sub_areas = node->sub_areas;
+        return mine;
+    }
+    t.sub_areas = 0;
+    t.axis = node->axis;
+    flatten(node->l, out, offset);
+    const int r = flatten(node->r, out, offset);
+    out[(size_t)mine].rchild_idx = r;
+    return mine;
+}
+
+void destroy(Node* n)
+{
+    if (!n) return;
+    destroy(n->l);
+    destroy(n->r);
+    delete n;
+}
+
+}  // namespace
+
+std::vector<b200pt_bvh_node> build_bvh_tree(std::vector<b200pt_triangle>& triangles)
+{
+    std::vector<b200pt_bvh_node> flat;
+    if (triangles.empty()) return flat;
+    std::vector<BoxRef> bb(triangles.size());
+    for (size_t i = 0; i < triangles.size(); ++i) {
+        const b200pt_triangle& t = triangles[i];
+        Box b;                                            // Triangle::getBoundingBox
+        b.lo = {fmin_glm(fmin_glm(t.vertices[0][0], t.vertices[1][0]), t.vertices[2][0]),
+                fmin_glm(fmin_glm(t.vertices[0][1], t.vertices[1][1]), t.vertices[2][1]),
+                fmin_glm(fmin_glm(t.vertices[0][2], t.vertices[1][2]), t.vertices[2][2])};
+        b.hi = {fmax_glm(fmax_glm(t.vertices[0][0], t.vertices[1][0]), t.vertices[2][0]),
+                fmax_glm(fmax_glm(t.vertices[0][1], t.vertices[1][1]), t.vertices[2][1]),
+                fmax_glm(fmax_glm(t.vertices[0][2], t.vertices[1][2]), t.vertices[2][2])};
+        bb[i].index = (int)i;
+        bb[i].bounds = b;
+        bb[i].center = 0.5f * (b.lo + b.hi);
+    }
+    std::vector<b200pt_triangle> ordered;
+    ordered.reserve(triangles.size());
+    int n_nodes = 0;
+    Node* root = build(bb, ordered, triangles, 0, (int)triangles.size(), n_nodes);
+    triangles.swap(ordered);
+    flat.assign((size_t)n_nodes, b200pt_bvh_node{});
+    int offset = 0;
+    flatten(root, flat, offset);
+    destroy(root);
+    return flat;
+}
+
+// =====================================================================================================
+// textures
+// =====================================================================================================
+TextureImage load_texture(const std::string& path)
+{
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("Texture load error! (cannot open " + path + ")");
+    std::stringstream buf;
+    buf << in.rdbuf();
+    const std::string raw = buf.str();
+    if (raw.size() < 2 || raw[0] != 'P' || (raw[1] != '5' && raw[1] != '6'))
+        throw std::runtime_error("Texture load error! (" + path + ": only binary PPM/PGM textures are decoded here; "
+                                 "convert other formats, e.g. JPEG, to .ppm)");
+    size_t at = 2;
+    auto next_int = [&]() {
+        while (at < raw.size()) {                          // white space and '#' comments
+            if (raw[at] == '#') { while (at < raw.size() && raw[at] != '\n' && raw[at] != '\r') ++at; }
+            else if (raw[at] == ' ' || raw[at] == '\t' || raw[at] == '\n' || raw[at] == '\r' || raw[at] == '\f' || raw[at] == '\v') ++at;
+            else break;
+        }
+        int v = 0;
+        bool any = false;
+        while (at < raw.size() && is_digit(raw[at])) { v = v * 10 + (raw[at] - '0'); ++at; any = true; }
+        if (!any) throw std::runtime_error("Texture load error! (" + path + ": bad PNM header)");
+        return v;
+    };
+    TextureImage t;
+    t.components = raw[1] == '6' ? 3 : 1;
+    t.width = next_int();
+    t.height = next_int();
+    const int maxv = next_int();
+    if (maxv > 255) throw std::runtime_error("Texture load error! (" + path + ": 16-bit PNM is not supported)");
+    ++at;                                                  // the single white-space byte after maxval
+    const size_t bytes = (size_t)t.width * t.height * t.components;
+    if (t.width <= 0 || t.height <= 0 || at + bytes > raw.size()) throw std::runtime_error("Texture load error! (" + path + ": truncated)");
+    t.pixels.assign(raw.begin() + (long)at, raw.begin() + (long)(at + bytes));
+    return t;
+}
+
+}  // namespace b200host

@@ -57,6 +57,9 @@ void Scene::loadFromJSON(const std::string& jsonName)
     std::stringstream buf;
     buf << f.rdbuf();
     const Json data = Json::parse(buf.str());
+    // scene.cpp:37: Models/ and Textures/ live next to the scene file
+    const size_t slash = jsonName.find_last_of("/\\");
+    const std::string dir = slash == std::string::npos ? std::string(".") : jsonName.substr(0, slash);
 
     // ---- Materials (scene.cpp:39-72): ids in the alphabetical order of the names -----------------
     std::map<std::string, int> id_of;
@@ -73,8 +76,11 @@ void Scene::loadFromJSON(const std::string& jsonName)
         store(m.color, col);
         store(m.specular_color, spec);
         m.texture_id = -1;
-        if (!p.value("TEXTURE_FILE", std::string()).empty())
-            throw std::runtime_error("material \"" + item.first + "\": TEXTURE_FILE is not supported yet");
+        const std::string tex = p.value("TEXTURE_FILE", std::string());
+        if (!tex.empty()) {                                               // scene.cpp:59-69
+            m.texture_id = (int)textures.size();
+            textures.push_back(load_texture(dir + "/Textures/" + tex));
+        }
         // extension keys (ignored by the reference's loader)
         m.hasRefractive = p.value("REFRACTIVE", 0.0f);
         m.indexOfRefraction = p.value("IOR", 0.0f);
@@ -84,6 +90,7 @@ void Scene::loadFromJSON(const std::string& jsonName)
     }
 
     // ---- Objects (scene.cpp:75-175) ------------------------------------------------------------------
+    int n_meshes = 0;
     for (const Json& p : data.at("Objects").arr) {
         b200pt_geom g;
         std::memset(&g, 0, sizeof(g));
@@ -104,7 +111,13 @@ void Scene::loadFromJSON(const std::string& jsonName)
         const std::string& type = p.at("TYPE").as_string();
         if (type == "cube") g.type = B200PT_CUBE;
         else if (type == "sphere") g.type = B200PT_SPHERE;
-        else if (type == "mesh") throw std::runtime_error("object TYPE \"mesh\" is not supported yet");
+        else if (type == "mesh") {                                        // scene.cpp:94-173
+            g.type = B200PT_MESH;
+            g.tri_start_idx = (int)triangles.size();
+            g.boundingbox_idx = n_meshes++;
+            load_obj_mesh(dir + "/Models/" + p.at("OBJ_FILE").as_string(), xf, it_, triangles, g.min_bound, g.max_bound);
+            g.tri_end_idx = (int)triangles.size();
+        }
         else throw std::runtime_error("unknown object TYPE \"" + type + "\"");
         geoms.push_back(g);
     }
@@ -135,6 +148,7 @@ void Scene::loadFromJSON(const std::string& jsonName)
     cam.pixelLength[1] = 2 * yscaled / (float)cam.resolution[1];
     store(cam.view, normalize(look - pos));
     state.image.assign(3 * (size_t)cam.resolution[0] * cam.resolution[1], 0.0f);
+    bvh_tree = build_bvh_tree(triangles);                                 // scene.cpp:218
 }
 
 void Scene::applyInteractiveCameraSetup()
@@ -172,16 +186,42 @@ b200pt_scene Scene::pod() const
     return s;
 }
 
+b200pt_scene_ext Scene::pod_ext() const
+{
+    texture_views_.clear();
+    for (const TextureImage& t : textures) texture_views_.push_back({t.width, t.height, t.components, t.pixels.data()});
+    b200pt_scene_ext e;
+    e.n_triangles = (int)triangles.size();
+    e.triangles = triangles.data();
+    e.n_bvh_nodes = (int)bvh_tree.size();
+    e.bvh = bvh_tree.data();
+    e.n_textures = (int)texture_views_.size();
+    e.textures = texture_views_.data();
+    return e;
+}
+
 void Scene::dump(const std::string& path) const
 {
     FILE* f = std::fopen(path.c_str(), "wb");
     if (!f) throw std::runtime_error("cannot write " + path);
     const int hdr[4] = {(int)geoms.size(), (int)materials.size(), state.traceDepth, (int)state.iterations};
-    std::fwrite("B2PTSCN1", 1, 8, f);
+    const bool v2 = !triangles.empty() || !textures.empty();
+    std::fwrite(v2 ? "B2PTSCN2" : "B2PTSCN1", 1, 8, f);
     std::fwrite(hdr, sizeof(int), 4, f);
     std::fwrite(&state.camera, sizeof(b200pt_camera), 1, f);
     std::fwrite(geoms.data(), sizeof(b200pt_geom), geoms.size(), f);
     std::fwrite(materials.data(), sizeof(b200pt_material), materials.size(), f);
+    if (v2) {
+        const int ext[4] = {(int)triangles.size(), (int)bvh_tree.size(), (int)textures.size(), 0};
+        std::fwrite(ext, sizeof(int), 4, f);
+        std::fwrite(triangles.data(), sizeof(b200pt_triangle), triangles.size(), f);
+        std::fwrite(bvh_tree.data(), sizeof(b200pt_bvh_node), bvh_tree.size(), f);
+        for (const TextureImage& t : textures) {
+            const int th[4] = {t.width, t.height, t.components, 0};
+            std::fwrite(th, sizeof(int), 4, f);
+            std::fwrite(t.pixels.data(), 1, t.pixels.size(), f);
+        }
+    }
     std::fclose(f);
 }
 

@@ -270,6 +270,65 @@ def write(name, scene):
         f.write("\n")
 
 
+def stress_assets():
+    """OBJ files that exercise the loader rather than the renderer: polygons of 3-6 corners (fan
+    triangulation), negative (relative) indices, floats with exponents / explicit signs / 17
+    significant digits (tinyobjloader's own decimal parser differs from strtod in the last place),
+    doubled blanks, g/s/usemtl/comment lines, clustered and grid-snapped vertices (many equal
+    centroids and bucket ties for the BVH build)."""
+    import random
+    rnd = random.Random(7)
+
+    def fmt(x):
+        r = rnd.random()
+        if r < 0.3:
+            return "%.17g" % x
+        if r < 0.5:
+            return "%.9e" % x
+        if r < 0.6:
+            return "%+.4f" % x
+        if r < 0.7:
+            return "%.12f" % x
+        return repr(float(x))
+
+    for name, n in (("stress_cloud", 260), ("stress_grid", 140), ("stress_few", 9)):
+        lines, nv = [], 0
+        for i in range(n):
+            cx, cy, cz = [rnd.choice([0, 0, 1, -1, .5]) * rnd.random() * 2 for _ in range(3)]
+            k = rnd.choice([3, 3, 3, 4, 5, 6])
+            for j in range(k):
+                if name == "stress_grid":
+                    lines.append("v %s %s %s" % (fmt(round(cx * 4) / 4 + (j % 2) * 0.25), fmt(round(cy * 4) / 4 + (j // 2) * 0.25),
+                                                 fmt(round(cz * 4) / 4)))
+                else:
+                    lines.append("v %s %s %s" % (fmt(cx + rnd.uniform(-.1, .1)), fmt(cy + rnd.uniform(-.1, .1)),
+                                                 fmt(cz + rnd.uniform(-.1, .1))))
+                lines.append("vt %s %s" % (fmt(rnd.random()), fmt(rnd.random())))
+                lines.append("vn %s %s %s" % (fmt(rnd.uniform(-1, 1)), fmt(rnd.uniform(-1, 1)), fmt(rnd.uniform(-1, 1))))
+            if rnd.random() < 0.5:
+                lines.append("f " + " ".join("%d/%d/%d" % ((nv + j + 1,) * 3) for j in range(k)))
+            else:
+                lines.append("f " + "  ".join("%d/%d/%d" % ((j - k,) * 3) for j in range(k)))
+            nv += k
+            if i % 50 == 0:
+                lines += ["g grp%d" % i, "# comment", "s off", "usemtl foo"]
+        with open(os.path.join(HERE, "Models", name + ".obj"), "w") as f:
+            f.write("\n".join(lines) + "\n")
+
+
+def mesh_stress():
+    sc = mesh_room((96, 96), 4, 8, "mesh_stress")
+    objs = [o for o in sc["Objects"] if o["TYPE"] != "mesh"]
+    proto = [o for o in sc["Objects"] if o["TYPE"] == "mesh"][0]
+    for nm, t, r, s_ in (("stress_cloud", [0, 5, 0], [10, 20, 30], [1.5, 1, 2]), ("stress_few", [1, 2, 3], [0, 0, 0], [1, 1, 1]),
+                         ("stress_grid", [-2, 4, 1], [45, 0, 90], [2, 2, 2]), ("stress_few", [0, 0, 0], [0, 90, 0], [3, .1, 3])):
+        o = dict(proto)
+        o.update(OBJ_FILE=nm + ".obj", TRANS=t, ROTAT=r, SCALE=s_)
+        objs.append(o)
+    sc["Objects"] = objs
+    return sc
+
+
 def main():
     write("cornell.json", cornell((800, 800), 5000, 8, "cornell", False))
     write("cornell_mirror.json", cornell((800, 800), 5000, 8, "cornell_mirror", True))
@@ -283,6 +342,8 @@ def main():
     mesh_assets()
     write("mesh_room.json", mesh_room((1200, 1200), 2000, 8, "mesh_room"))
     write("mesh_room_small.json", mesh_room((160, 160), 32, 8, "mesh_room_small"))
+    stress_assets()
+    write("mesh_stress.json", mesh_stress())
 
 
 if __name__ == "__main__":

@@ -29,6 +29,7 @@ SCENES = {
     "synthetic_600_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
     "mesh_room_small": [],
     "mesh_room": [],
+    "mesh_stress": [],      # loader / BVH-builder stress (scenes/make_scenes.py stress_assets)
     "synthetic_4096": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
 }
 # (scene, iterations, extra renderer flags, tag)

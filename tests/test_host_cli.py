@@ -21,7 +21,8 @@ from pt_cases import GOLD, bits_equal, ref_sum
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
 SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
-          "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096"]
+          "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096",
+          "mesh_room", "mesh_room_small", "mesh_stress"]   # OBJ meshes + BVH + textures ("B2PTSCN2")
 
 
 def scene_path(name):
@@ -115,7 +116,10 @@ def test_png_writer_pixels(tmp_path):
 # ---- on a B200 ---------------------------------------------------------------------------------------
 @pytest.mark.gpu
 @pytest.mark.parametrize("scene,iters,flags,tag", [("cornell_small", 16, [], "default"),
-                                                    ("cornell_glass_small", 16, ["--sort"], "sort")])
+                                                    ("cornell_glass_small", 16, ["--sort"], "sort"),
+                                                    # OBJ + BVH + textures through the C++ loader
+                                                    ("mesh_room_small", 8, [], "default"),
+                                                    ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain")])
 def test_cli_render_matches_reference_cuda_build(tmp_path, scene, iters, flags, tag):
     sum_out, base = str(tmp_path / "sum.bin"), str(tmp_path / "out")
     subprocess.run([EXE, scene_path(scene), "--iters", str(iters), "--batch", "1", "--sum-out", sum_out,

@@ -256,7 +256,12 @@ def test_reference_shaped_api(pt, torch):
 def test_errors_are_returned_not_fatal(pt):
     from cuda_pathtracer_b200 import B200Error
     sc = load_scene("cornell_tiny")
-    sc.geoms[0].type = 2                                 # MESH: not supported yet -> error code
+    sc.geoms[0].type = 2                                 # MESH whose triangle range is not in the scene
+    sc.geoms[0].tri_end_idx = 5
+    with pytest.raises(B200Error):
+        pt.Renderer(sc)
+    sc = load_scene("cornell_tiny")
+    sc.geoms[0].type = 7                                 # unknown GeomType
     with pytest.raises(B200Error):
         pt.Renderer(sc)
     sc = load_scene("cornell_tiny")
