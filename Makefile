@@ -13,7 +13,7 @@ SC_HDRS := $(CSRC)/sc_kernels.cuh $(CSRC)/sc_tmpl.cuh $(CSRC)/lookback.cuh inclu
 .PHONY: all lib host oracle clean
 all: lib host oracle
 
-PT_SRCS := $(CSRC)/pt_kernels.cu $(CSRC)/pt_api.cu
+PT_SRCS := $(CSRC)/pt_kernels.cu $(CSRC)/pt_api.cu $(CSRC)/pt_gbvh.cu
 PT_HDRS := $(CSRC)/pt_kernels.cuh $(CSRC)/pt_math.cuh $(CSRC)/pt_shade.cuh $(CSRC)/lookback.cuh include/b200_pt.h
 
 lib: $(PKG)/libb200sc.so $(PKG)/libb200pt.so

@@ -1,0 +1,22 @@
+#!/bin/bash
+# Profiling pass of one round (run on the GPU box through gpurun; one GPU):
+#   bash benchmarks/profile_round.sh r2
+# 1. the program first runs WITHOUT ncu (must exit 0),
+# 2. launch list of the same command (per-launch gpu__time_duration; cold-cache, serialised),
+# 3. one `--set full` capture each of the top kernels: k_bounce (path tracer), the single-pass scan and compact.
+# Outputs land in gpurun_out/; the summaries to be judged are copied into profiles/ by hand.
+tag=${1:-rX}
+out=gpurun_out
+mkdir -p $out
+cmd="python bench.py --steps 2 --warmup 1 --cpu-iters 1 --ref-cuda-iters 1"
+$cmd > $out/${tag}_prof_plain.json 2> $out/${tag}_prof_plain.err || { echo "plain run failed"; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \
+    $cmd > $out/${tag}_ncu_launches.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 8 -c 4 -f -o $out/${tag}_k_bounce \
+    python bench.py --steps 1 --warmup 1 --skip-extras > $out/${tag}_ncu_bounce.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:k_scan_lookback|k_compact' -s 2 -c 2 -f -o $out/${tag}_k_scan \
+    $cmd > $out/${tag}_ncu_scan.log 2>&1
+for k in k_bounce k_scan; do
+  ncu -i $out/${tag}_${k}.ncu-rep --page raw --csv > $out/${tag}_${k}_raw.csv 2>/dev/null
+done
+ls -la $out | grep ${tag}_

@@ -7,9 +7,11 @@
 // exit at once).  Several iterations are traced concurrently as independent batch slots of the
 // same launches (each slot compacts in its own index space, so the per-(iteration, slot-index,
 // depth) seeds -- and therefore the random paths -- are exactly the reference's).
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200_pt.h"
@@ -55,6 +57,17 @@ struct b200pt {
     TexRec* d_tex = nullptr;
     unsigned char* d_texels = nullptr;
     MeshScene mesh{};
+    // geometry BVH over the sphere / cube primitives (pt_gbvh.cu); rebuilt whenever the primitives change
+    float4* d_gnodes = nullptr;
+    float4* d_gboxes = nullptr;
+    PrimRec* d_gprims = nullptr;
+    int* d_gmesh = nullptr;
+    size_t gnodes_cap = 0, gboxes_cap = 0, gprims_cap = 0, gmesh_cap = 0;
+    GeomBvh gb{};
+    int n_indexed = 0;                 // sphere / cube primitives in the tree
+    std::vector<float4> host_gnodes, host_gboxes;
+    std::vector<PrimRec> host_gprims;
+    std::vector<int> host_gmesh;
     unsigned epoch = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     uint64_t iterations = 0, launches = 0;
@@ -127,6 +140,57 @@ int ensure_batch(b200pt* h, int batch)
 }
 
 int upload_meshes(b200pt* h, const b200pt_scene_ext* ext);
+
+int grow_buffer(void** p, size_t* cap, size_t bytes)
+{
+    if (bytes <= *cap) return 0;
+    cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    int r = dev_alloc(p, bytes);
+    if (!r) *cap = bytes;
+    return r;
+}
+
+// (re)build the geometry BVH of the packed primitives and upload it on stream s
+int upload_geom_bvh(b200pt* h, const b200pt_scene* sc, const std::vector<PrimRec>& prims, cudaStream_t s)
+{
+    const double cam[3] = {sc->camera.position[0], sc->camera.position[1], sc->camera.position[2]};
+    double mlo[3] = {0, 0, 0}, mhi[3] = {0, 0, 0};
+    bool have = false;
+    for (int i = 0; i < sc->n_geoms; ++i) {
+        const b200pt_geom& g = sc->geoms[i];
+        if (g.type != B200PT_MESH || g.tri_end_idx <= g.tri_start_idx) continue;
+        for (int a = 0; a < 3; ++a) {
+            // (max_bound starts at FLT_MIN in the reference's loader, scene.cpp:115: may exceed the true maximum)
+            const double lo = std::min((double)g.min_bound[a], (double)g.max_bound[a]), hi = std::max((double)g.min_bound[a], (double)g.max_bound[a]);
+            mlo[a] = have ? std::min(mlo[a], lo) : lo;
+            mhi[a] = have ? std::max(mhi[a], hi) : hi;
+        }
+        have = true;
+    }
+    build_geom_bvh(prims, cam, mlo, mhi, have, h->host_gnodes, h->host_gprims, h->host_gboxes, h->host_gmesh);
+    h->gb = GeomBvh{};
+    h->n_indexed = (int)h->host_gprims.size();
+    if (h->host_gnodes.empty()) return 0;
+    int r = grow_buffer((void**)&h->d_gnodes, &h->gnodes_cap, sizeof(float4) * h->host_gnodes.size());
+    if (!r) r = grow_buffer((void**)&h->d_gprims, &h->gprims_cap, sizeof(PrimRec) * h->host_gprims.size());
+    if (!r) r = grow_buffer((void**)&h->d_gboxes, &h->gboxes_cap, sizeof(float4) * h->host_gboxes.size());
+    if (!r) r = grow_buffer((void**)&h->d_gmesh, &h->gmesh_cap, sizeof(int) * (h->host_gmesh.size() + 1));
+    if (r) return r;
+    CK(cudaMemcpyAsync(h->d_gnodes, h->host_gnodes.data(), sizeof(float4) * h->host_gnodes.size(), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_gprims, h->host_gprims.data(), sizeof(PrimRec) * h->host_gprims.size(), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_gboxes, h->host_gboxes.data(), sizeof(float4) * h->host_gboxes.size(), cudaMemcpyHostToDevice, s));
+    if (!h->host_gmesh.empty())
+        CK(cudaMemcpyAsync(h->d_gmesh, h->host_gmesh.data(), sizeof(int) * h->host_gmesh.size(), cudaMemcpyHostToDevice, s));
+    h->gb.nodes = h->d_gnodes;
+    h->gb.prims = h->d_gprims;
+    h->gb.boxes = h->d_gboxes;
+    h->gb.mesh_prims = h->d_gmesh;
+    h->gb.n_nodes = (int)(h->host_gnodes.size() / 4);
+    h->gb.n_smem_nodes = std::min(h->gb.n_nodes, PT_SMEM_GNODES);
+    h->gb.n_mesh_prims = (int)h->host_gmesh.size();
+    return 0;
+}
 
 int sort_bins(const b200pt* h) { return h->n_mats < 256 ? h->n_mats : 256; }
 int sort_passes(const b200pt* h)
@@ -316,6 +380,23 @@ int upload_meshes(b200pt* h, const b200pt_scene_ext* ext)
     h->mesh.n_tris = n_tris;
     h->mesh.n_tex = n_tex;
     h->mesh.n_smem_nodes = h->mesh.n_nodes < PT_SMEM_NODES ? h->mesh.n_nodes : PT_SMEM_NODES;
+    // depth of the tree (levels): below BVH_MAX_SEARCH_DEPTH the reference's 64-entry stack can never
+    // fill up, so its overflow behaviour is unreachable and the deferred / pruned walk is exact
+    int levels = 0;
+    if (h->mesh.n_nodes) {
+        std::vector<std::pair<int, int>> todo{{0, 1}};
+        while (!todo.empty()) {
+            const std::pair<int, int> at = todo.back();
+            todo.pop_back();
+            levels = std::max(levels, at.second);
+            if (levels > 4 * BVH_MAX_SEARCH_DEPTH) break;
+            const b200pt_bvh_node& nd = ext->bvh[at.first];
+            if (nd.sub_areas > 0) continue;
+            todo.push_back({at.first + 1, at.second + 1});
+            todo.push_back({nd.rchild_idx, at.second + 1});
+        }
+    }
+    h->mesh.literal_walk = levels >= BVH_MAX_SEARCH_DEPTH ? 1 : 0;
     return 0;
 }
 
@@ -334,6 +415,7 @@ void b200pt_default_options(b200pt_options* o)
     o->focal_len = 10.0f;
     o->first_bounce_cache = 0;
     o->batch = 0;
+    o->geom_bvh = 0;
 }
 
 int b200pt_create(const b200pt_scene* sc, b200pt** out) { return b200pt_create_ext(sc, nullptr, out); }
@@ -374,6 +456,8 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
     CK(cudaEventCreate(&h->ev1));
     r = b200pt_reset(h);
     if (!r && ext) r = upload_meshes(h, ext);
+    if (!r) r = upload_geom_bvh(h, sc, prims, nullptr);
+    if (!r && cudaStreamSynchronize(nullptr) != cudaSuccess) r = (int)cudaGetLastError();
     if (r) { b200pt_destroy(h); return r; }
     *out = h;
     return 0;
@@ -388,6 +472,7 @@ int b200pt_destroy(b200pt* h)
     cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
     cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv);
     cudaFree(h->d_nodes); cudaFree(h->d_tv); cudaFree(h->d_ta); cudaFree(h->d_tex); cudaFree(h->d_texels);
+    cudaFree(h->d_gnodes); cudaFree(h->d_gboxes); cudaFree(h->d_gprims); cudaFree(h->d_gmesh);
     b200_sc_ctx_destroy(h->sc);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -398,7 +483,7 @@ int b200pt_destroy(b200pt* h)
 
 int b200pt_set_options(b200pt* h, const b200pt_options* o)
 {
-    if (!h || !o || o->batch < 0 || o->batch > 64) return B200_E_BADARG;
+    if (!h || !o || o->batch < 0 || o->batch > 64 || o->geom_bvh < -1 || o->geom_bvh > 1) return B200_E_BADARG;
     // the cached first-bounce hits depend on the camera rays: any change of what shapes them drops the cache
     if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache)
         h->cache_valid = false;
@@ -437,6 +522,10 @@ int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
     cudaStream_t s = (cudaStream_t)stream;
     CK(cudaMemcpyAsync(h->d_prims, h->host_prims.data(), sizeof(PrimRec) * h->host_prims.size(), cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice, s));
+    {
+        const int r = upload_geom_bvh(h, sc, h->host_prims, s);
+        if (r) return r;
+    }
     CK(cudaStreamSynchronize(s));      // host_prims / caller memory may be reused on return
     pack_camera(sc->camera, h->cam);
     h->cache_valid = false;
@@ -476,6 +565,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.mats = h->d_mats;
     p.n_prims = h->n_prims;
     p.n_mats = h->n_mats;
+    if (h->gb.n_nodes > 0 && (h->opt.geom_bvh > 0 || (h->opt.geom_bvh == 0 && h->n_indexed >= PT_GBVH_AUTO))) p.gb = h->gb;
     p.cam = h->cam;
     p.opt.rr = h->opt.russian_roulette;
     p.opt.ssaa = h->opt.ssaa;

@@ -1,0 +1,212 @@
+// pt_gbvh.cu -- host-side build of the geometry BVH (GeomBvh, pt_kernels.cuh): an index over the
+// sphere / cube primitives of a scene.  The reference has no such structure -- computeIntersections
+// tests every Geom for every ray (pathtrace.cu:247-290) -- and nothing here changes WHICH hit is
+// found: the tree only prunes primitives the ray cannot touch, every candidate still goes through
+// the exact (bit-reproducing) intersection routines, and the winner is the minimum of (t, index).
+//
+// Why the boxes are padded.  The reference decides hit / miss in fp32 in the primitive's object
+// space, so it also reports hits for rays that pass just OUTSIDE the exact shape:
+//   * sphere (intersections.cu:60-115): radicand = dot(o,d)^2 - (dot(o,o) - r^2) cancels two numbers
+//     of size (D/s)^2 (D = distance ray origin -> centre, s = smallest scale), error of a few
+//     ulp((D/s)^2), i.e. the sphere appears up to ~ 4e-7 * D^2 / s larger in world space
+//     (0.006 for D = 70, s = 0.3);
+//   * cube: slab distances carry a few ulp(D/s) in object space, ~ 1e-6 * D in world space.
+// A primitive must be found whenever the reference would find it, so each world box is grown by
+// pad = 256 * eps * D_max (+ 32 * eps * D_max^2 / s_min for a sphere), eps = 2^-23, D_max = diagonal
+// of everything a ray can start from (all primitives, all meshes, the camera): an order of
+// magnitude or more above those errors.  tests/test_pt_gpu.py checks BVH on / off bit-identity on every scene, and
+// the 600-primitive golden render of the reference's CUDA build pins the BVH path directly.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "pt_kernels.cuh"
+
+namespace ptk {
+
+namespace {
+
+struct Box3 {
+    double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+    void grow(const double p[3]) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    void grow(const Box3& b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    double area() const
+    {
+        const double d[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]};
+        if (d[0] < 0) return 0.0;
+        return 2.0 * (d[0] * d[1] + d[0] * d[2] + d[1] * d[2]);
+    }
+};
+
+struct Ref {
+    int prim;
+    Box3 box;
+    double c[3];
+};
+
+struct Tmp {                       // build-time node
+    Box3 box;
+    int left = -1, right = -1;     // children (Tmp indices) or -1
+    int first = 0, count = 0;      // leaf range in the ordered refs
+};
+
+constexpr int kBins = 16;
+
+int build(std::vector<Tmp>& nodes, std::vector<Ref>& refs, int begin, int end, int depth)
+{
+    const int me = (int)nodes.size();
+    nodes.emplace_back();
+    Box3 box, cbox;
+    for (int i = begin; i < end; ++i) { box.grow(refs[i].box); cbox.grow(refs[i].c); }
+    nodes[me].box = box;
+    const int n = end - begin;
+    if (n <= PT_GBVH_LEAF) { nodes[me].first = begin; nodes[me].count = n; return me; }
+
+    int axis = 0;
+    for (int a = 1; a < 3; ++a) if (cbox.hi[a] - cbox.lo[a] > cbox.hi[axis] - cbox.lo[axis]) axis = a;
+    const double ext = cbox.hi[axis] - cbox.lo[axis];
+    int mid = -1;
+    if (ext > 0.0 && depth < 32) {                              // binned surface-area heuristic
+        Box3 bb[kBins];
+        int bc[kBins] = {0};
+        auto bin_of = [&](const Ref& r) { return std::min(kBins - 1, (int)(kBins * (r.c[axis] - cbox.lo[axis]) / ext)); };
+        for (int i = begin; i < end; ++i) { const int b = bin_of(refs[i]); bc[b]++; bb[b].grow(refs[i].box); }
+        double best = DBL_MAX;
+        int split = -1;
+        for (int s = 1; s < kBins; ++s) {
+            Box3 l, r;
+            int nl = 0, nr = 0;
+            for (int b = 0; b < s; ++b) if (bc[b]) { l.grow(bb[b]); nl += bc[b]; }
+            for (int b = s; b < kBins; ++b) if (bc[b]) { r.grow(bb[b]); nr += bc[b]; }
+            if (!nl || !nr) continue;
+            const double cost = nl * l.area() + nr * r.area();
+            if (cost < best) { best = cost; split = s; }
+        }
+        if (split > 0)
+            mid = (int)(std::partition(refs.begin() + begin, refs.begin() + end, [&](const Ref& r) { return bin_of(r) < split; }) -
+                        refs.begin());
+    }
+    if (mid <= begin || mid >= end) {                           // equal centroids / depth guard: median by index
+        mid = begin + n / 2;
+        if (ext > 0.0)
+            std::nth_element(refs.begin() + begin, refs.begin() + mid, refs.begin() + end,
+                             [&](const Ref& a, const Ref& b) { return a.c[axis] < b.c[axis]; });
+    }
+    const int l = build(nodes, refs, begin, mid, depth + 1);
+    const int r = build(nodes, refs, mid, end, depth + 1);
+    nodes[me].left = l;
+    nodes[me].right = r;
+    return me;
+}
+
+}  // namespace
+
+void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], const double mesh_lo[3], const double mesh_hi[3],
+                    bool have_mesh_bounds, std::vector<float4>& nodes_out, std::vector<PrimRec>& prims_out,
+                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out)
+{
+    nodes_out.clear(); prims_out.clear(); boxes_out.clear(); mesh_prims_out.clear();
+    const double eps = 1.1920928955078125e-7;
+    std::vector<Ref> refs;
+    std::vector<double> smin;
+    Box3 world;
+    world.grow(cam_pos);
+    if (have_mesh_bounds) { world.grow(mesh_lo); world.grow(mesh_hi); }
+    for (int i = 0; i < (int)prims.size(); ++i) {
+        const PrimRec& g = prims[i];
+        if (g.type == 2) { mesh_prims_out.push_back(i); continue; }
+        Ref r;
+        r.prim = i;
+        for (int k = 0; k < 8; ++k) {                            // the unit cube bounds the r = 0.5 sphere too
+            const double u[3] = {k & 1 ? 0.5 : -0.5, k & 2 ? 0.5 : -0.5, k & 4 ? 0.5 : -0.5};
+            double w[3];
+            for (int row = 0; row < 3; ++row)
+                w[row] = (double)g.fwd[0 * 3 + row] * u[0] + (double)g.fwd[1 * 3 + row] * u[1] + (double)g.fwd[2 * 3 + row] * u[2] +
+                         (double)g.fwd[3 * 3 + row];
+            r.box.grow(w);
+        }
+        double s = DBL_MAX;                                      // smallest column norm of the linear part = smallest scale
+        for (int c = 0; c < 3; ++c)
+            s = std::min(s, std::sqrt((double)g.fwd[c * 3] * g.fwd[c * 3] + (double)g.fwd[c * 3 + 1] * g.fwd[c * 3 + 1] +
+                                      (double)g.fwd[c * 3 + 2] * g.fwd[c * 3 + 2]));
+        smin.push_back(s);
+        world.grow(r.box);
+        refs.push_back(r);
+    }
+    if (refs.empty()) return;
+    double diag2 = 0.0;
+    for (int a = 0; a < 3; ++a) diag2 += (world.hi[a] - world.lo[a]) * (world.hi[a] - world.lo[a]);
+    const double dmax = std::sqrt(diag2) * 1.05 + 1.0;           // + lens offsets / the 1e-4 surface offsets
+    for (size_t i = 0; i < refs.size(); ++i) {
+        double pad = 256.0 * eps * dmax;
+        if (prims[(size_t)refs[i].prim].type == 0) pad += smin[i] > 0.0 ? 32.0 * eps * dmax * dmax / smin[i] : dmax;   // sphere
+        if (!(pad < dmax)) pad = dmax;                           // degenerate scale: the box covers everything
+        for (int a = 0; a < 3; ++a) {
+            if (!std::isfinite(refs[i].box.lo[a]) || !std::isfinite(refs[i].box.hi[a])) { refs[i].box.lo[a] = -1e30; refs[i].box.hi[a] = 1e30; }
+            refs[i].box.lo[a] -= pad;
+            refs[i].box.hi[a] += pad;
+            refs[i].c[a] = 0.5 * (refs[i].box.lo[a] + refs[i].box.hi[a]);
+        }
+    }
+    std::vector<Tmp> tmp;
+    tmp.reserve(2 * refs.size());
+    build(tmp, refs, 0, (int)refs.size(), 0);
+
+    prims_out.resize(refs.size());
+    for (size_t i = 0; i < refs.size(); ++i) {
+        prims_out[i] = prims[(size_t)refs[i].prim];
+        prims_out[i].pad0 = refs[i].prim;                        // index in the scene's primitive array
+    }
+    // inner nodes in breadth-first order (the top levels first: they are the ones staged in shared memory)
+    std::vector<int> order, id_of(tmp.size(), -1);
+    if (tmp[0].left < 0) {                                       // a single leaf: give it a parent with two equal children
+        Tmp root;
+        root.box = tmp[0].box;
+        root.left = root.right = 0;
+        tmp.push_back(root);
+        order.push_back((int)tmp.size() - 1);
+        id_of.push_back(0);
+    } else {
+        order.push_back(0);
+        id_of[0] = 0;
+    }
+    for (size_t at = 0; at < order.size(); ++at) {
+        const Tmp& t = tmp[(size_t)order[at]];
+        for (int child : {t.left, t.right})
+            if (tmp[(size_t)child].left >= 0 && id_of[(size_t)child] < 0) { id_of[(size_t)child] = (int)order.size(); order.push_back(child); }
+    }
+    auto ref_of = [&](int child) {
+        const Tmp& c = tmp[(size_t)child];
+        return c.left >= 0 ? id_of[(size_t)child] : ~((c.first << 3) | (c.count - 1));
+    };
+    auto lo4 = [](const Box3& b, int w) {                        // round outwards
+        float4 q;
+        q.x = std::nextafterf((float)b.lo[0], -FLT_MAX); q.y = std::nextafterf((float)b.lo[1], -FLT_MAX);
+        q.z = std::nextafterf((float)b.lo[2], -FLT_MAX); std::memcpy(&q.w, &w, 4);
+        return q;
+    };
+    auto hi4 = [](const Box3& b, int w) {
+        float4 q;
+        q.x = std::nextafterf((float)b.hi[0], FLT_MAX); q.y = std::nextafterf((float)b.hi[1], FLT_MAX);
+        q.z = std::nextafterf((float)b.hi[2], FLT_MAX); std::memcpy(&q.w, &w, 4);
+        return q;
+    };
+    boxes_out.resize(2 * refs.size());
+    for (size_t i = 0; i < refs.size(); ++i) {
+        boxes_out[2 * i + 0] = lo4(refs[i].box, 0);
+        boxes_out[2 * i + 1] = hi4(refs[i].box, 0);
+    }
+    nodes_out.resize(4 * order.size());
+    for (size_t i = 0; i < order.size(); ++i) {
+        const Tmp& t = tmp[(size_t)order[i]];
+        const Tmp &l = tmp[(size_t)t.left], &r = tmp[(size_t)t.right];
+        nodes_out[4 * i + 0] = lo4(l.box, ref_of(t.left));
+        nodes_out[4 * i + 1] = hi4(l.box, ref_of(t.right));
+        nodes_out[4 * i + 2] = lo4(r.box, 0);
+        nodes_out[4 * i + 3] = hi4(r.box, 0);
+    }
+}
+
+}  // namespace ptk

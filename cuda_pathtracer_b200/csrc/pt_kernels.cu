@@ -91,6 +91,108 @@ __device__ __forceinline__ void closest_in_chunk(const PrimRec* __restrict__ sp,
     }
 }
 
+// conservative ray / box test of the geometry BVH: entry distance, or a negative value on a miss.
+// Not parity-critical (it only prunes), so plain fast arithmetic; fminf / fmaxf drop the NaNs of
+// 0 * inf, which makes a degenerate slab "no constraint".
+__device__ __forceinline__ float gbox_entry(const float4& lo, const float4& hi, const V3& o, const V3& inv, float t_lim)
+{
+    const float ax = (lo.x - o.x) * inv.x, bx = (hi.x - o.x) * inv.x;
+    const float ay = (lo.y - o.y) * inv.y, by = (hi.y - o.y) * inv.y;
+    const float az = (lo.z - o.z) * inv.z, bz = (hi.z - o.z) * inv.z;
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_lim));
+    return tn <= tf * 1.00001f + 1e-5f ? tn : -1.0f;
+}
+
+// closest hit among the sphere / cube primitives through the geometry BVH, then the MESH primitives.
+// Two alternating phases keep the warp converged although every thread walks its own way through
+// the tree: (1) traversal with box tests only -- the primitives of a reached leaf are tested
+// against their OWN boxes and the survivors appended to a per-thread candidate list, in roughly
+// near-to-far order; (2) the exact tests of the listed candidates, where a thread first skips the
+// candidates that start behind its current hit, so that every trip of the loop does real work in
+// every lane that is still busy.  (Testing leaves as they are met costs a full exact test per
+// trip as soon as ONE lane of the warp sits at a leaf.)
+constexpr int PT_GCAND = 32;       // candidate list capacity; drained when fewer than 16 slots are free
+
+__device__ __forceinline__ void closest_in_gbvh(const RenderParams& p, const float4* __restrict__ snodes_g, const V3& o,
+                                                const V3& d, const MeshHit& mh, float& t_min, int& hit, Cand& best,
+                                                int& owner)
+{
+    const V3 inv = v3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
+    int stack[64];
+    int cand_prim[PT_GCAND];
+    float cand_t[PT_GCAND];
+    int sp = 0, nc = 0, node = 0;
+    bool more = true;
+    while (more) {
+        // ---- phase 1: traverse, collect candidates ----
+        // the pruning distance trails the exact t_min by a margin far above the rounding of the box test
+        const float t_lim = fmaf(t_min, 1.0001f, 1e-4f);
+        while (true) {
+            const float4* q = node < p.gb.n_smem_nodes ? snodes_g + 4 * node : p.gb.nodes + 4 * (size_t)node;
+            const float4 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+            const float tl = gbox_entry(q0, q1, o, inv, t_lim), tr = gbox_entry(q2, q3, o, inv, t_lim);
+            int ref_near = __float_as_int(q0.w), ref_far = __float_as_int(q1.w);
+            bool near_ok = tl >= 0.0f, far_ok = tr >= 0.0f;
+            if (far_ok && (!near_ok || tr < tl)) {
+                const int r = ref_near; ref_near = ref_far; ref_far = r;
+                const bool b = near_ok; near_ok = far_ok; far_ok = b;
+            }
+            int next = -1;
+#pragma unroll
+            for (int side = 0; side < 2; ++side) {
+                const int ref = side == 0 ? ref_near : ref_far;
+                const bool ok = side == 0 ? near_ok : far_ok;
+                if (!ok) continue;
+                if (ref < 0) {
+                    const int v = ~ref, first = v >> 3, count = (v & 7) + 1;
+                    for (int k = 0; k < count; ++k) {
+                        const float te = gbox_entry(p.gb.boxes[2 * (first + k)], p.gb.boxes[2 * (first + k) + 1], o, inv, t_lim);
+                        if (te >= 0.0f) { cand_prim[nc] = first + k; cand_t[nc] = te; ++nc; }
+                    }
+                } else if (next < 0) {
+                    next = ref;
+                } else {
+                    stack[sp++] = ref;
+                }
+            }
+            if (next >= 0) node = next;
+            else if (sp > 0) node = stack[--sp];
+            else { more = false; break; }
+            if (nc > PT_GCAND - 16) break;
+        }
+        // ---- phase 2: exact tests of the candidates ----
+        int k = 0;
+        while (true) {
+            const float lim = fmaf(t_min, 1.0001f, 1e-4f);
+            while (k < nc && cand_t[k] > lim) ++k;
+            if (k >= nc) break;
+            const PrimRec& g = p.gb.prims[cand_prim[k]];
+            ++k;
+            const Cand c = prim_test(g, o, d);
+            const int gi = g.pad0;
+            // lexicographic minimum of (t, index): what the ascending loop with strict `<` finds
+            if (c.t > 0.0f && (t_min > c.t || (t_min == c.t && gi < hit))) {
+                t_min = c.t;
+                hit = gi;
+                best = c;
+            }
+        }
+        nc = 0;
+    }
+    for (int k = 0; k < p.gb.n_mesh_prims; ++k) {
+        const int gi = p.gb.mesh_prims[k];
+        const PrimRec& g = p.prims[gi];
+        if (mh.any && mh.id >= g.pad0 && mh.id < g.pad1) {
+            if (owner < 0) owner = gi;
+            if (mh.t > 0.0f && (t_min > mh.t || (t_min == mh.t && gi < hit))) {
+                t_min = mh.t;
+                hit = gi;
+            }
+        }
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
@@ -138,10 +240,21 @@ __device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
 }
 
 // producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
+// (with the geometry BVH: the top of that tree instead of primitive chunks)
 __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared& sh, MatRec* smats, int n_smem_mats,
                                             BvhRec* snodes, PrimRec* sprims, bool want_prims)
 {
     if (threadIdx.x != 0) return;
+    if (p.gb.n_nodes > 0) {
+        const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
+        const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
+        const unsigned g_bytes = want_prims ? (unsigned)(p.gb.n_smem_nodes * 4 * sizeof(float4)) : 0u;
+        mbar_expect_tx(&sh.bar[0], mat_bytes + node_bytes + g_bytes);
+        if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
+        if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &sh.bar[0]);
+        if (g_bytes) bulk_g2s(sprims, p.gb.nodes, g_bytes, &sh.bar[0]);
+        return;
+    }
     const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
     const int chunk_cap = n_chunks > 1 ? PT_CHUNK : p.n_prims;
     const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
@@ -160,20 +273,26 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared&
 
 // computeIntersections (pathtrace.cu:230-298) over the TMA-staged primitive chunks.  Every thread of
 // the CTA must call it (it contains the chunk barriers); inactive threads only take part in those.
+// GB: the sphere / cube primitives are searched through the geometry BVH (whose top levels lie
+// where the primitive chunks would) instead of the linear scan.
+template <bool GB>
 __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, BounceShared& sh, const BvhRec* snodes,
                                                      const PrimRec* sprims, bool active, const V3& o, const V3& d)
 {
-    const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
+    const int n_chunks = GB ? 0 : (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
     float t_min = 3.402823466e+38f;
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
     MeshHit mh = no_mesh_hit();
     int owner = -1;
-    if (p.mesh.n_nodes > 0) {                        // one BVH traversal serves every MESH primitive
-        mbar_wait(&sh.bar[0], 0u);                   // the staged top of the tree
-        if (active) mh = bvh_traverse(p.mesh, snodes, o, d);
-    }
+    if (GB || p.mesh.n_nodes > 0) mbar_wait(&sh.bar[0], 0u);     // the staged top(s) of the tree(s)
+    // A ray whose direction is NaN (glm::refract past the critical angle, interactions.cu:68) hits
+    // nothing in the reference: every t it computes is NaN and `t > 0` fails.  In a tree such a ray
+    // passes every box test (NaN compares false) and would visit all of it: skip the trees, same result.
+    const bool walk = active && d.x == d.x && d.y == d.y && d.z == d.z;
+    if (p.mesh.n_nodes > 0 && walk) mh = bvh_traverse(p.mesh, snodes, o, d);   // one traversal serves every MESH primitive
+    if (GB && walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, mh, t_min, hit, best, owner);
     for (int ch = 0; ch < n_chunks; ++ch) {
         mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
         const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
@@ -196,7 +315,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
     h.mat = 0;
     h.u = h.v = 0.0f;
     if (hit >= 0) {
-        const PrimRec& g = n_chunks > 1 ? p.prims[hit] : sprims[hit];
+        const PrimRec& g = (GB || n_chunks > 1) ? p.prims[hit] : sprims[hit];
         if (g.type == 2) {
             tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, h.n, h.u, h.v);
         } else {
@@ -279,7 +398,7 @@ __device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceS
 // k_bounce: the fused bounce.  CACHE (first-bounce cache, bounce 0 only, valid when the camera rays
 // do not change between iterations, i.e. SSAA and DoF off): 0 = off, 1 = trace and fill the cache
 // (slot 0 writes it), 2 = replace the closest-hit search by one 20-byte cache read per path.
-template <int CACHE>
+template <int CACHE, bool GB>
 __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -315,7 +434,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         h.u = cuv.x; h.v = cuv.y;
         mbar_wait(&sh.bar[0], 0u);                  // the materials
     } else {
-        h = closest_hit_staged(p, sh, snodes, sprims, active, s.o, s.d);
+        h = closest_hit_staged<GB>(p, sh, snodes, sprims, active, s.o, s.d);
         if (CACHE == 1 && slot == 0 && active) {
             p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             p.cache_k[idx] = h.mat;
@@ -330,6 +449,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
 // (thrust::sort_by_key on materialId, pathtrace.cu:410-414,479-491): k_isect writes the hit
 // records, k_sort_hist / (scan) / k_sort_scatter build the stable sorted order as a permutation
 // (LSD radix, 8 bits per pass, one pass for up to 256 materials), k_shade gathers through it.
+template <bool GB>
 __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -347,7 +467,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     const bool active = idx < n_live;
     const size_t at = (size_t)slot * p.P + (active ? idx : 0);
     const float4 a = p.in.a[at], b = p.in.b[at];
-    const HitRec h = closest_hit_staged(p, sh, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
+    const HitRec h = closest_hit_staged<GB>(p, sh, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
     if (active) {
         p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
         p.hit_k[at] = h.mat;
@@ -570,10 +690,11 @@ __global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
-size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes)
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes)
 {
     const int n_chunks = (n_prims + PT_CHUNK - 1) / PT_CHUNK;
-    const size_t prim_bytes = (size_t)(n_chunks > 1 ? 2 * PT_CHUNK : n_prims) * sizeof(PrimRec);
+    const size_t prim_bytes = n_gnodes ? (size_t)n_gnodes * 4 * sizeof(float4)
+                                       : (size_t)(n_chunks > 1 ? 2 * PT_CHUNK : n_prims) * sizeof(PrimRec);
     const size_t mat_bytes = (size_t)(n_mats <= PT_SMEM_MATS ? n_mats : 0) * sizeof(MatRec);
     const size_t node_bytes = (size_t)(n_nodes < PT_SMEM_NODES ? n_nodes : PT_SMEM_NODES) * sizeof(BvhRec);
     return sizeof(BounceShared) + mat_bytes + node_bytes + prim_bytes;
@@ -582,10 +703,13 @@ size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes)
 cudaError_t configure_kernels()
 {
     const int cap = (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS, PT_SMEM_NODES);
-    cudaError_t e = cudaFuncSetAttribute(k_bounce<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaError_t e = cudaFuncSetAttribute(k_bounce<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     return e;
 }
@@ -599,16 +723,21 @@ cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
 {
     const dim3 grid(p.tiles, p.batch);
-    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes);
-    if (p.cache_mode == 1) k_bounce<1><<<grid, PT_THREADS, smem, s>>>(p);
-    else if (p.cache_mode == 2) k_bounce<2><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
-    else k_bounce<0><<<grid, PT_THREADS, smem, s>>>(p);
+    const bool gb = p.gb.n_nodes > 0;
+    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes);
+    if (p.cache_mode == 2) k_bounce<2, false><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
+    else if (p.cache_mode == 1 && gb) k_bounce<1, true><<<grid, PT_THREADS, smem, s>>>(p);
+    else if (p.cache_mode == 1) k_bounce<1, false><<<grid, PT_THREADS, smem, s>>>(p);
+    else if (gb) k_bounce<0, true><<<grid, PT_THREADS, smem, s>>>(p);
+    else k_bounce<0, false><<<grid, PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
 {
-    k_isect<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes), s>>>(p);
+    const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes);
+    if (p.gb.n_nodes > 0) k_isect<true><<<dim3(p.tiles, p.batch), PT_THREADS, smem, s>>>(p);
+    else k_isect<false><<<dim3(p.tiles, p.batch), PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 

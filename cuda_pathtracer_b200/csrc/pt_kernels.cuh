@@ -2,6 +2,7 @@
 // C ABI of include/b200_pt.h).  Not part of the public boundary.
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include "pt_shade.cuh"
 
 namespace ptk {
@@ -10,6 +11,9 @@ constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
 constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
+constexpr int PT_SMEM_GNODES = 192;        // geometry-BVH nodes kept in shared memory (12 KB): breadth-first order => the top levels
+constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
+constexpr int PT_GBVH_AUTO = 32;           // geom_bvh = auto: use the BVH from this many sphere / cube primitives
 constexpr int PT_DESC_STRIDE = 16;         // 64-bit words between look-back descriptors: one 128-B line each
                                            // (packed descriptors make the lines around the prefix frontier an
                                            // L2 hot spot, see lookback.cuh)
@@ -22,6 +26,24 @@ struct Pool {
     float4* a;
     float4* b;
     float4* c;
+};
+
+// Geometry BVH: an index over the sphere / cube primitives that replaces the linear scan of
+// computeIntersections (pathtrace.cu:247-290) when the scene has many of them.  It only PRUNES:
+// every primitive whose (padded, see pt_api.cu) world box the ray may touch still goes through
+// the exact prim_test, and the winner is the lexicographic minimum of (t, index) -- the same hit
+// the reference's ascending loop with its strict `<` selects.
+//   node = 4 x float4: {lo_L, ref_L} {hi_L, ref_R} {lo_R, -} {hi_R, -}
+//   ref >= 0: inner node index; ref < 0: leaf, v = ~ref, first = v >> 3, count = (v & 7) + 1
+struct GeomBvh {
+    const float4* nodes;
+    const PrimRec* prims;              // copies in leaf order; pad0 = index in the scene's primitive array
+    const float4* boxes;               // padded world box of each of them: {lo, -} {hi, -}
+    const int* mesh_prims;             // indices of the MESH primitives, ascending
+    int n_nodes;                       // 0 = not in use (linear scan over the staged primitives)
+    int n_smem_nodes;
+    int n_mesh_prims;
+    int pad;
 };
 
 struct RenderParams {
@@ -55,9 +77,10 @@ struct RenderParams {
     float2* hit_uv;                    // [batch][P] hit record texture coordinate (mesh hits)
     float2* cache_uv;                  // [P]
     MeshScene mesh;                    // triangle meshes / BVH / textures (n_nodes == 0: none)
+    GeomBvh gb;
 };
 
-size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes);
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);           // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
@@ -73,5 +96,11 @@ cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, MeshScene 
 cudaError_t launch_debug_shade(const MatRec* mats, MeshScene mesh, OptRec opt, int iter, int n, const float* isects,
                                float* segments, cudaStream_t s);
 cudaError_t configure_kernels();
+
+// pt_gbvh.cu (host): nodes (4 float4 each, breadth first), the sphere / cube records in leaf order
+// (pad0 = scene index) with their padded boxes, and the indices of the MESH primitives.  Empty nodes_out: nothing to index.
+void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], const double mesh_lo[3], const double mesh_hi[3],
+                    bool have_mesh_bounds, std::vector<float4>& nodes_out, std::vector<PrimRec>& prims_out,
+                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out);
 
 }  // namespace ptk

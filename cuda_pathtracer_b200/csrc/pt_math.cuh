@@ -267,6 +267,8 @@ struct MeshScene {
     const TexRec* tex;
     const unsigned char* texels;
     int n_nodes, n_tris, n_tex, n_smem_nodes;
+    int literal_walk;    // the tree is >= BVH_MAX_SEARCH_DEPTH levels deep: keep the reference's stack-overflow behaviour
+    int pad_[3];
 };
 
 struct MeshHit {
@@ -281,14 +283,17 @@ struct MeshHit {
 __device__ __forceinline__ float gmin(float x, float y) { return x < y ? x : y; }
 __device__ __forceinline__ float gmax(float x, float y) { return x > y ? x : y; }
 
+// BoundingBox::intersect (boundingbox.h:74-92).  `entry` (only meaningful on a hit) is the slab
+// entry distance the test computes anyway.
 __device__ __forceinline__ bool bbox_hit(const float* __restrict__ lo, const float* __restrict__ hi, const V3& o,
-                                         const V3& inv)
+                                         const V3& inv, float& entry)
 {
     const float mx = __fmul_rn(__fsub_rn(lo[0], o.x), inv.x), Mx = __fmul_rn(__fsub_rn(hi[0], o.x), inv.x);
     const float my = __fmul_rn(__fsub_rn(lo[1], o.y), inv.y), My = __fmul_rn(__fsub_rn(hi[1], o.y), inv.y);
     const float mz = __fmul_rn(__fsub_rn(lo[2], o.z), inv.z), Mz = __fmul_rn(__fsub_rn(hi[2], o.z), inv.z);
     const float tmin = gmax(gmax(gmin(mx, Mx), gmin(my, My)), gmin(mz, Mz));
     const float tmax = gmin(gmin(gmax(mx, Mx), gmax(my, My)), gmax(mz, Mz));
+    entry = tmin;
     if (tmax < 0.0f) return false;
     if (tmin > tmax) return false;
     return true;
@@ -323,31 +328,36 @@ constexpr int BVH_MAX_SEARCH_DEPTH = 64;     // intersections.cu:177
 // (pathtrace.cu:262-272); the traversal itself does not depend on the geom, so it is done once.
 // snodes: the first M.n_smem_nodes nodes staged in shared memory (DFS order keeps the top of the
 // tree there).
-__device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec* __restrict__ snodes, const V3& o,
-                                                const V3& d)
+__device__ __forceinline__ void tri_candidate(const MeshScene& M, int at, const V3& o, const V3& d, MeshHit& h)
+{
+    float bx, by, bt;
+    if (tri_test(M.tv[at], o, d, bx, by, bt)) {
+        h.any = true;
+        if (h.t == -1.0f || bt < h.t) {      // strict: the first one met wins a tie
+            h.t = bt; h.tri = at; h.bx = bx; h.by = by;
+        }
+    }
+}
+
+// The reference's walk, literally: leaves are tested as they are met, no pruning by distance, and a
+// full stack silently drops the node at hand (intersections.cu:203-206).  Used for trees deep
+// enough (>= BVH_MAX_SEARCH_DEPTH levels) for that drop to be reachable.
+__device__ __forceinline__ MeshHit bvh_traverse_literal(const MeshScene& M, const BvhRec* __restrict__ snodes, const V3& o,
+                                                        const V3& d)
 {
     MeshHit h;
     h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
-    if (M.n_nodes == 0) return h;
     int to_visit[BVH_MAX_SEARCH_DEPTH];
     int sp = 0, cur = 0;
     const bool neg[3] = {d.x < 0.0f, d.y < 0.0f, d.z < 0.0f};
     const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     while (true) {
         const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
-        if (bbox_hit(nd.lo, nd.hi, o, inv)) {
+        float entry;
+        if (bbox_hit(nd.lo, nd.hi, o, inv, entry)) {
             const int n_leaf = nd.sub_areas;
             if (n_leaf > 0) {
-                const int first = nd.first;
-                for (int i = 0; i < n_leaf; ++i) {
-                    float bx, by, bt;
-                    if (tri_test(M.tv[first + i], o, d, bx, by, bt)) {
-                        h.any = true;
-                        if (h.t == -1.0f || bt < h.t) {
-                            h.t = bt; h.tri = first + i; h.bx = bx; h.by = by;
-                        }
-                    }
-                }
+                for (int i = 0; i < n_leaf; ++i) tri_candidate(M, nd.first + i, o, d, h);
                 if (sp == 0) break;
                 cur = to_visit[--sp];
             } else {
@@ -359,6 +369,67 @@ __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec
             if (sp == 0) break;
             cur = to_visit[--sp];
         }
+    }
+    if (h.tri >= 0) h.id = M.tv[h.tri].id;
+    return h;
+}
+
+// Same result, arranged for the SIMT machine.  The reference's walk visits the same nodes in the
+// same order whatever it has hit so far, and keeps the nearest triangle, the first one met on a
+// tie.  So (1) the triangle tests of the leaves can be deferred: the walk only runs the (exact)
+// box tests and lists the leaves it reaches, then the listed triangles are tested in the order
+// met -- one triangle per lane per trip, instead of a whole leaf whenever ANY lane of the warp
+// stands at one; (2) a node or leaf whose box starts behind the current hit (with a margin far
+// above the rounding of the slab distances) cannot hold a nearer or equal one and is skipped.
+constexpr int PT_MLEAVES = 12;      // listed leaves before the list is worked off
+
+// a distance safely beyond t (t may be negative: glm::intersectRayTriangle also reports hits behind the origin)
+__device__ __forceinline__ float prune_limit(float t) { return fmaf(fabsf(t), 1e-4f, t) + 1e-4f; }
+
+__device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec* __restrict__ snodes, const V3& o,
+                                                const V3& d)
+{
+    MeshHit h;
+    h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
+    if (M.n_nodes == 0) return h;
+    if (M.literal_walk) return bvh_traverse_literal(M, snodes, o, d);
+    int to_visit[BVH_MAX_SEARCH_DEPTH];
+    int leaf_first[PT_MLEAVES], leaf_count[PT_MLEAVES];
+    float leaf_entry[PT_MLEAVES];
+    int sp = 0, cur = 0, nl = 0;
+    const bool neg[3] = {d.x < 0.0f, d.y < 0.0f, d.z < 0.0f};
+    const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    bool more = true;
+    while (more) {
+        const float lim = prune_limit(h.t);
+        while (true) {                                   // the walk: box tests only
+            const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
+            float entry;
+            bool descend = false;
+            if (bbox_hit(nd.lo, nd.hi, o, inv, entry) && !(entry > lim)) {
+                if (nd.sub_areas > 0) {
+                    leaf_first[nl] = nd.first; leaf_count[nl] = nd.sub_areas; leaf_entry[nl] = entry; ++nl;
+                } else {
+                    descend = true;
+                    if (neg[nd.axis]) { to_visit[sp++] = cur + 1; cur = nd.rchild; }
+                    else { to_visit[sp++] = nd.rchild; cur = cur + 1; }
+                }
+            }
+            if (!descend) {
+                if (sp == 0) { more = false; break; }
+                cur = to_visit[--sp];
+            }
+            if (nl == PT_MLEAVES) break;
+        }
+        int k = 0, i = 0;                                // the listed triangles, in the order met
+        while (true) {
+            const float lim2 = prune_limit(h.t);
+            while (k < nl && (i >= leaf_count[k] || leaf_entry[k] > lim2)) { ++k; i = 0; }
+            if (k >= nl) break;
+            tri_candidate(M, leaf_first[k] + i, o, d, h);
+            ++i;
+        }
+        nl = 0;
     }
     if (h.tri >= 0) h.id = M.tv[h.tri].id;
     return h;

@@ -15,6 +15,8 @@
 //   --no-ssaa            SSAA = false                     --no-dof      DoF = false
 //   --aperture A         (default 0.1)                    --focal F     focal_len (default 10.0)
 //   --first-bounce-cache reuse bounce 0's hits (honoured only with --no-ssaa --no-dof)
+//   --geom-bvh on|off|auto   closest hit over spheres / cubes through a BVH instead of the linear scan
+//                        (same image either way; auto = on from 32 primitives)
 //   --batch B            iterations in flight (0 = library default, 1 = the reference's exact
 //                        accumulation order: bit-identical float SUM image)
 //   --iter-first F --iter-stride S   trace iterations F, F+S, ... (N of them): the multi-GPU split
@@ -114,6 +116,13 @@ int main(int argc, char** argv)
         else if (a == "--focal") opt.focal_len = (float)std::atof(next());
         else if (a == "--first-bounce-cache") opt.first_bounce_cache = 1;
         else if (a == "--batch") opt.batch = std::atoi(next());
+        else if (a == "--geom-bvh") {
+            const std::string v = next();
+            if (v == "on") opt.geom_bvh = 1;
+            else if (v == "off") opt.geom_bvh = -1;
+            else if (v == "auto") opt.geom_bvh = 0;
+            else { usage(argv[0]); return 1; }
+        }
         else if (a == "--iter-first") { iter_first = std::atoi(next()); iter_first_given = true; }
         else if (a == "--resume-sum") resume_sum = next();
         else if (a == "--samples-done") samples_done = std::atoi(next());

@@ -77,7 +77,7 @@ class _OptionsC(ctypes.Structure):
     _fields_ = [("russian_roulette", ctypes.c_int32), ("sort_by_material", ctypes.c_int32),
                 ("ssaa", ctypes.c_int32), ("dof", ctypes.c_int32), ("aperture", ctypes.c_float),
                 ("focal_len", ctypes.c_float), ("first_bounce_cache", ctypes.c_int32),
-                ("batch", ctypes.c_int32)]
+                ("batch", ctypes.c_int32), ("geom_bvh", ctypes.c_int32)]
 
 
 class _StatsC(ctypes.Structure):
@@ -92,7 +92,7 @@ assert ctypes.sizeof(Triangle) == 124 and ctypes.sizeof(BVHNode) == 40
 
 
 class GuiDataContainer:
-    """utilities.h:17-34, same field names and defaults (+ the two new knobs)."""
+    """utilities.h:17-34, same field names and defaults (+ the new knobs)."""
 
     def __init__(self):
         self.TracedDepth = 0
@@ -107,6 +107,7 @@ class GuiDataContainer:
         self.focal_len = 10.0
         self.firstBounceCache = False       # new
         self.batch = 0                      # new: iterations in flight (0 = default, 1 = exact order)
+        self.geomBVH = 0                    # new: BVH over spheres / cubes (0 = auto, 1 = always, -1 = linear scan)
 
 
 class Scene:
@@ -224,7 +225,8 @@ class Renderer:
 
     def set_options(self, gui):
         o = _OptionsC(int(gui.russianRoulette), int(gui.sortbyMaterial), int(gui.SSAA), int(gui.DoF),
-                      float(gui.aperture), float(gui.focal_len), int(gui.firstBounceCache), int(gui.batch))
+                      float(gui.aperture), float(gui.focal_len), int(gui.firstBounceCache), int(gui.batch),
+                      int(getattr(gui, "geomBVH", 0)))
         check(_lib().b200pt_set_options(self._h, ctypes.byref(o)))
 
     def reset(self):

@@ -143,6 +143,11 @@ typedef struct b200pt_options {
     int32_t batch;              /* NEW: iterations traced concurrently in one wavefront
                                    (0 = library default).  1 keeps the reference's accumulation
                                    order so the float sum image is bit-identical to it.       */
+    int32_t geom_bvh;           /* NEW: closest hit over the sphere / cube primitives through a bounding
+                                   volume hierarchy instead of the reference's linear scan
+                                   (pathtrace.cu:247-290).  It only prunes primitives a ray cannot touch:
+                                   the hit found -- hence the image -- is bit-identical either way.
+                                   0 = automatic (on from 32 such primitives), 1 = always, -1 = never. */
 } b200pt_options;
 
 typedef struct b200pt b200pt;

@@ -3,8 +3,9 @@
 // This is the file a maintainer of the reference adds INSTEAD OF pathtrace.cu, intersections.cu,
 // interactions.cu and stream_compaction/*.cu (path_tracer/src/): it defines the four functions of
 // pathtrace.h:6-9 against the reference's own Scene / GuiDataContainer types and forwards to the
-// C ABI of include/b200_pt.h.  Geom, Material and Camera are passed as they lie in memory (the ABI's
-// POD structs have the same byte layout, sceneStructs.h:24-72).  Conventions kept
+// C ABI of include/b200_pt.h.  Geom, Material, Camera, Triangle and BVHTree are passed as they lie in
+// memory (the ABI's POD structs have the same byte layout, sceneStructs.h:24-72,120-160,
+// BVH_tree.h); textures as (width, height, components, host pixels).  Conventions kept
 // (pathtrace.cu:108-177,423-528): file-static state, Free tolerates being called before Init, the
 // toggles are read from the GuiDataContainer on every call, the float SUM image is copied back to
 // scene->state.image on every call, the 8-bit preview goes to the caller's DEVICE buffer.
@@ -14,6 +15,7 @@
 // tests/test_dropin_gpu.py checks its output is bit-identical to the reference build's.
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include <cuda_runtime.h>
 
@@ -24,7 +26,8 @@
 #include "b200_pt.h"
 
 static_assert(sizeof(Geom) == sizeof(b200pt_geom) && sizeof(Material) == sizeof(b200pt_material) &&
-                  sizeof(Camera) == sizeof(b200pt_camera), "POD layouts must agree");
+                  sizeof(Camera) == sizeof(b200pt_camera) && sizeof(Triangle) == sizeof(b200pt_triangle) &&
+                  sizeof(BVHTree) == sizeof(b200pt_bvh_node), "POD layouts must agree");
 
 static Scene* hst_scene = NULL;
 static GuiDataContainer* guiData = NULL;
@@ -49,7 +52,17 @@ void pathtraceInit(Scene* scene)
     s.geoms = reinterpret_cast<const b200pt_geom*>(scene->geoms.data());
     s.n_materials = (int)scene->materials.size();
     s.materials = reinterpret_cast<const b200pt_material*>(scene->materials.data());
-    check(b200pt_create(&s, &renderer), "pathtraceInit");
+    // triangle meshes, the flattened BVH and the textures of the scene (scene.cpp:59-69,94-173,218)
+    std::vector<b200pt_texture> tex;
+    for (const Texture& t : scene->textures) tex.push_back({t.width, t.height, t.components, t.image});
+    b200pt_scene_ext e;
+    e.n_triangles = (int)scene->triangles.size();
+    e.triangles = reinterpret_cast<const b200pt_triangle*>(scene->triangles.data());
+    e.n_bvh_nodes = scene->triangles.empty() ? 0 : scene->n_bvh_nodes;
+    e.bvh = reinterpret_cast<const b200pt_bvh_node*>(scene->bvh_tree);
+    e.n_textures = (int)tex.size();
+    e.textures = tex.data();
+    check(b200pt_create_ext(&s, &e, &renderer), "pathtraceInit");
 }
 
 void pathtraceFree()

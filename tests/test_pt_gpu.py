@@ -136,6 +136,52 @@ def test_render_batched_within_north_star_tolerance(pt, scene, iters, flags, tag
     r.close()
 
 
+# ---- geometry BVH: prunes, never changes the hit ----------------------------------------------------------
+@pytest.mark.parametrize("scene,iters,flags,tag", RENDERS + SORT_RENDERS)
+@pytest.mark.parametrize("geom_bvh", [1, -1])
+def test_geometry_bvh_on_and_off_are_bit_identical_to_the_reference(pt, scene, iters, flags, tag, geom_bvh):
+    """forced on (even for the 7-primitive Cornell box and the mesh scene's six cubes) and forced off
+    (linear scan, also for the 600-primitive scene): same float SUM image as the reference's CUDA build"""
+    sc = load_scene(scene)
+    r = pt.Renderer(sc)
+    g = gui_from_flags(flags, batch=1)
+    g.geomBVH = geom_bvh
+    r.set_options(g)
+    r.render(1, iters)
+    img = r.read_sum()
+    assert bits_equal(img, ref_sum(scene, iters, tag, img.shape))
+    r.close()
+
+
+def test_geometry_bvh_full_size_many_primitives(pt):
+    """BASELINE config 5's scene (4096 primitives) at a reduced resolution: BVH == linear scan, bit for bit,
+    incl. after an update_scene that moves primitives (the tree is rebuilt)"""
+    sc = load_scene("synthetic_4096")
+    sc.camera.resolution[0], sc.camera.resolution[1] = 256, 144
+    imgs = []
+    for mode in (1, -1):
+        r = pt.Renderer(sc)
+        g = gui_from_flags([], batch=1)
+        g.geomBVH = mode
+        r.set_options(g)
+        r.render(1, 2)
+        a = r.read_sum()
+        for k in range(0, len(sc.geoms), 7):                 # shift a subset of the primitives
+            sc.geoms[k].transform[12] += 0.25
+            sc.geoms[k].inverseTransform[12] -= 0.25 * sc.geoms[k].inverseTransform[0]
+            sc.geoms[k].inverseTransform[13] -= 0.25 * sc.geoms[k].inverseTransform[1]
+            sc.geoms[k].inverseTransform[14] -= 0.25 * sc.geoms[k].inverseTransform[2]
+        r.update_scene(sc)
+        r.reset()
+        r.render(3, 2)
+        imgs.append((a, r.read_sum(), r.stats()["path_segments"]))
+        r.close()
+        sc = load_scene("synthetic_4096")
+        sc.camera.resolution[0], sc.camera.resolution[1] = 256, 144
+    assert bits_equal(imgs[0][0], imgs[1][0]) and bits_equal(imgs[0][1], imgs[1][1]) and imgs[0][2] == imgs[1][2]
+    assert not bits_equal(imgs[0][0], imgs[0][1])
+
+
 # ---- material sort (A9) and first-bounce cache ----------------------------------------------------------
 def have_golden(scene, iters, tag):
     return os.path.exists(os.path.join(GOLD, f"{scene}.{tag}.{iters}it.refsum.bin"))
