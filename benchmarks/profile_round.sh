@@ -8,15 +8,16 @@
 tag=${1:-rX}
 out=gpurun_out
 mkdir -p $out
-cmd="python bench.py --steps 2 --warmup 1 --cpu-iters 1 --ref-cuda-iters 1"
+cmd="python bench.py --steps 2 --warmup 1 --skip-extras"
 $cmd > $out/${tag}_prof_plain.json 2> $out/${tag}_prof_plain.err || { echo "plain run failed"; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \
     $cmd > $out/${tag}_ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 8 -c 4 -f -o $out/${tag}_k_bounce \
     python bench.py --steps 1 --warmup 1 --skip-extras > $out/${tag}_ncu_bounce.log 2>&1
-ncu --set full --clock-control none --import-source on -k 'regex:k_scan_lookback|k_compact' -s 2 -c 2 -f -o $out/${tag}_k_scan \
-    $cmd > $out/${tag}_ncu_scan.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:k_scan_lookback|k_compact' -s 6 -c 2 -f -o $out/${tag}_k_scan \
+    python benchmarks/sc_sweep.py --lg 28 --iters 2 > $out/${tag}_ncu_scan.log 2>&1
 for k in k_bounce k_scan; do
   ncu -i $out/${tag}_${k}.ncu-rep --page raw --csv > $out/${tag}_${k}_raw.csv 2>/dev/null
 done
+ncu -i $out/${tag}_k_bounce.ncu-rep --page source --csv > $out/${tag}_k_bounce_src.csv 2>/dev/null
 ls -la $out | grep ${tag}_

@@ -108,7 +108,7 @@ __device__ __forceinline__ float gbox_entry(const float4& lo, const float4& hi, 
 // Two alternating phases keep the warp converged although every thread walks its own way through
 // the tree: (1) traversal with box tests only -- the primitives of a reached leaf are tested
 // against their OWN boxes and the survivors appended to a per-thread candidate list, in roughly
-// near-to-far order; (2) the exact tests of the listed candidates, where a thread first skips the
+// near-to-far order (keeping the list sorted costs more than it prunes: measured); (2) the exact tests of the listed candidates, where a thread first skips the
 // candidates that start behind its current hit, so that every trip of the loop does real work in
 // every lane that is still busy.  (Testing leaves as they are met costs a full exact test per
 // trip as soon as ONE lane of the warp sits at a leaf.)

@@ -13,7 +13,8 @@ constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (1
 constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
 constexpr int PT_SMEM_GNODES = 192;        // geometry-BVH nodes kept in shared memory (12 KB): breadth-first order => the top levels
 constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
-constexpr int PT_GBVH_AUTO = 32;           // geom_bvh = auto: use the BVH from this many sphere / cube primitives
+constexpr int PT_GBVH_AUTO = 1;            // geom_bvh = auto: use the BVH from this many sphere / cube primitives (with fewer
+                                           // than a leaf's worth the tree is one node and the per-primitive boxes do the culling)
 constexpr int PT_DESC_STRIDE = 16;         // 64-bit words between look-back descriptors: one 128-B line each
                                            // (packed descriptors make the lines around the prefix frontier an
                                            // L2 hot spot, see lookback.cuh)

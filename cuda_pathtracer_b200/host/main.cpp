@@ -16,7 +16,7 @@
 //   --aperture A         (default 0.1)                    --focal F     focal_len (default 10.0)
 //   --first-bounce-cache reuse bounce 0's hits (honoured only with --no-ssaa --no-dof)
 //   --geom-bvh on|off|auto   closest hit over spheres / cubes through a BVH instead of the linear scan
-//                        (same image either way; auto = on from 32 primitives)
+//                        (same image either way; auto = on)
 //   --batch B            iterations in flight (0 = library default, 1 = the reference's exact
 //                        accumulation order: bit-identical float SUM image)
 //   --iter-first F --iter-stride S   trace iterations F, F+S, ... (N of them): the multi-GPU split

@@ -147,7 +147,7 @@ typedef struct b200pt_options {
                                    volume hierarchy instead of the reference's linear scan
                                    (pathtrace.cu:247-290).  It only prunes primitives a ray cannot touch:
                                    the hit found -- hence the image -- is bit-identical either way.
-                                   0 = automatic (on from 32 such primitives), 1 = always, -1 = never. */
+                                   0 = automatic (on), 1 = always, -1 = never (the reference's loop). */
 } b200pt_options;
 
 typedef struct b200pt b200pt;
