@@ -189,6 +189,9 @@ int upload_geom_bvh(b200pt* h, const b200pt_scene* sc, const std::vector<PrimRec
     h->gb.n_nodes = (int)(h->host_gnodes.size() / 4);
     h->gb.n_smem_nodes = std::min(h->gb.n_nodes, PT_SMEM_GNODES);
     h->gb.n_mesh_prims = (int)h->host_gmesh.size();
+    h->gb.cap_mesh_walk = 1;
+    for (int i = 0; i < sc->n_geoms; ++i)
+        if (sc->geoms[i].type != B200PT_MESH && sc->materials[sc->geoms[i].materialid].texture_id != -1) h->gb.cap_mesh_walk = 0;
     return 0;
 }
 

@@ -104,7 +104,7 @@ __device__ __forceinline__ float gbox_entry(const float4& lo, const float4& hi, 
     return tn <= tf * 1.00001f + 1e-5f ? tn : -1.0f;
 }
 
-// closest hit among the sphere / cube primitives through the geometry BVH, then the MESH primitives.
+// closest hit among the sphere / cube primitives through the geometry BVH.
 // Two alternating phases keep the warp converged although every thread walks its own way through
 // the tree: (1) traversal with box tests only -- the primitives of a reached leaf are tested
 // against their OWN boxes and the survivors appended to a per-thread candidate list, in roughly
@@ -115,8 +115,7 @@ __device__ __forceinline__ float gbox_entry(const float4& lo, const float4& hi, 
 constexpr int PT_GCAND = 32;       // candidate list capacity; drained when fewer than 16 slots are free
 
 __device__ __forceinline__ void closest_in_gbvh(const RenderParams& p, const float4* __restrict__ snodes_g, const V3& o,
-                                                const V3& d, const MeshHit& mh, float& t_min, int& hit, Cand& best,
-                                                int& owner)
+                                                const V3& d, float& t_min, int& hit, Cand& best)
 {
     const V3 inv = v3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
     int stack[64];
@@ -180,6 +179,12 @@ __device__ __forceinline__ void closest_in_gbvh(const RenderParams& p, const flo
         }
         nc = 0;
     }
+}
+
+// the MESH primitives: the candidate of each is the BVH hit if the hit triangle belongs to it
+__device__ __forceinline__ void closest_among_mesh_prims(const RenderParams& p, const MeshHit& mh, float& t_min, int& hit,
+                                                         int& owner)
+{
     for (int k = 0; k < p.gb.n_mesh_prims; ++k) {
         const int gi = p.gb.mesh_prims[k];
         const PrimRec& g = p.prims[gi];
@@ -291,8 +296,17 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
     // nothing in the reference: every t it computes is NaN and `t > 0` fails.  In a tree such a ray
     // passes every box test (NaN compares false) and would visit all of it: skip the trees, same result.
     const bool walk = active && d.x == d.x && d.y == d.y && d.z == d.z;
-    if (p.mesh.n_nodes > 0 && walk) mh = bvh_traverse(p.mesh, snodes, o, d);   // one traversal serves every MESH primitive
-    if (GB && walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, mh, t_min, hit, best, owner);
+    if (GB) {
+        // spheres / cubes first: their nearest hit caps the mesh walk (when nothing behind it can show)
+        if (walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, t_min, hit, best);
+        if (p.mesh.n_nodes > 0 && walk) {
+            const float cap = p.gb.cap_mesh_walk ? prune_limit(t_min) : 3.402823466e+38f;
+            mh = bvh_traverse(p.mesh, snodes, o, d, cap);       // one traversal serves every MESH primitive
+            closest_among_mesh_prims(p, mh, t_min, hit, owner);
+        }
+    } else if (p.mesh.n_nodes > 0 && walk) {
+        mh = bvh_traverse(p.mesh, snodes, o, d);
+    }
     for (int ch = 0; ch < n_chunks; ++ch) {
         mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
         const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);

@@ -44,7 +44,9 @@ struct GeomBvh {
     int n_nodes;                       // 0 = not in use (linear scan over the staged primitives)
     int n_smem_nodes;
     int n_mesh_prims;
-    int pad;
+    int cap_mesh_walk;                 // no sphere / cube has a textured material: a mesh hit behind the nearest
+                                       // sphere / cube hit cannot show anywhere (not even as the stale texture
+                                       // coordinate of pathtrace.cu:267,283), so the mesh walk may stop there
 };
 
 struct RenderParams {

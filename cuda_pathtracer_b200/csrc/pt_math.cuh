@@ -386,8 +386,9 @@ constexpr int PT_MLEAVES = 12;      // listed leaves before the list is worked o
 // a distance safely beyond t (t may be negative: glm::intersectRayTriangle also reports hits behind the origin)
 __device__ __forceinline__ float prune_limit(float t) { return fmaf(fabsf(t), 1e-4f, t) + 1e-4f; }
 
+// t_cap: nothing at or beyond this distance is of interest to the caller (+inf: everything is).
 __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec* __restrict__ snodes, const V3& o,
-                                                const V3& d)
+                                                const V3& d, float t_cap = 3.402823466e+38f)
 {
     MeshHit h;
     h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
@@ -401,7 +402,7 @@ __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec
     const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     bool more = true;
     while (more) {
-        const float lim = prune_limit(h.t);
+        const float lim = fminf(prune_limit(h.t), t_cap);
         while (true) {                                   // the walk: box tests only
             const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
             float entry;
@@ -423,7 +424,7 @@ __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec
         }
         int k = 0, i = 0;                                // the listed triangles, in the order met
         while (true) {
-            const float lim2 = prune_limit(h.t);
+            const float lim2 = fminf(prune_limit(h.t), t_cap);
             while (k < nl && (i >= leaf_count[k] || leaf_entry[k] > lim2)) { ++k; i = 0; }
             if (k >= nl) break;
             tri_candidate(M, leaf_first[k] + i, o, d, h);
