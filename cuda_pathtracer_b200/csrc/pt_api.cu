@@ -7,6 +7,7 @@
 // exit at once).  Several iterations are traced concurrently as independent batch slots of the
 // same launches (each slot compacts in its own index space, so the per-(iteration, slot-index,
 // depth) seeds -- and therefore the random paths -- are exactly the reference's).
+#include <cstdlib>
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -24,7 +25,7 @@ enum { B200_E_UNSUPPORTED = 10004 };   // B200_OK / BADARG / NODEVICE / NOMEM co
 
 struct b200pt {
     int device = 0;
-    int W = 0, H = 0, P = 0, depth = 0, tiles = 0;
+    int W = 0, H = 0, P = 0, depth = 0, tiles = 0, ptiles = 0;
     int n_prims = 0, n_mats = 0;
     CamRec cam{};
     b200pt_options opt{};
@@ -34,6 +35,7 @@ struct b200pt {
     float4* d_pool = nullptr;          // 2 pools x 3 arrays x batch_cap x P
     int* d_counts = nullptr;           // (depth + 1) x batch_cap
     unsigned long long* d_desc = nullptr;
+    int* d_tickets = nullptr;          // depth work-item counters of the persistent bounce kernel
     unsigned long long* d_segments = nullptr;
     float* d_image = nullptr;
     // split pipeline (material sort): hit records, radix-sort permutation ping-pong, digit histograms
@@ -130,10 +132,10 @@ int ensure_batch(b200pt* h, int batch)
     if (r) return r;
     r = dev_alloc((void**)&h->d_counts, sizeof(int) * (size_t)(h->depth + 1) * batch);
     if (r) return r;
-    r = dev_alloc((void**)&h->d_desc, sizeof(unsigned long long) * (size_t)batch * h->tiles * PT_DESC_STRIDE);
+    r = dev_alloc((void**)&h->d_desc, sizeof(unsigned long long) * (size_t)batch * h->ptiles * PT_DESC_STRIDE);
     if (r) return r;
     CK(cudaMemset(h->d_counts, 0, sizeof(int) * (size_t)(h->depth + 1) * batch));
-    CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->tiles * PT_DESC_STRIDE));
+    CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->ptiles * PT_DESC_STRIDE));
     h->epoch = 0;
     h->batch_cap = batch;
     return 0;
@@ -185,6 +187,8 @@ int upload_geom_bvh(b200pt* h, const b200pt_scene* sc, const std::vector<PrimRec
     h->gb.nodes = h->d_gnodes;
     h->gb.prims = h->d_gprims;
     h->gb.boxes = h->d_gboxes;
+    h->gb.crecs = h->d_gboxes + 2 * h->host_gprims.size();
+    h->gb.n_small = h->n_indexed <= PT_SMALL_MAX ? h->n_indexed : 0;
     h->gb.mesh_prims = h->d_gmesh;
     h->gb.n_nodes = (int)(h->host_gnodes.size() / 4);
     h->gb.n_smem_nodes = std::min(h->gb.n_nodes, PT_SMEM_GNODES);
@@ -440,6 +444,7 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
     h->P = h->W * h->H;
     h->depth = sc->trace_depth;
     h->tiles = (h->P + PT_THREADS - 1) / PT_THREADS;
+    h->ptiles = (h->P + PT_PTILE - 1) / PT_PTILE;
     h->n_prims = sc->n_geoms;
     h->n_mats = sc->n_materials;
     pack_camera(sc->camera, h->cam);
@@ -451,6 +456,7 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
     if (!r) r = dev_alloc((void**)&h->d_mats, sizeof(MatRec) * (size_t)sc->n_materials);
     if (!r) r = dev_alloc((void**)&h->d_image, sizeof(float) * 3 * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_segments, sizeof(unsigned long long));
+    if (!r) r = dev_alloc((void**)&h->d_tickets, sizeof(int) * (size_t)(h->depth > 0 ? h->depth : 1));
     if (r) { b200pt_destroy(h); return r; }
     CK(cudaMemcpy(h->d_prims, prims.data(), sizeof(PrimRec) * prims.size(), cudaMemcpyHostToDevice));
     static_assert(sizeof(b200pt_material) == sizeof(MatRec), "material layouts must agree");
@@ -468,9 +474,10 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
 
 int b200pt_destroy(b200pt* h)
 {
+    if (getenv("B200PT_DEBUG")) ptk::debug_dump();
     if (!h) return 0;
     cudaFree(h->d_prims); cudaFree(h->d_mats); cudaFree(h->d_pool); cudaFree(h->d_counts);
-    cudaFree(h->d_desc); cudaFree(h->d_segments); cudaFree(h->d_image);
+    cudaFree(h->d_desc); cudaFree(h->d_tickets); cudaFree(h->d_segments); cudaFree(h->d_image);
     cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
     cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
     cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv);
@@ -486,7 +493,7 @@ int b200pt_destroy(b200pt* h)
 
 int b200pt_set_options(b200pt* h, const b200pt_options* o)
 {
-    if (!h || !o || o->batch < 0 || o->batch > 64 || o->geom_bvh < -1 || o->geom_bvh > 1) return B200_E_BADARG;
+    if (!h || !o || o->batch < 0 || o->batch > PT_MAX_BATCH || o->geom_bvh < -1 || o->geom_bvh > 1) return B200_E_BADARG;
     // the cached first-bounce hits depend on the camera rays: any change of what shapes them drops the cache
     if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache)
         h->cache_valid = false;
@@ -578,6 +585,8 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.depth = h->depth;
     p.P = h->P;
     p.tiles = h->tiles;
+    p.ptiles = h->ptiles;
+    p.tickets = h->d_tickets;
     p.stride = iter_stride;
 
     const bool sort_on = h->opt.sort_by_material != 0;
@@ -612,7 +621,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
         for (int b = 0; b < h->depth; ++b) {
             p.bounce = b;
             if (++h->epoch >= (1u << 30)) {
-                CK(cudaMemsetAsync(h->d_desc, 0, sizeof(unsigned long long) * (size_t)h->batch_cap * h->tiles * PT_DESC_STRIDE, s));
+                CK(cudaMemsetAsync(h->d_desc, 0, sizeof(unsigned long long) * (size_t)h->batch_cap * h->ptiles * PT_DESC_STRIDE, s));
                 h->epoch = 1;
             }
             p.epoch = h->epoch;

@@ -11,10 +11,19 @@
 //     ulp((D/s)^2), i.e. the sphere appears up to ~ 4e-7 * D^2 / s larger in world space
 //     (0.006 for D = 70, s = 0.3);
 //   * cube: slab distances carry a few ulp(D/s) in object space, ~ 1e-6 * D in world space.
-// A primitive must be found whenever the reference would find it, so each world box is grown by
-// pad = 256 * eps * D_max (+ 32 * eps * D_max^2 / s_min for a sphere), eps = 2^-23, D_max = diagonal
-// of everything a ray can start from (all primitives, all meshes, the camera): an order of
-// magnitude or more above those errors.  tests/test_pt_gpu.py checks BVH on / off bit-identity on every scene, and
+// A primitive must be found whenever the reference would find it, and the distance the tree code
+// prunes with must never exceed the distance the reference would report.  Two margins per primitive:
+//   d_hit = 24 * eps * D_max (+ 32 * eps * D_max^2 / s_min for a sphere), eps = 2^-23, D_max = diagonal of
+//           everything a ray can start from (all primitives, all meshes, the camera): covers the rounding
+//           of the reference's hit / miss decision and of the conservative tests here;
+//   d_t   = 1.05e-4 * s_max + 24 * eps * D_max: the reference reports the distance to a point pulled back
+//           by 1e-4 OBJECT units along the ray (getPointOnRay, intersections.h:29-32), up to 1e-4 * s_max
+//           in world units.
+// The tree boxes are grown by d_hit + d_t (they decide hit / miss and bound the distance at once).  The
+// per-primitive cull records of small scenes (crecs, see closest_small in pt_kernels.cu) keep the two
+// apart: a ray that has just left a surface starts 1e-4 outside it -- inside the d_t margin but outside
+// the d_hit one -- and must not cost an exact test of the surface it leaves.
+// tests/test_pt_gpu.py checks BVH on / off bit-identity on every scene, and
 // the 600-primitive golden render of the reference's CUDA build pins the BVH path directly.
 #include <algorithm>
 #include <cfloat>
@@ -42,6 +51,7 @@ struct Box3 {
 
 struct Ref {
     int prim;
+    int ex;                        // position in the per-primitive side table (refs get reordered by the build)
     Box3 box;
     double c[3];
 };
@@ -108,6 +118,8 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
                     std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out)
 {
     nodes_out.clear(); prims_out.clear(); boxes_out.clear(); mesh_prims_out.clear();
+    struct Extra { double s[3]; double d_hit, d_t; bool aligned, finite; Box3 tight; };
+    std::vector<Extra> extra;
     const double eps = 1.1920928955078125e-7;
     std::vector<Ref> refs;
     std::vector<double> smin;
@@ -127,10 +139,30 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
                          (double)g.fwd[3 * 3 + row];
             r.box.grow(w);
         }
-        double s = DBL_MAX;                                      // smallest column norm of the linear part = smallest scale
-        for (int c = 0; c < 3; ++c)
-            s = std::min(s, std::sqrt((double)g.fwd[c * 3] * g.fwd[c * 3] + (double)g.fwd[c * 3 + 1] * g.fwd[c * 3 + 1] +
-                                      (double)g.fwd[c * 3 + 2] * g.fwd[c * 3 + 2]));
+        Extra ex{};
+        ex.finite = true;
+        for (int k = 0; k < 12; ++k) ex.finite = ex.finite && std::isfinite(g.fwd[k]) && std::isfinite(g.inv[k]);
+        double s = DBL_MAX;                                      // column norms of the linear part = the three scales
+        for (int c = 0; c < 3; ++c) {
+            ex.s[c] = std::sqrt((double)g.fwd[c * 3] * g.fwd[c * 3] + (double)g.fwd[c * 3 + 1] * g.fwd[c * 3 + 1] +
+                                (double)g.fwd[c * 3 + 2] * g.fwd[c * 3 + 2]);
+            s = std::min(s, ex.s[c]);
+        }
+        // axis aligned: every object axis maps onto one world axis (the world box IS the cube)
+        ex.aligned = true;
+        for (int c = 0; c < 3; ++c) {
+            int nz = 0;
+            for (int row = 0; row < 3; ++row) nz += g.fwd[c * 3 + row] != 0.0f;
+            if (nz != 1) ex.aligned = false;
+        }
+        for (int row = 0; row < 3; ++row) {
+            int nz = 0;
+            for (int c = 0; c < 3; ++c) nz += g.fwd[c * 3 + row] != 0.0f;
+            if (nz != 1) ex.aligned = false;
+        }
+        ex.tight = r.box;
+        r.ex = (int)extra.size();
+        extra.push_back(ex);
         smin.push_back(s);
         world.grow(r.box);
         refs.push_back(r);
@@ -140,11 +172,14 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
     for (int a = 0; a < 3; ++a) diag2 += (world.hi[a] - world.lo[a]) * (world.hi[a] - world.lo[a]);
     const double dmax = std::sqrt(diag2) * 1.05 + 1.0;           // + lens offsets / the 1e-4 surface offsets
     for (size_t i = 0; i < refs.size(); ++i) {
-        double pad = 256.0 * eps * dmax;
-        if (prims[(size_t)refs[i].prim].type == 0) pad += smin[i] > 0.0 ? 32.0 * eps * dmax * dmax / smin[i] : dmax;   // sphere
+        Extra& ex = extra[i];
+        ex.d_hit = 24.0 * eps * dmax;
+        if (prims[(size_t)refs[i].prim].type == 0) ex.d_hit += smin[i] > 0.0 ? 32.0 * eps * dmax * dmax / smin[i] : dmax;   // sphere
+        ex.d_t = 1.05e-4 * std::max(ex.s[0], std::max(ex.s[1], ex.s[2])) + 24.0 * eps * dmax;
+        double pad = ex.d_hit + ex.d_t;
         if (!(pad < dmax)) pad = dmax;                           // degenerate scale: the box covers everything
         for (int a = 0; a < 3; ++a) {
-            if (!std::isfinite(refs[i].box.lo[a]) || !std::isfinite(refs[i].box.hi[a])) { refs[i].box.lo[a] = -1e30; refs[i].box.hi[a] = 1e30; }
+            if (!std::isfinite(refs[i].box.lo[a]) || !std::isfinite(refs[i].box.hi[a])) { refs[i].box.lo[a] = -1e30; refs[i].box.hi[a] = 1e30; ex.finite = false; }
             refs[i].box.lo[a] -= pad;
             refs[i].box.hi[a] += pad;
             refs[i].c[a] = 0.5 * (refs[i].box.lo[a] + refs[i].box.hi[a]);
@@ -193,10 +228,45 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
         q.z = std::nextafterf((float)b.hi[2], FLT_MAX); std::memcpy(&q.w, &w, 4);
         return q;
     };
-    boxes_out.resize(2 * refs.size());
+    boxes_out.resize(4 * refs.size());
     for (size_t i = 0; i < refs.size(); ++i) {
         boxes_out[2 * i + 0] = lo4(refs[i].box, 0);
         boxes_out[2 * i + 1] = hi4(refs[i].box, 0);
+    }
+    // Cull records of the small-scene path, two float4 per primitive, in the same (leaf) order, behind the boxes:
+    //   kind 0  axis-aligned cube: {world lo - d_hit, kind} {world hi + d_hit, d_t}
+    //   kind 1  cube:              {object half extents 0.5 + d_hit / s_a, kind} {d_t / s_a, -}
+    //   kind 2  sphere:            {r_hit^2, r_t^2, -, kind}, r = 0.5 + margin / s_min in object space
+    //   kind 3  degenerate transform: always a candidate
+    auto up = [](double v) { return std::nextafterf((float)v, FLT_MAX); };
+    for (size_t i = 0; i < refs.size(); ++i) {
+        const Extra& ex = extra[(size_t)refs[i].ex];
+        const int type = prims[(size_t)refs[i].prim].type;
+        const double smin_i = std::min(ex.s[0], std::min(ex.s[1], ex.s[2]));
+        int kind = 3;
+        float4 q0 = {0, 0, 0, 0}, q1 = {0, 0, 0, 0};
+        if (ex.finite && smin_i > 0.0 && ex.d_hit + ex.d_t < dmax) {
+            if (type == 1 && ex.aligned) {
+                kind = 0;
+                Box3 b = ex.tight;
+                for (int a = 0; a < 3; ++a) { b.lo[a] -= ex.d_hit; b.hi[a] += ex.d_hit; }
+                q0 = lo4(b, 0);
+                q1 = hi4(b, 0);
+                q1.w = up(ex.d_t);
+            } else if (type == 1) {
+                kind = 1;
+                q0.x = up(0.5 + ex.d_hit / ex.s[0]); q0.y = up(0.5 + ex.d_hit / ex.s[1]); q0.z = up(0.5 + ex.d_hit / ex.s[2]);
+                q1.x = up(ex.d_t / ex.s[0]); q1.y = up(ex.d_t / ex.s[1]); q1.z = up(ex.d_t / ex.s[2]);
+            } else if (type == 0) {
+                kind = 2;
+                const double rh = 0.5 + ex.d_hit / smin_i, rt = 0.5 + (ex.d_hit + ex.d_t) / smin_i;
+                q0.x = up(rh * rh * (1.0 + 1e-6));
+                q0.y = up(rt * rt * (1.0 + 1e-6));
+            }
+        }
+        std::memcpy(&q0.w, &kind, 4);
+        boxes_out[2 * refs.size() + 2 * i + 0] = q0;
+        boxes_out[2 * refs.size() + 2 * i + 1] = q1;
     }
     nodes_out.resize(4 * order.size());
     for (size_t i = 0; i < order.size(); ++i) {

@@ -18,6 +18,7 @@
 // Roofline: the Cornell-size scenes are FP32-issue bound (about 1.8 k instructions per path
 // segment: IEEE div/sqrt/rcp sequences that exact parity requires) with HBM close behind;
 // algorithmic bytes are 96 B per path segment + 24 B per pixel per iteration.
+#include <cstdio>
 #include "pt_kernels.cuh"
 #include "lookback.cuh"
 
@@ -181,6 +182,113 @@ __device__ __forceinline__ void closest_in_gbvh(const RenderParams& p, const flo
     }
 }
 
+// ---- small scenes: no tree, conservative per-primitive tests that also bound the distance ----------
+// With a handful of primitives (Cornell: 7) walking a tree costs more than it saves, and what limits
+// the kernel is how many EXACT tests a warp runs: the candidates of a ray used to be tested in index
+// order, so a warp ran as many trips of the exact test as its unluckiest lane had overlapping boxes
+// (ncu: 21 of 32 lanes active there, profiles/r4_*).  Here every primitive gets a cheap conservative
+// test against its true shape (world box for an axis-aligned cube, object-space slabs for a rotated one,
+// the quadratic for a sphere), all lanes on the same primitive at the same time, which yields a lower
+// bound t_lo of the distance the reference would report (pt_gbvh.cu: margins d_hit / d_t).  The exact
+// test then runs on the candidate with the smallest t_lo first -- nearly always the winner, after
+// which the others are pruned by t_lo > t -- so most rays cost ONE exact test.  Selection is by the
+// lexicographic minimum of (t, index), as everywhere.
+__device__ __forceinline__ bool cull_test(const float4& q0, const float4& q1, const PrimRec& g, const V3& o, const V3& d,
+                                          const V3& inv, float& t_lo)
+{
+    const int kind = __float_as_int(q0.w);
+    float nx, ny, nz, fx, fy, fz, kx, ky, kz;
+    if (kind == 0) {
+        const float ax = (q0.x - o.x) * inv.x, bx = (q1.x - o.x) * inv.x;
+        const float ay = (q0.y - o.y) * inv.y, by = (q1.y - o.y) * inv.y;
+        const float az = (q0.z - o.z) * inv.z, bz = (q1.z - o.z) * inv.z;
+        nx = fminf(ax, bx); fx = fmaxf(ax, bx);
+        ny = fminf(ay, by); fy = fmaxf(ay, by);
+        nz = fminf(az, bz); fz = fmaxf(az, bz);
+        kx = q1.w * fabsf(inv.x); ky = q1.w * fabsf(inv.y); kz = q1.w * fabsf(inv.z);
+    } else if (kind == 1 || kind == 2) {
+        const float* m = g.inv;
+        const V3 qo = v3(fmaf(o.x, m[0], fmaf(o.y, m[3], fmaf(o.z, m[6], m[9]))), fmaf(o.x, m[1], fmaf(o.y, m[4], fmaf(o.z, m[7], m[10]))),
+                         fmaf(o.x, m[2], fmaf(o.y, m[5], fmaf(o.z, m[8], m[11]))));
+        const V3 qd = v3(fmaf(d.x, m[0], fmaf(d.y, m[3], d.z * m[6])), fmaf(d.x, m[1], fmaf(d.y, m[4], d.z * m[7])),
+                         fmaf(d.x, m[2], fmaf(d.y, m[5], d.z * m[8])));
+        if (kind == 2) {                         // |qo + t qd|^2 = r^2; qd is not normalised, so t is the world distance
+            const float a = fmaf(qd.x, qd.x, fmaf(qd.y, qd.y, qd.z * qd.z));
+            const float b = fmaf(qo.x, qd.x, fmaf(qo.y, qd.y, qo.z * qd.z));
+            const float c = fmaf(qo.x, qo.x, fmaf(qo.y, qo.y, qo.z * qo.z));
+            const float disc = fmaf(b, b, -a * (c - q0.x));
+            if (!(disc >= 0.0f)) return false;
+            const float ia = __fdividef(1.0f, a);
+            if ((sqrtf(disc) - b) * ia < 0.0f) return false;          // the far root lies behind the origin
+            const float disc_t = fmaf(b, b, -a * (c - q0.y));         // the larger sphere: its near root bounds t
+            t_lo = (-b - sqrtf(fmaxf(disc_t, disc))) * ia;
+            return true;
+        }
+        const V3 iq = v3(__fdividef(1.0f, qd.x), __fdividef(1.0f, qd.y), __fdividef(1.0f, qd.z));
+        const float ax = (-q0.x - qo.x) * iq.x, bx = (q0.x - qo.x) * iq.x;
+        const float ay = (-q0.y - qo.y) * iq.y, by = (q0.y - qo.y) * iq.y;
+        const float az = (-q0.z - qo.z) * iq.z, bz = (q0.z - qo.z) * iq.z;
+        nx = fminf(ax, bx); fx = fmaxf(ax, bx);
+        ny = fminf(ay, by); fy = fmaxf(ay, by);
+        nz = fminf(az, bz); fz = fmaxf(az, bz);
+        kx = q1.x * fabsf(iq.x); ky = q1.y * fabsf(iq.y); kz = q1.z * fabsf(iq.z);
+    } else {
+        t_lo = -3.402823466e+38f;
+        return true;
+    }
+    // fminf / fmaxf drop the NaNs of 0 * inf: a degenerate slab is "no constraint"
+    const float tn = fmaxf(fmaxf(nx, ny), nz), tf = fminf(fminf(fx, fy), fz);
+    if (!(tn <= tf && tf >= 0.0f)) return false;
+    t_lo = fmaxf(fmaxf(nx - kx, ny - ky), nz - kz);      // entry into the box grown by d_t
+    return true;
+}
+
+// sp: the n sphere / cube records (pad0 = index in the scene's primitive array), cr: their cull records
+__device__ __forceinline__ void closest_small(const PrimRec* __restrict__ sp, const float4* __restrict__ cr, int n, const V3& o,
+                                              const V3& d, float& t_min, int& hit, int& hit_k, Cand& best)
+{
+    const V3 inv = v3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
+    const float INF = 3.402823466e+38f;
+    float t1 = INF, t2 = INF;                    // the two smallest t_lo
+    int k1 = -1, k2 = -1;
+    unsigned cand = 0u;
+    for (int k = 0; k < n; ++k) {
+        float t_lo;
+        if (cull_test(cr[2 * k], cr[2 * k + 1], sp[k], o, d, inv, t_lo)) {
+            cand |= 1u << k;
+            if (t_lo < t1) { t2 = t1; k2 = k1; t1 = t_lo; k1 = k; }
+            else if (t_lo < t2) { t2 = t_lo; k2 = k; }
+        }
+    }
+    if (k1 < 0) return;
+    cand &= ~(1u << k1);
+    if (k2 >= 0) cand &= ~(1u << k2);
+    int next = k1;
+    bool first = true;
+    while (next >= 0) {                          // one call site of the exact test: the kernel is large enough as it is
+        const PrimRec& g = sp[next];
+        const Cand c = prim_test(g, o, d);
+        const int gi = g.pad0;
+        if (c.t > 0.0f && (t_min > c.t || (t_min == c.t && gi < hit))) {
+            t_min = c.t;
+            hit = gi;
+            hit_k = next;
+            best = c;
+        }
+        if (first) {
+            first = false;
+            // no margin needed: t_lo is a true lower bound of what the reference would report (pt_gbvh.cu)
+            if (k2 >= 0 && !(t2 > t_min)) { next = k2; continue; }
+        }
+        if (cand) {                              // three or more candidates: rare, no pruning
+            next = __ffs(cand) - 1;
+            cand &= cand - 1u;
+        } else {
+            next = -1;
+        }
+    }
+}
+
 // the MESH primitives: the candidate of each is the BVH hit if the hit triangle belongs to it
 __device__ __forceinline__ void closest_among_mesh_prims(const RenderParams& p, const MeshHit& mh, float& t_min, int& hit,
                                                          int& owner)
@@ -206,6 +314,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_raygen(const __grid_constant__ R
     const int slot = blockIdx.y;
     const int idx = blockIdx.x * PT_THREADS + threadIdx.x;
     if (idx == 0) p.counts[slot] = p.P;             // live paths entering bounce 0
+    if (idx == 0 && slot == 0)
+        for (int b = 0; b < p.depth; ++b) p.tickets[b] = 0;     // work-item counters of this batch's bounce launches
     if (idx >= p.P) return;
     const int y = idx / p.cam.W, x = idx - y * p.cam.W;
     const int iter = p.iter0 + slot * p.stride;
@@ -233,11 +343,11 @@ __device__ __forceinline__ MeshHit no_mesh_hit()
     return h;
 }
 
-__device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
+__device__ __forceinline__ void bounce_barriers_init(unsigned long long* bar)
 {
     if (threadIdx.x == 0) {
-        mbar_init(&sh.bar[0], 1);
-        mbar_init(&sh.bar[1], 1);
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -246,18 +356,28 @@ __device__ __forceinline__ void bounce_barriers_init(BounceShared& sh)
 
 // producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
 // (with the geometry BVH: the top of that tree instead of primitive chunks)
-__device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared& sh, MatRec* smats, int n_smem_mats,
+__device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long long* bar, MatRec* smats, int n_smem_mats,
                                             BvhRec* snodes, PrimRec* sprims, bool want_prims)
 {
     if (threadIdx.x != 0) return;
     if (p.gb.n_nodes > 0) {
         const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
         const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
+        if (p.gb.n_small > 0) {                  // the records themselves and their cull records, no tree
+            const unsigned r_bytes = want_prims ? (unsigned)(p.gb.n_small * sizeof(PrimRec)) : 0u;
+            const unsigned c_bytes = want_prims ? (unsigned)(p.gb.n_small * 2 * sizeof(float4)) : 0u;
+            mbar_expect_tx(&bar[0], mat_bytes + node_bytes + r_bytes + c_bytes);
+            if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &bar[0]);
+            if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &bar[0]);
+            if (r_bytes) bulk_g2s(sprims, p.gb.prims, r_bytes, &bar[0]);
+            if (c_bytes) bulk_g2s(sprims + p.gb.n_small, p.gb.crecs, c_bytes, &bar[0]);
+            return;
+        }
         const unsigned g_bytes = want_prims ? (unsigned)(p.gb.n_smem_nodes * 4 * sizeof(float4)) : 0u;
-        mbar_expect_tx(&sh.bar[0], mat_bytes + node_bytes + g_bytes);
-        if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
-        if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &sh.bar[0]);
-        if (g_bytes) bulk_g2s(sprims, p.gb.nodes, g_bytes, &sh.bar[0]);
+        mbar_expect_tx(&bar[0], mat_bytes + node_bytes + g_bytes);
+        if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &bar[0]);
+        if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &bar[0]);
+        if (g_bytes) bulk_g2s(sprims, p.gb.nodes, g_bytes, &bar[0]);
         return;
     }
     const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
@@ -265,14 +385,14 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared&
     const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
     const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
     const int n0 = want_prims ? min(chunk_cap, p.n_prims) : 0;
-    mbar_expect_tx(&sh.bar[0], mat_bytes + node_bytes + (unsigned)(n0 * sizeof(PrimRec)));
-    if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &sh.bar[0]);
-    if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &sh.bar[0]);
-    if (n0) bulk_g2s(sprims, p.prims, (unsigned)(n0 * sizeof(PrimRec)), &sh.bar[0]);
+    mbar_expect_tx(&bar[0], mat_bytes + node_bytes + (unsigned)(n0 * sizeof(PrimRec)));
+    if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &bar[0]);
+    if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &bar[0]);
+    if (n0) bulk_g2s(sprims, p.prims, (unsigned)(n0 * sizeof(PrimRec)), &bar[0]);
     if (want_prims && n_chunks > 1) {
         const int n1 = min(PT_CHUNK, p.n_prims - PT_CHUNK);
-        mbar_expect_tx(&sh.bar[1], (unsigned)(n1 * sizeof(PrimRec)));
-        bulk_g2s(sprims + PT_CHUNK, p.prims + PT_CHUNK, (unsigned)(n1 * sizeof(PrimRec)), &sh.bar[1]);
+        mbar_expect_tx(&bar[1], (unsigned)(n1 * sizeof(PrimRec)));
+        bulk_g2s(sprims + PT_CHUNK, p.prims + PT_CHUNK, (unsigned)(n1 * sizeof(PrimRec)), &bar[1]);
     }
 }
 
@@ -280,8 +400,9 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, BounceShared&
 // the CTA must call it (it contains the chunk barriers); inactive threads only take part in those.
 // GB: the sphere / cube primitives are searched through the geometry BVH (whose top levels lie
 // where the primitive chunks would) instead of the linear scan.
-template <bool GB>
-__device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, BounceShared& sh, const BvhRec* snodes,
+// GB: 0 = linear scan over the staged primitive chunks, 1 = geometry BVH, 2 = small-scene search
+template <int GB>
+__device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsigned long long* bar, const BvhRec* snodes,
                                                      const PrimRec* sprims, bool active, const V3& o, const V3& d)
 {
     const int n_chunks = GB ? 0 : (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
@@ -291,14 +412,17 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
     MeshHit mh = no_mesh_hit();
     int owner = -1;
-    if (GB || p.mesh.n_nodes > 0) mbar_wait(&sh.bar[0], 0u);     // the staged top(s) of the tree(s)
+    if (GB || p.mesh.n_nodes > 0) mbar_wait(&bar[0], 0u);     // the staged top(s) of the tree(s)
     // A ray whose direction is NaN (glm::refract past the critical angle, interactions.cu:68) hits
     // nothing in the reference: every t it computes is NaN and `t > 0` fails.  In a tree such a ray
     // passes every box test (NaN compares false) and would visit all of it: skip the trees, same result.
     const bool walk = active && d.x == d.x && d.y == d.y && d.z == d.z;
+    int hit_k = -1;
     if (GB) {
         // spheres / cubes first: their nearest hit caps the mesh walk (when nothing behind it can show)
-        if (walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, t_min, hit, best);
+        if (GB == 2) {
+            if (walk) closest_small(sprims, reinterpret_cast<const float4*>(sprims + p.gb.n_small), p.gb.n_small, o, d, t_min, hit, hit_k, best);
+        } else if (walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, t_min, hit, best);
         if (p.mesh.n_nodes > 0 && walk) {
             const float cap = p.gb.cap_mesh_walk ? prune_limit(t_min) : 3.402823466e+38f;
             mh = bvh_traverse(p.mesh, snodes, o, d, cap);       // one traversal serves every MESH primitive
@@ -308,7 +432,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
         mh = bvh_traverse(p.mesh, snodes, o, d);
     }
     for (int ch = 0; ch < n_chunks; ++ch) {
-        mbar_wait(&sh.bar[ch & 1], (unsigned)((ch >> 1) & 1));
+        mbar_wait(&bar[ch & 1], (unsigned)((ch >> 1) & 1));
         const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
         const PrimRec* sp = sprims + (n_chunks > 1 ? (ch & 1) * PT_CHUNK : 0);
         if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, mh, t_min, hit, best, owner);
@@ -317,9 +441,9 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
             if (threadIdx.x == 0) {
                 const int n2 = min(PT_CHUNK, p.n_prims - (ch + 2) * PT_CHUNK);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_expect_tx(&sh.bar[ch & 1], (unsigned)(n2 * sizeof(PrimRec)));
+                mbar_expect_tx(&bar[ch & 1], (unsigned)(n2 * sizeof(PrimRec)));
                 bulk_g2s(const_cast<PrimRec*>(sprims) + (ch & 1) * PT_CHUNK, p.prims + (size_t)(ch + 2) * PT_CHUNK,
-                         (unsigned)(n2 * sizeof(PrimRec)), &sh.bar[ch & 1]);
+                         (unsigned)(n2 * sizeof(PrimRec)), &bar[ch & 1]);
             }
         }
     }
@@ -329,7 +453,9 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, Boun
     h.mat = 0;
     h.u = h.v = 0.0f;
     if (hit >= 0) {
-        const PrimRec& g = (GB || n_chunks > 1) ? p.prims[hit] : sprims[hit];
+        // (small-scene search: a MESH winner is not among the staged records -> hit_k stays behind)
+        const bool staged = GB == 2 ? (hit_k >= 0 && sprims[hit_k].pad0 == hit) : (GB == 0 && n_chunks <= 1);
+        const PrimRec& g = staged ? sprims[GB == 2 ? hit_k : hit] : p.prims[hit];
         if (g.type == 2) {
             tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, h.n, h.u, h.v);
         } else {
@@ -357,11 +483,9 @@ __device__ __forceinline__ PathState load_path(const Pool& pool, size_t at)
 // shadeMaterials + scatterRay for the path at compacted slot `idx`, finalGather for a path that
 // ends here, and the stable single-pass compaction of the survivors into the other pool.
 // Every thread of the CTA must call it.
-__device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceShared& sh, const MatRec* smats,
-                                                  int n_smem_mats, PathState& s, const HitRec& h, bool active,
-                                                  int slot, int tile, int idx, int n_live, int* count_out)
+__device__ __forceinline__ bool shade_path(const RenderParams& p, const MatRec* smats, int n_smem_mats, PathState& s,
+                                           const HitRec& h, bool active, int slot, int idx)
 {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     bool live = false;
     if (active) {
         const MatRec& m = n_smem_mats ? smats[h.mat] : p.mats[h.mat];
@@ -378,6 +502,15 @@ __device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceS
             atomicAdd(px + 2, s.c.z);
         }
     }
+    return live;
+}
+
+__device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceShared& sh, const MatRec* smats,
+                                                  int n_smem_mats, PathState& s, const HitRec& h, bool active,
+                                                  int slot, int tile, int idx, int n_live, int* count_out)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool live = shade_path(p, smats, n_smem_mats, s, h, active, slot, idx);
     // ---- stable compaction of the survivors (mark_valid + scan + keep, pathtrace.cu:359-407) ---
     const unsigned bal = __ballot_sync(FULL_MASK, live);
     const int wrank = __popc(bal & ((1u << lane) - 1u));
@@ -412,8 +545,8 @@ __device__ __forceinline__ void shade_and_compact(const RenderParams& p, BounceS
 // k_bounce: the fused bounce.  CACHE (first-bounce cache, bounce 0 only, valid when the camera rays
 // do not change between iterations, i.e. SSAA and DoF off): 0 = off, 1 = trace and fill the cache
 // (slot 0 writes it), 2 = replace the closest-hit search by one 20-byte cache read per path.
-template <int CACHE, bool GB>
-__global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ RenderParams p)
+template <int CACHE, int GB>
+__global__ void __launch_bounds__(PT_THREADS) k_bounce_tile(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
@@ -431,8 +564,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         return;
     }
     if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
-    bounce_barriers_init(sh);
-    stage_begin(p, sh, smats, n_smem_mats, snodes, sprims, CACHE != 2);
+    bounce_barriers_init(sh.bar);
+    stage_begin(p, sh.bar, smats, n_smem_mats, snodes, sprims, CACHE != 2);
 
     // this thread's path (overlaps the bulk copies)
     const int idx = tile * PT_THREADS + threadIdx.x;
@@ -448,7 +581,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         h.u = cuv.x; h.v = cuv.y;
         mbar_wait(&sh.bar[0], 0u);                  // the materials
     } else {
-        h = closest_hit_staged<GB>(p, sh, snodes, sprims, active, s.o, s.d);
+        h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, s.o, s.d);
         if (CACHE == 1 && slot == 0 && active) {
             p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             p.cache_k[idx] = h.mat;
@@ -459,11 +592,231 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_bounce: the fused bounce as a PERSISTENT kernel with a warp-specialised look-back.
+//
+// In k_bounce_tile every tile's 256 threads sit at a barrier while warp 0 looks back over the
+// predecessors' descriptors -- and the predecessors are tiles that started at about the same time
+// and take about as long, so the wait is a sizeable part of a tile's life (ncu, Cornell 800x800:
+// 23-29 % of all warp samples were that one barrier, profiles/r4_k_bounce_*).  Here
+//   * a CTA is 7 compute warps + 1 scan warp and keeps taking tiles (224 paths) from an atomic
+//     ticket counter -- so a tile's predecessors are
+//     always held by running CTAs that work their tickets off in order: no deadlock whatever the
+//     residency -- with the scene staged into its shared memory by TMA once, not once per tile;
+//   * the compute warps of tile k rank their survivors (ballot), stash them in shared memory (each
+//     warp in its own 32-slot region), hand {slot, tile, aggregate} to the scan warp through a
+//     two-entry mailbox, and go straight on to tile k+1;
+//   * the scan warp publishes the aggregate, looks back, publishes the inclusive prefix (and the
+//     live count of the next bounce after a slot's last tile) and posts the exclusive prefix;
+//   * the compute warps pick that prefix up one tile later and write the stashed survivors of
+//     tile k to the other pool, warp by warp (stable: e + ranks inside the tile).
+// One CTA-wide barrier per tile is left (the seven warp counts), on named barrier 1 so that the
+// scan warp is not part of it.
+struct alignas(16) PersistShared {
+    unsigned long long bar[2];            // TMA staging
+    int warp_cnt[2][8];                   // survivors per compute warp, by tile parity
+    int item[2][4];                       // {slot (-1: no more work), tile, -, -} of the tile with this parity
+    int req[2][4];                        // mailbox to the scan warp: {slot, tile (-1: stop), aggregate, last tile of the slot}
+    int resp[2];                          // exclusive prefix of the tile with this parity
+    int req_seq, resp_seq;                // requests posted / answered so far
+    int item_seq;                         // work items fetched so far
+    int total_items;
+    int n_live[PT_MAX_BATCH];             // live paths of each slot entering this bounce
+    int item_base[PT_MAX_BATCH + 4];      // first work item of each slot (exclusive prefix of the live tile counts)
+};
+static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it must stay 16-byte aligned");
+
+#ifndef PT_LB_K
+#define PT_LB_K 1
+#endif
+constexpr size_t PT_STASH_BYTES = (size_t)3 * PT_PTILE * sizeof(float4);
+
+__device__ unsigned long long g_dbg[8];
+__device__ __forceinline__ int ld_volatile_shared(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+
+// work item w -> (slot, tile); one thread
+__device__ __forceinline__ void put_item(PersistShared& sh, int w, int parity)
+{
+    int slot = -1, tile = 0;
+    if (w < sh.total_items) {
+        slot = 0;
+        while (w >= sh.item_base[slot + 1]) ++slot;
+        tile = w - sh.item_base[slot];
+    }
+    sh.item[parity][0] = slot;
+    sh.item[parity][1] = tile;
+}
+
+template <int CACHE, int GB>
+__global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    PersistShared& sh = *reinterpret_cast<PersistShared*>(smem_raw);
+    const int n_smem_mats = p.n_mats <= PT_SMEM_MATS ? p.n_mats : 0;
+    float4* stash = reinterpret_cast<float4*>(smem_raw + sizeof(PersistShared));      // [3][PT_PWARPS][32]
+    MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(PersistShared) + PT_STASH_BYTES);
+    BvhRec* snodes = reinterpret_cast<BvhRec*>(smats + n_smem_mats);
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE != 2 ? p.mesh.n_smem_nodes : 0));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // ---- prologue: the work-item table of this launch, the first ticket, the staging copies ----
+    if (threadIdx.x < p.batch) sh.n_live[threadIdx.x] = p.counts[p.bounce * p.batch + threadIdx.x];
+    bounce_barriers_init(sh.bar);                    // contains a __syncthreads
+    if (threadIdx.x == 0) {
+        int base = 0;
+        for (int sl = 0; sl < p.batch; ++sl) {
+            sh.item_base[sl] = base;
+            base += (sh.n_live[sl] + PT_PTILE - 1) / PT_PTILE;
+        }
+        sh.item_base[p.batch] = base;
+        sh.total_items = base;
+        sh.req_seq = 0;
+        sh.resp_seq = 0;
+        put_item(sh, atomicAdd(p.tickets + p.bounce, 1), 0);
+        sh.item_seq = 1;
+        // a CTA without work must not leave bulk copies in flight when it exits
+        if (sh.item[0][0] >= 0) stage_begin(p, sh.bar, smats, n_smem_mats, snodes, sprims, CACHE != 2);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < p.batch) {
+        const int n = sh.n_live[threadIdx.x];
+        if (n == 0) p.counts[(p.bounce + 1) * p.batch + threadIdx.x] = 0;       // nobody else writes a dead slot's count
+        else atomicAdd(p.segments, (unsigned long long)n);
+    }
+    __syncthreads();
+
+    // ---- the scan warp ----
+    if (warp == PT_PWARPS) {
+        for (int it = 0;; ++it) {
+            while (ld_volatile_shared(&sh.req_seq) <= it) __nanosleep(40);
+            __threadfence_block();
+            const int slot = ld_volatile_shared(&sh.req[it & 1][0]), tile = ld_volatile_shared(&sh.req[it & 1][1]);
+            const int aggregate = ld_volatile_shared(&sh.req[it & 1][2]), last = ld_volatile_shared(&sh.req[it & 1][3]);
+            if (tile < 0) break;
+            unsigned long long* desc = p.desc + (size_t)slot * p.ptiles * PT_DESC_STRIDE;
+            const int e = b200::lb_exclusive_prefix_cfg<PT_LB_K, b200::LB_DEFAULT_BACKOFF_NS, PT_DESC_STRIDE>(
+                desc, (unsigned)tile, p.epoch, aggregate, 0, lane);
+            if (lane == 0) {
+                if (last) p.counts[(p.bounce + 1) * p.batch + slot] = e + aggregate;
+                sh.resp[it & 1] = e;
+                __threadfence_block();
+                *reinterpret_cast<volatile int*>(&sh.resp_seq) = it + 1;
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ---- the compute warps ----
+    float4* my_stash = stash + warp * 32;            // + k * PT_PTILE for word k of the path
+    int prev_cnt = 0, prev_off = 0, prev_slot = 0;
+    int it = 0;
+    for (;; ++it) {
+        while (ld_volatile_shared(&sh.item_seq) <= it) __nanosleep(20);
+        __threadfence_block();
+        const int slot = ld_volatile_shared(&sh.item[it & 1][0]), tile = ld_volatile_shared(&sh.item[it & 1][1]);
+        if (slot < 0) break;                          // uniform over the CTA
+        const int n_live = sh.n_live[slot];
+        const int idx = tile * PT_PTILE + threadIdx.x;
+        const bool active = idx < n_live;
+        PathState s = load_path(p.in, (size_t)slot * p.P + (active ? idx : 0));
+
+        HitRec h;
+        if (CACHE == 2) {
+            const float4 cn = p.cache_n[active ? idx : 0];
+            const float2 cuv = p.cache_uv[active ? idx : 0];
+            h.t = cn.x; h.n = v3(cn.y, cn.z, cn.w);
+            h.mat = p.cache_k[active ? idx : 0];
+            h.u = cuv.x; h.v = cuv.y;
+            mbar_wait(&sh.bar[0], 0u);                // the materials
+        } else {
+            h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, s.o, s.d);
+            if (CACHE == 1 && slot == 0 && active) {
+                p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+                p.cache_k[idx] = h.mat;
+                p.cache_uv[idx] = make_float2(h.u, h.v);
+            }
+        }
+        // The CTA's next work item: the ticket is drawn here, between closest hit and shading, so that the
+        // atomic's round trip hides behind the shading, and is turned into (slot, tile) after the barrier.
+        // Not earlier: a ticket that sits unprocessed while higher ones are worked off elsewhere makes
+        // every look-back wait for the straggler (drawn a whole tile ahead, half of all flushes found their
+        // prefix not ready, 10 us each); not later: the whole CTA would wait for the round trip every tile.
+        int next_w = 0;
+        if (threadIdx.x == 0) next_w = atomicAdd(p.tickets + p.bounce, 1);
+        const bool live = shade_path(p, smats, n_smem_mats, s, h, active, slot, idx);
+
+        const unsigned bal = __ballot_sync(FULL_MASK, live);
+        const int wrank = __popc(bal & ((1u << lane) - 1u));
+        const int cnt = __popc(bal);
+        if (lane == 0) sh.warp_cnt[it & 1][warp] = cnt;
+        asm volatile("bar.sync 1, %0;" ::"n"(PT_PTILE) : "memory");
+        int warp_prefix = 0, aggregate = 0;
+#pragma unroll
+        for (int w = 0; w < PT_PWARPS; ++w) {
+            const int c = sh.warp_cnt[it & 1][w];
+            if (w < warp) warp_prefix += c;
+            aggregate += c;
+        }
+        if (threadIdx.x == 0) {
+            sh.req[it & 1][0] = slot;
+            sh.req[it & 1][1] = tile;
+            sh.req[it & 1][2] = aggregate;
+            sh.req[it & 1][3] = tile == (n_live - 1) / PT_PTILE;
+            __threadfence_block();
+            *reinterpret_cast<volatile int*>(&sh.req_seq) = it + 1;
+            put_item(sh, next_w, (it + 1) & 1);
+            __threadfence_block();
+            *reinterpret_cast<volatile int*>(&sh.item_seq) = it + 2;
+        }
+        if (it > 0) {                                 // the previous tile's survivors, now that its prefix is known
+            {
+                int spins = 0;
+                while (ld_volatile_shared(&sh.resp_seq) < it) { __nanosleep(200); ++spins; }
+                if (lane == 0) { atomicAdd(&g_dbg[0], 1ull); if (spins) { atomicAdd(&g_dbg[1], 1ull); atomicAdd(&g_dbg[2], (unsigned long long)spins); } }
+            }
+            __threadfence_block();
+            const int e = ld_volatile_shared(&sh.resp[(it - 1) & 1]);
+            if (lane < prev_cnt) {
+                const size_t at = (size_t)prev_slot * p.P + (size_t)(e + prev_off + lane);
+                p.out.a[at] = my_stash[lane];
+                p.out.b[at] = my_stash[PT_PTILE + lane];
+                p.out.c[at] = my_stash[2 * PT_PTILE + lane];
+            }
+            __syncwarp();
+        }
+        if (live) {
+            my_stash[wrank] = make_float4(s.o.x, s.o.y, s.o.z, __int_as_float(s.pixel));
+            my_stash[PT_PTILE + wrank] = make_float4(s.d.x, s.d.y, s.d.z, __int_as_float(s.remaining));
+            my_stash[2 * PT_PTILE + wrank] = make_float4(s.c.x, s.c.y, s.c.z, __int_as_float(s.bounces));
+        }
+        __syncwarp();
+        prev_cnt = cnt;
+        prev_off = warp_prefix;
+        prev_slot = slot;
+    }
+    if (threadIdx.x == 0) {                           // tell the scan warp to leave
+        sh.req[it & 1][1] = -1;
+        __threadfence_block();
+        *reinterpret_cast<volatile int*>(&sh.req_seq) = it + 1;
+    }
+    if (it > 0) {
+        while (ld_volatile_shared(&sh.resp_seq) < it) { }
+        __threadfence_block();
+        const int e = ld_volatile_shared(&sh.resp[(it - 1) & 1]);
+        if (lane < prev_cnt) {
+            const size_t at = (size_t)prev_slot * p.P + (size_t)(e + prev_off + lane);
+            p.out.a[at] = my_stash[lane];
+            p.out.b[at] = my_stash[PT_PTILE + lane];
+            p.out.c[at] = my_stash[2 * PT_PTILE + lane];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // The split pipeline used when paths are bucketed by material between intersection and shading
 // (thrust::sort_by_key on materialId, pathtrace.cu:410-414,479-491): k_isect writes the hit
 // records, k_sort_hist / (scan) / k_sort_scatter build the stable sorted order as a permutation
 // (LSD radix, 8 bits per pass, one pass for up to 256 materials), k_shade gathers through it.
-template <bool GB>
+template <int GB>
 __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -475,13 +828,13 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     const int n_live = p.counts[p.bounce * p.batch + slot];
     if (tile * PT_THREADS >= n_live) return;
     if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
-    bounce_barriers_init(sh);
-    stage_begin(p, sh, nullptr, 0, snodes, sprims, true);
+    bounce_barriers_init(sh.bar);
+    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
     const int idx = tile * PT_THREADS + threadIdx.x;
     const bool active = idx < n_live;
     const size_t at = (size_t)slot * p.P + (active ? idx : 0);
     const float4 a = p.in.a[at], b = p.in.b[at];
-    const HitRec h = closest_hit_staged<GB>(p, sh, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
+    const HitRec h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
     if (active) {
         p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
         p.hit_k[at] = h.mat;
@@ -588,8 +941,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_shade(const __grid_constant__ Re
         return;
     }
     if (p.cache_mode == 2 && tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
-    bounce_barriers_init(sh);
-    stage_begin(p, sh, smats, n_smem_mats, nullptr, nullptr, false);
+    bounce_barriers_init(sh.bar);
+    stage_begin(p, sh.bar, smats, n_smem_mats, nullptr, nullptr, false);
     const int j = tile * PT_THREADS + threadIdx.x;
     const bool active = j < n_live;
     const int src = active ? (p.perm_in ? p.perm_in[(size_t)slot * p.P + j] : j) : 0;
@@ -704,27 +1057,53 @@ __global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
-size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes)
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes, int n_small)
 {
     const int n_chunks = (n_prims + PT_CHUNK - 1) / PT_CHUNK;
-    const size_t prim_bytes = n_gnodes ? (size_t)n_gnodes * 4 * sizeof(float4)
+    const size_t prim_bytes = n_small ? (size_t)n_small * (sizeof(PrimRec) + 2 * sizeof(float4))
+                              : n_gnodes ? (size_t)n_gnodes * 4 * sizeof(float4)
                                        : (size_t)(n_chunks > 1 ? 2 * PT_CHUNK : n_prims) * sizeof(PrimRec);
     const size_t mat_bytes = (size_t)(n_mats <= PT_SMEM_MATS ? n_mats : 0) * sizeof(MatRec);
     const size_t node_bytes = (size_t)(n_nodes < PT_SMEM_NODES ? n_nodes : PT_SMEM_NODES) * sizeof(BvhRec);
     return sizeof(BounceShared) + mat_bytes + node_bytes + prim_bytes;
 }
 
+// shared memory of the persistent bounce kernel: its control block and survivor stash in front of the staged scene
+static size_t persist_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes, int n_small = 0)
+{
+    return bounce_smem_bytes(n_prims, n_mats, n_nodes, n_gnodes, n_small) - sizeof(BounceShared) + sizeof(PersistShared) + PT_STASH_BYTES;
+}
+
+void debug_dump()
+{
+    unsigned long long h[8];
+    if (cudaMemcpyFromSymbol(h, g_dbg, sizeof(h)) == cudaSuccess)
+        fprintf(stderr, "dbg: flush waits %llu, not ready %llu, sleeps %llu\n", h[0], h[1], h[2]);
+}
+
+template <typename K>
+static cudaError_t allow_smem(K kernel, int bytes)
+{
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
 cudaError_t configure_kernels()
 {
     const int cap = (int)bounce_smem_bytes(2 * PT_CHUNK, PT_SMEM_MATS, PT_SMEM_NODES);
-    cudaError_t e = cudaFuncSetAttribute(k_bounce<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bounce<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_isect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    const int pcap = (int)persist_smem_bytes(PT_CHUNK, PT_SMEM_MATS, PT_SMEM_NODES, 0);
+    cudaError_t e = allow_smem(k_bounce_tile<0, 0>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce_tile<1, 0>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<0, 0>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<1, 0>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<2, 0>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<0, 1>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<1, 1>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<0, 2>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<1, 2>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<0>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<1>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<2>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_shade, cap);
     return e;
 }
 
@@ -734,24 +1113,78 @@ cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
     return cudaGetLastError();
 }
 
+bool bounce_is_persistent(const RenderParams& p)
+{
+    return p.cache_mode == 2 || p.gb.n_nodes > 0 || p.n_prims <= PT_CHUNK;
+}
+
+// CTAs of a persistent launch: as many as are resident at once (more would only queue up behind them)
+template <typename K>
+static cudaError_t persistent_grid(K kernel, size_t smem, int work_items, int& grid)
+{
+    static int sm_count = 0;
+    if (sm_count == 0) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+    }
+    int per_sm = 0;
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PT_THREADS, smem);
+    if (e != cudaSuccess) return e;
+    grid = sm_count * (per_sm > 0 ? per_sm : 1);
+    if (grid > work_items) grid = work_items;
+    if (grid < 1) grid = 1;
+    return cudaSuccess;
+}
+
+template <int CACHE, int GB>
+static cudaError_t launch_persistent(const RenderParams& p, size_t smem, cudaStream_t s)
+{
+    // the occupancy query is a host-side table lookup, but cache it anyway per shared-memory size
+    static size_t cached_smem = ~(size_t)0;
+    static int cached_grid = 0;
+    if (cached_smem != smem) {
+        int g = 0;
+        const cudaError_t e = persistent_grid(k_bounce<CACHE, GB>, smem, 1 << 30, g);
+        if (e != cudaSuccess) return e;
+        cached_grid = g;
+        cached_smem = smem;
+    }
+    const int items = p.batch * p.ptiles;
+    k_bounce<CACHE, GB><<<cached_grid < items ? cached_grid : items, PT_THREADS, smem, s>>>(p);
+    return cudaGetLastError();
+}
+
+// which closest-hit search a launch uses: 0 = linear scan, 1 = geometry BVH, 2 = small-scene search
+static int search_mode(const RenderParams& p) { return p.gb.n_nodes > 0 ? (p.gb.n_small > 0 ? 2 : 1) : 0; }
+
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
 {
+    const int mode = search_mode(p);
+    if (bounce_is_persistent(p)) {
+        const size_t smem = persist_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
+        if (p.cache_mode == 2) return launch_persistent<2, 0>(p, persist_smem_bytes(0, p.n_mats, 0, 0), s);
+        if (p.cache_mode == 1)
+            return mode == 2 ? launch_persistent<1, 2>(p, smem, s) : mode == 1 ? launch_persistent<1, 1>(p, smem, s) : launch_persistent<1, 0>(p, smem, s);
+        return mode == 2 ? launch_persistent<0, 2>(p, smem, s) : mode == 1 ? launch_persistent<0, 1>(p, smem, s) : launch_persistent<0, 0>(p, smem, s);
+    }
+    // linear scan over more than one chunk of primitives (geom_bvh off): one CTA per tile, chunks streamed by TMA
     const dim3 grid(p.tiles, p.batch);
-    const bool gb = p.gb.n_nodes > 0;
-    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes);
-    if (p.cache_mode == 2) k_bounce<2, false><<<grid, PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
-    else if (p.cache_mode == 1 && gb) k_bounce<1, true><<<grid, PT_THREADS, smem, s>>>(p);
-    else if (p.cache_mode == 1) k_bounce<1, false><<<grid, PT_THREADS, smem, s>>>(p);
-    else if (gb) k_bounce<0, true><<<grid, PT_THREADS, smem, s>>>(p);
-    else k_bounce<0, false><<<grid, PT_THREADS, smem, s>>>(p);
+    const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, 0);
+    if (p.cache_mode == 1) k_bounce_tile<1, 0><<<grid, PT_THREADS, smem, s>>>(p);
+    else k_bounce_tile<0, 0><<<grid, PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
 {
-    const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes);
-    if (p.gb.n_nodes > 0) k_isect<true><<<dim3(p.tiles, p.batch), PT_THREADS, smem, s>>>(p);
-    else k_isect<false><<<dim3(p.tiles, p.batch), PT_THREADS, smem, s>>>(p);
+    const int mode = search_mode(p);
+    const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
+    const dim3 grid(p.tiles, p.batch);
+    if (mode == 2) k_isect<2><<<grid, PT_THREADS, smem, s>>>(p);
+    else if (mode == 1) k_isect<1><<<grid, PT_THREADS, smem, s>>>(p);
+    else k_isect<0><<<grid, PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 

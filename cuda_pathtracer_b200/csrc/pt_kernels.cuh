@@ -8,6 +8,10 @@
 namespace ptk {
 
 constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
+constexpr int PT_PWARPS = 7;                // compute warps of the persistent fused bounce kernel; its eighth warp
+                                           // only runs the look-backs of the CTA's tiles (k_bounce, pt_kernels.cu)
+constexpr int PT_PTILE = PT_PWARPS * 32;   // paths per tile of that kernel
+constexpr int PT_MAX_BATCH = 64;           // iterations in flight (b200pt_options::batch upper bound)
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
 constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
@@ -15,6 +19,7 @@ constexpr int PT_SMEM_GNODES = 192;        // geometry-BVH nodes kept in shared 
 constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
 constexpr int PT_GBVH_AUTO = 1;            // geom_bvh = auto: use the BVH from this many sphere / cube primitives (with fewer
                                            // than a leaf's worth the tree is one node and the per-primitive boxes do the culling)
+constexpr int PT_SMALL_MAX = 24;           // sphere / cube primitives up to which the small-scene search replaces the tree
 constexpr int PT_DESC_STRIDE = 16;         // 64-bit words between look-back descriptors: one 128-B line each
                                            // (packed descriptors make the lines around the prefix frontier an
                                            // L2 hot spot, see lookback.cuh)
@@ -40,10 +45,13 @@ struct GeomBvh {
     const float4* nodes;
     const PrimRec* prims;              // copies in leaf order; pad0 = index in the scene's primitive array
     const float4* boxes;               // padded world box of each of them: {lo, -} {hi, -}
+    const float4* crecs;               // cull records (two float4 per primitive, same order; pt_gbvh.cu)
     const int* mesh_prims;             // indices of the MESH primitives, ascending
     int n_nodes;                       // 0 = not in use (linear scan over the staged primitives)
     int n_smem_nodes;
     int n_mesh_prims;
+    int n_small;                       // > 0: so few sphere / cube primitives (<= PT_SMALL_MAX) that the tree is
+                                       // skipped: all of them and their cull records are staged in shared memory
     int cap_mesh_walk;                 // no sphere / cube has a textured material: a mesh hit behind the nearest
                                        // sphere / cube hit cannot show anywhere (not even as the stale texture
                                        // coordinate of pathtrace.cu:267,283), so the mesh walk may stop there
@@ -63,6 +71,8 @@ struct RenderParams {
     int depth;
     int P;                             // pixels = paths per iteration
     int tiles;                         // ceil(P / PT_THREADS)
+    int ptiles;                        // ceil(P / PT_PTILE): tiles per slot of the persistent bounce kernel
+    int* tickets;                      // [depth]: next work item of each bounce's persistent launch (zeroed by k_raygen)
     int batch;                         // iterations in flight in this launch (grid.y)
     int iter0, stride;                 // slot s traces iteration iter0 + s * stride
     int bounce;                        // which bounce this launch is
@@ -83,7 +93,7 @@ struct RenderParams {
     GeomBvh gb;
 };
 
-size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0);
+size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0, int n_small = 0);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);           // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
@@ -99,6 +109,10 @@ cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, MeshScene 
 cudaError_t launch_debug_shade(const MatRec* mats, MeshScene mesh, OptRec opt, int iter, int n, const float* isects,
                                float* segments, cudaStream_t s);
 cudaError_t configure_kernels();
+void debug_dump();
+// true when launch_bounce runs the persistent kernel for these parameters (everything except the
+// linear scan over more than one shared-memory chunk of primitives)
+bool bounce_is_persistent(const RenderParams& p);
 
 // pt_gbvh.cu (host): nodes (4 float4 each, breadth first), the sphere / cube records in leaf order
 // (pad0 = scene index) with their padded boxes, and the indices of the MESH primitives.  Empty nodes_out: nothing to index.
