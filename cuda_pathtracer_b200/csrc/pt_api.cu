@@ -474,7 +474,6 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
 
 int b200pt_destroy(b200pt* h)
 {
-    if (getenv("B200PT_DEBUG")) ptk::debug_dump();
     if (!h) return 0;
     cudaFree(h->d_prims); cudaFree(h->d_mats); cudaFree(h->d_pool); cudaFree(h->d_counts);
     cudaFree(h->d_desc); cudaFree(h->d_tickets); cudaFree(h->d_segments); cudaFree(h->d_image);

@@ -148,17 +148,19 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
                                 (double)g.fwd[c * 3 + 2] * g.fwd[c * 3 + 2]);
             s = std::min(s, ex.s[c]);
         }
-        // axis aligned: every object axis maps onto one world axis (the world box IS the cube)
+        // axis aligned: every object axis maps onto one world axis -- up to 1e-5 of its length, so that a
+        // 90-degree rotation (cos = -4.4e-8 in fp32) still counts; the world box of the corners then exceeds
+        // the cube by that little, which a conservative test may
         ex.aligned = true;
         for (int c = 0; c < 3; ++c) {
-            int nz = 0;
-            for (int row = 0; row < 3; ++row) nz += g.fwd[c * 3 + row] != 0.0f;
-            if (nz != 1) ex.aligned = false;
+            int big = 0;
+            for (int row = 0; row < 3; ++row) big += std::fabs((double)g.fwd[c * 3 + row]) > 1e-5 * ex.s[c];
+            if (big != 1) ex.aligned = false;
         }
         for (int row = 0; row < 3; ++row) {
-            int nz = 0;
-            for (int c = 0; c < 3; ++c) nz += g.fwd[c * 3 + row] != 0.0f;
-            if (nz != 1) ex.aligned = false;
+            int big = 0;
+            for (int c = 0; c < 3; ++c) big += std::fabs((double)g.fwd[c * 3 + row]) > 1e-5 * ex.s[c];
+            if (big != 1) ex.aligned = false;
         }
         ex.tight = r.box;
         r.ex = (int)extra.size();
@@ -236,7 +238,7 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
     // Cull records of the small-scene path, two float4 per primitive, in the same (leaf) order, behind the boxes:
     //   kind 0  axis-aligned cube: {world lo - d_hit, kind} {world hi + d_hit, d_t}
     //   kind 1  cube:              {object half extents 0.5 + d_hit / s_a, kind} {d_t / s_a, -}
-    //   kind 2  sphere:            {r_hit^2, r_t^2, -, kind}, r = 0.5 + margin / s_min in object space
+    //   kind 2  sphere:            {object-space error of a transformed point, d_t / s_min, -, kind}
     //   kind 3  degenerate transform: always a candidate
     auto up = [](double v) { return std::nextafterf((float)v, FLT_MAX); };
     for (size_t i = 0; i < refs.size(); ++i) {
@@ -258,10 +260,11 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
                 q0.x = up(0.5 + ex.d_hit / ex.s[0]); q0.y = up(0.5 + ex.d_hit / ex.s[1]); q0.z = up(0.5 + ex.d_hit / ex.s[2]);
                 q1.x = up(ex.d_t / ex.s[0]); q1.y = up(ex.d_t / ex.s[1]); q1.z = up(ex.d_t / ex.s[2]);
             } else if (type == 0) {
+                // object-space error of the transformed origin (the reference's rounding and this code's) and
+                // the distance margin; the radius margin depends on where the ray starts (closest_small)
                 kind = 2;
-                const double rh = 0.5 + ex.d_hit / smin_i, rt = 0.5 + (ex.d_hit + ex.d_t) / smin_i;
-                q0.x = up(rh * rh * (1.0 + 1e-6));
-                q0.y = up(rt * rt * (1.0 + 1e-6));
+                q0.x = up(8.0 * eps * dmax / smin_i);
+                q0.y = up(ex.d_t / smin_i);
             }
         }
         std::memcpy(&q0.w, &kind, 4);

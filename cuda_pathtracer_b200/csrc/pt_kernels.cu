@@ -49,6 +49,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
 {
     asm volatile(
@@ -216,11 +220,18 @@ __device__ __forceinline__ bool cull_test(const float4& q0, const float4& q1, co
             const float a = fmaf(qd.x, qd.x, fmaf(qd.y, qd.y, qd.z * qd.z));
             const float b = fmaf(qo.x, qd.x, fmaf(qo.y, qd.y, qo.z * qd.z));
             const float c = fmaf(qo.x, qo.x, fmaf(qo.y, qo.y, qo.z * qo.z));
-            const float disc = fmaf(b, b, -a * (c - q0.x));
+            // The reference's radicand dot(o,d)^2 - (dot(o,o) - r^2) (intersections.cu:74-79) cancels numbers of
+            // size c = |qo|^2 and inherits the rounding q0.x of qo: the sphere it sees may be this much larger.
+            // The margin grows with the distance of the origin, so a ray LEAVING the sphere (origin 1e-4 outside
+            // it) keeps a tight one and is rejected here instead of costing an exact test.
+            const float rh2 = 0.25f + fmaf(1.9073486e-6f, c + 0.25f, q0.x * fmaf(4.0f, sqrtf(c), 4.0f * q0.x));
+            const float disc = fmaf(b, b, -a * (c - rh2));
             if (!(disc >= 0.0f)) return false;
+            const float sq = sqrtf(disc);
+            if (sq - b < -9.5367432e-7f * (sq + fabsf(b))) return false;          // the far root lies behind the origin
             const float ia = __fdividef(1.0f, a);
-            if ((sqrtf(disc) - b) * ia < 0.0f) return false;          // the far root lies behind the origin
-            const float disc_t = fmaf(b, b, -a * (c - q0.y));         // the larger sphere: its near root bounds t
+            const float rt = sqrtf(rh2) + q0.y;                                    // + d_t: its near root bounds t from below
+            const float disc_t = fmaf(b, b, -a * (c - rt * rt * 1.000001f));
             t_lo = (-b - sqrtf(fmaxf(disc_t, disc))) * ia;
             return true;
         }
@@ -613,13 +624,18 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce_tile(const __grid_constan
 // scan warp is not part of it.
 struct alignas(16) PersistShared {
     unsigned long long bar[2];            // TMA staging
+    // Mailbox signalling between the compute warps and the scan warp: one single-arrival mbarrier per
+    // parity and direction (waiting on an mbarrier suspends the warp in hardware; polling a flag in shared
+    // memory cost 12 % of all issued instructions).  Request `it` uses req_bar[it & 1], phase it >> 1, and
+    // cannot be posted before the answer to request it - 2 has been consumed, so a waiter never sees the
+    // barrier more than one phase ahead.
+    unsigned long long req_bar[2], resp_bar[2];
     int warp_cnt[2][8];                   // survivors per compute warp, by tile parity
     int item[2][4];                       // {slot (-1: no more work), tile, -, -} of the tile with this parity
     int req[2][4];                        // mailbox to the scan warp: {slot, tile (-1: stop), aggregate, last tile of the slot}
     int resp[2];                          // exclusive prefix of the tile with this parity
-    int req_seq, resp_seq;                // requests posted / answered so far
-    int item_seq;                         // work items fetched so far
     int total_items;
+    int pad_;
     int n_live[PT_MAX_BATCH];             // live paths of each slot entering this bounce
     int item_base[PT_MAX_BATCH + 4];      // first work item of each slot (exclusive prefix of the live tile counts)
 };
@@ -630,8 +646,6 @@ static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it m
 #endif
 constexpr size_t PT_STASH_BYTES = (size_t)3 * PT_PTILE * sizeof(float4);
 
-__device__ unsigned long long g_dbg[8];
-__device__ __forceinline__ int ld_volatile_shared(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 
 // work item w -> (slot, tile); one thread
 __device__ __forceinline__ void put_item(PersistShared& sh, int w, int parity)
@@ -660,7 +674,11 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
 
     // ---- prologue: the work-item table of this launch, the first ticket, the staging copies ----
     if (threadIdx.x < p.batch) sh.n_live[threadIdx.x] = p.counts[p.bounce * p.batch + threadIdx.x];
-    bounce_barriers_init(sh.bar);                    // contains a __syncthreads
+    if (threadIdx.x == 0) {
+        mbar_init(&sh.req_bar[0], 1); mbar_init(&sh.req_bar[1], 1);
+        mbar_init(&sh.resp_bar[0], 1); mbar_init(&sh.resp_bar[1], 1);
+    }
+    bounce_barriers_init(sh.bar);                    // fences the initialisations; contains a __syncthreads
     if (threadIdx.x == 0) {
         int base = 0;
         for (int sl = 0; sl < p.batch; ++sl) {
@@ -669,10 +687,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         }
         sh.item_base[p.batch] = base;
         sh.total_items = base;
-        sh.req_seq = 0;
-        sh.resp_seq = 0;
         put_item(sh, atomicAdd(p.tickets + p.bounce, 1), 0);
-        sh.item_seq = 1;
         // a CTA without work must not leave bulk copies in flight when it exits
         if (sh.item[0][0] >= 0) stage_begin(p, sh.bar, smats, n_smem_mats, snodes, sprims, CACHE != 2);
     }
@@ -686,21 +701,19 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     // ---- the scan warp ----
     if (warp == PT_PWARPS) {
         for (int it = 0;; ++it) {
-            while (ld_volatile_shared(&sh.req_seq) <= it) __nanosleep(40);
-            __threadfence_block();
-            const int slot = ld_volatile_shared(&sh.req[it & 1][0]), tile = ld_volatile_shared(&sh.req[it & 1][1]);
-            const int aggregate = ld_volatile_shared(&sh.req[it & 1][2]), last = ld_volatile_shared(&sh.req[it & 1][3]);
+            mbar_wait(&sh.req_bar[it & 1], (unsigned)((it >> 1) & 1));
+            const int slot = sh.req[it & 1][0], tile = sh.req[it & 1][1];
+            const int aggregate = sh.req[it & 1][2], last = sh.req[it & 1][3];
             if (tile < 0) break;
             unsigned long long* desc = p.desc + (size_t)slot * p.ptiles * PT_DESC_STRIDE;
             const int e = b200::lb_exclusive_prefix_cfg<PT_LB_K, b200::LB_DEFAULT_BACKOFF_NS, PT_DESC_STRIDE>(
                 desc, (unsigned)tile, p.epoch, aggregate, 0, lane);
+            __syncwarp();                             // every lane has read the request before it can be answered
             if (lane == 0) {
                 if (last) p.counts[(p.bounce + 1) * p.batch + slot] = e + aggregate;
                 sh.resp[it & 1] = e;
-                __threadfence_block();
-                *reinterpret_cast<volatile int*>(&sh.resp_seq) = it + 1;
+                mbar_arrive(&sh.resp_bar[it & 1]);
             }
-            __syncwarp();
         }
         return;
     }
@@ -710,9 +723,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     int prev_cnt = 0, prev_off = 0, prev_slot = 0;
     int it = 0;
     for (;; ++it) {
-        while (ld_volatile_shared(&sh.item_seq) <= it) __nanosleep(20);
-        __threadfence_block();
-        const int slot = ld_volatile_shared(&sh.item[it & 1][0]), tile = ld_volatile_shared(&sh.item[it & 1][1]);
+        const int slot = sh.item[it & 1][0], tile = sh.item[it & 1][1];    // written before the previous tile's barrier
         if (slot < 0) break;                          // uniform over the CTA
         const int n_live = sh.n_live[slot];
         const int idx = tile * PT_PTILE + threadIdx.x;
@@ -748,6 +759,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
         const int wrank = __popc(bal & ((1u << lane) - 1u));
         const int cnt = __popc(bal);
         if (lane == 0) sh.warp_cnt[it & 1][warp] = cnt;
+        if (threadIdx.x == 0) put_item(sh, next_w, (it + 1) & 1);
         asm volatile("bar.sync 1, %0;" ::"n"(PT_PTILE) : "memory");
         int warp_prefix = 0, aggregate = 0;
 #pragma unroll
@@ -761,20 +773,11 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
             sh.req[it & 1][1] = tile;
             sh.req[it & 1][2] = aggregate;
             sh.req[it & 1][3] = tile == (n_live - 1) / PT_PTILE;
-            __threadfence_block();
-            *reinterpret_cast<volatile int*>(&sh.req_seq) = it + 1;
-            put_item(sh, next_w, (it + 1) & 1);
-            __threadfence_block();
-            *reinterpret_cast<volatile int*>(&sh.item_seq) = it + 2;
+            mbar_arrive(&sh.req_bar[it & 1]);
         }
         if (it > 0) {                                 // the previous tile's survivors, now that its prefix is known
-            {
-                int spins = 0;
-                while (ld_volatile_shared(&sh.resp_seq) < it) { __nanosleep(200); ++spins; }
-                if (lane == 0) { atomicAdd(&g_dbg[0], 1ull); if (spins) { atomicAdd(&g_dbg[1], 1ull); atomicAdd(&g_dbg[2], (unsigned long long)spins); } }
-            }
-            __threadfence_block();
-            const int e = ld_volatile_shared(&sh.resp[(it - 1) & 1]);
+            mbar_wait(&sh.resp_bar[(it - 1) & 1], (unsigned)(((it - 1) >> 1) & 1));
+            const int e = sh.resp[(it - 1) & 1];
             if (lane < prev_cnt) {
                 const size_t at = (size_t)prev_slot * p.P + (size_t)(e + prev_off + lane);
                 p.out.a[at] = my_stash[lane];
@@ -795,13 +798,11 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce(const __grid_constant__ R
     }
     if (threadIdx.x == 0) {                           // tell the scan warp to leave
         sh.req[it & 1][1] = -1;
-        __threadfence_block();
-        *reinterpret_cast<volatile int*>(&sh.req_seq) = it + 1;
+        mbar_arrive(&sh.req_bar[it & 1]);
     }
     if (it > 0) {
-        while (ld_volatile_shared(&sh.resp_seq) < it) { }
-        __threadfence_block();
-        const int e = ld_volatile_shared(&sh.resp[(it - 1) & 1]);
+        mbar_wait(&sh.resp_bar[(it - 1) & 1], (unsigned)(((it - 1) >> 1) & 1));
+        const int e = sh.resp[(it - 1) & 1];
         if (lane < prev_cnt) {
             const size_t at = (size_t)prev_slot * p.P + (size_t)(e + prev_off + lane);
             p.out.a[at] = my_stash[lane];
@@ -1072,13 +1073,6 @@ size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes, int
 static size_t persist_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes, int n_small = 0)
 {
     return bounce_smem_bytes(n_prims, n_mats, n_nodes, n_gnodes, n_small) - sizeof(BounceShared) + sizeof(PersistShared) + PT_STASH_BYTES;
-}
-
-void debug_dump()
-{
-    unsigned long long h[8];
-    if (cudaMemcpyFromSymbol(h, g_dbg, sizeof(h)) == cudaSuccess)
-        fprintf(stderr, "dbg: flush waits %llu, not ready %llu, sleeps %llu\n", h[0], h[1], h[2]);
 }
 
 template <typename K>

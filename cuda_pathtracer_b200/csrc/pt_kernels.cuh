@@ -109,7 +109,6 @@ cudaError_t launch_debug_intersect(const PrimRec* prims, int n_prims, MeshScene 
 cudaError_t launch_debug_shade(const MatRec* mats, MeshScene mesh, OptRec opt, int iter, int n, const float* isects,
                                float* segments, cudaStream_t s);
 cudaError_t configure_kernels();
-void debug_dump();
 // true when launch_bounce runs the persistent kernel for these parameters (everything except the
 // linear scan over more than one shared-memory chunk of primitives)
 bool bounce_is_persistent(const RenderParams& p);
