@@ -34,7 +34,10 @@ void load_obj_mesh(const std::string& path, const Mat4& transform, const Mat4& i
 // Reorders `triangles` (leaf order) and returns the flattened BVH; empty input -> empty BVH.
 std::vector<b200pt_bvh_node> build_bvh_tree(std::vector<b200pt_triangle>& triangles);
 
-// Binary PPM (P6, maxval 255) and PGM (P5) are decoded natively.  Throws on other formats.
+// Baseline JPEG (jpeg.cpp: the same bytes stb_image returns, which is what the reference loads textures
+// with) and binary PPM (P6, maxval 255) / PGM (P5) are decoded natively.  Throws on other formats.
 TextureImage load_texture(const std::string& path);
+bool looks_like_jpeg(const unsigned char* data, size_t size);
+TextureImage decode_jpeg(const unsigned char* data, size_t size, const std::string& name);
 
 }  // namespace b200host

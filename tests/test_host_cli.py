@@ -22,7 +22,8 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
 SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
           "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096",
-          "mesh_room", "mesh_room_small", "mesh_stress"]   # OBJ meshes + BVH + textures ("B2PTSCN2")
+          "mesh_room", "mesh_room_small", "mesh_stress",   # OBJ meshes + BVH + textures ("B2PTSCN2")
+          "jpeg_textures"]   # twelve baseline JPEGs (scenes/make_jpeg_fixtures.py) decoded by host/jpeg.cpp vs stb_image
 
 
 def scene_path(name):
@@ -74,6 +75,45 @@ def test_loader_against_the_reference_tree_when_present(tmp_path):
     subprocess.run([dump, ref_scene, a], check=True, stdout=subprocess.DEVNULL)
     subprocess.run([EXE, ref_scene, "--dump-scene", b], check=True, stdout=subprocess.DEVNULL)
     assert open(a, "rb").read() == open(b, "rb").read()
+
+
+REF_ROOM = os.path.join(REPO, "oracle", "_ref", "ref_scenes", "room.json")     # staged by oracle/Makefile
+
+
+def test_reference_room_scene_loads_unmodified(tmp_path):
+    """the reference's own scenes/room.json (4 OBJ meshes, chair.jpg 1024x1024 + wallpaper.jpg 500x250,
+    both baseline 4:2:0 JPEG) through both loaders: every byte equal, texels included"""
+    dump = os.path.join(REPO, "oracle", "_ref", "ref_scene_dump")
+    if not (os.path.exists(REF_ROOM) and os.path.exists(dump)):
+        pytest.skip("needs oracle/_ref (reference scene files + ref_scene_dump, build container)")
+    a, b = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+    subprocess.run([dump, REF_ROOM, a], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run([EXE, REF_ROOM, "--dump-scene", b], check=True, stdout=subprocess.DEVNULL)
+    raw = open(a, "rb").read()
+    assert len(raw) > 3 * 1024 * 1024 and raw == open(b, "rb").read()
+
+
+def test_jpeg_decoder_rejects_what_it_does_not_decode(tmp_path):
+    """progressive JPEG / truncated data: a load error naming the file (exit 255 as for any load error), never garbage texels"""
+    from PIL import Image
+    tex = tmp_path / "Textures"
+    tex.mkdir()
+    img = Image.fromarray((np.arange(48 * 40 * 3) % 251).astype(np.uint8).reshape(40, 48, 3))
+    img.save(str(tex / "prog.jpg"), "JPEG", progressive=True)
+    img.save(str(tex / "ok.jpg"), "JPEG")
+    whole = (tex / "ok.jpg").read_bytes()
+    (tex / "cut.jpg").write_bytes(whole[:len(whole) // 3])
+    for name, code in (("ok.jpg", 0), ("prog.jpg", 255), ("cut.jpg", 255)):
+        scene = {"Materials": {"m": {"TYPE": "Diffuse", "RGB": [1, 1, 1], "TEXTURE_FILE": name}},
+                 "Camera": {"RES": [8, 8], "FOVY": 45.0, "ITERATIONS": 1, "DEPTH": 1, "FILE": "t", "EYE": [0, 0, 5],
+                            "LOOKAT": [0, 0, 0], "UP": [0, 1, 0]},
+                 "Objects": [{"TYPE": "cube", "MATERIAL": "m", "TRANS": [0, 0, 0], "ROTAT": [0, 0, 0], "SCALE": [1, 1, 1]}]}
+        import json
+        (tmp_path / "s.json").write_text(json.dumps(scene))
+        r = subprocess.run([EXE, str(tmp_path / "s.json"), "--dump-scene", str(tmp_path / "o.bin")], capture_output=True, text=True)
+        assert r.returncode == code, (name, r.stdout, r.stderr)
+        if code:
+            assert name in (r.stdout + r.stderr)
 
 
 def test_material_ids_follow_alphabetical_key_order(tmp_path):
@@ -130,6 +170,23 @@ def test_cli_render_matches_reference_cuda_build(tmp_path, scene, iters, flags, 
     got = got.reshape(h, w, 3)
     assert bits_equal(got, ref_sum(scene, iters, tag, got.shape))
     assert np.array_equal(png, expected_png_pixels(got, iters))
+
+
+@pytest.mark.gpu
+def test_reference_room_scene_renders_bit_identical_to_the_reference_cuda_build(tmp_path):
+    """The reference's scenes/room.json, unmodified (1200x1200, OBJ meshes + BVH + JPEG textures), through
+    this repo's CLI and through the reference's own CUDA build on this box: the float SUM images are equal
+    bit for bit.  Needs oracle/_ref (travels with the snapshot from the build container)."""
+    ref_exe = os.path.join(REPO, "oracle", "_ref", "ref_pathtracer")
+    if not (os.path.exists(REF_ROOM) and os.path.exists(ref_exe)):
+        pytest.skip("needs oracle/_ref (reference scene files + the reference CUDA build)")
+    want, got = str(tmp_path / "ref.bin"), str(tmp_path / "got.bin")
+    subprocess.run([ref_exe, REF_ROOM, "--iters", "3", "--out", want], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run([EXE, REF_ROOM, "--iters", "3", "--batch", "1", "--no-png", "--sum-out", got], check=True,
+                   stdout=subprocess.DEVNULL)
+    a, b = np.fromfile(want, dtype=np.float32), np.fromfile(got, dtype=np.float32)
+    assert a.size == 1200 * 1200 * 3 and bits_equal(a, b)
+    assert np.count_nonzero(a) > a.size // 4            # a real picture, not two black frames
 
 
 @pytest.mark.gpu
