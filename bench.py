@@ -315,6 +315,11 @@ def run_own(args, rank, world, local_rank):
         if world > 1:
             dist.destroy_process_group()
         return
+    traffic = None      # DRAM bytes per k_bounce launch from the committed ncu capture of this workload
+    try:
+        traffic = json.load(open(os.path.join(REPO, "profiles", "k_bounce_traffic.json")))["bytes_per_launch"]
+    except Exception:
+        pass
     alg_bytes = st["path_segments"] * ALG_BYTES_PER_SEGMENT + st["iterations"] * P * ALG_BYTES_PER_PIXEL_ITER
     achieved = alg_bytes / (bounce_ms * 1e-3) / 1e9 if bounce_ms > 0 else 0.0
     line = {
@@ -333,7 +338,8 @@ def run_own(args, rank, world, local_rank):
         "clocks": clocks,
         "roofline": {"kernel": "k_bounce (closest hit + shade + look-back compaction, one launch per bounce)",
                      "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "peak_kind": peak_kind, "traffic": None,
+                     "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic,
+                     "alg_bytes_per_launch": alg_bytes / bounce_n if bounce_n else None,
                      "avg_launch_ms": bounce_ms / bounce_n if bounce_n else None, "launches": bounce_n,
                      "share_of_step": bounce_ms / ms if ms > 0 else None,
                      "note": "algorithmic bytes = 96 B per path segment + 24 B per pixel per iteration; the kernel "

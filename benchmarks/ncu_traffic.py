@@ -1,0 +1,38 @@
+"""DRAM traffic per launch of k_bounce from an `ncu --set full` raw page (CSV):
+
+    python benchmarks/ncu_traffic.py gpurun_out/r5_k_bounce_raw.csv profiles/k_bounce_traffic.json
+
+The capture (benchmarks/profile_round.sh) holds the depth consecutive launches of ONE batch -- bounce 0 to
+depth-1 of the same iterations in flight -- so their mean is the per-launch figure bench.py's
+roofline.achieved is quoted per (algorithmic bytes / launch vs dram__bytes_read.sum + dram__bytes_write.sum)."""
+import csv
+import json
+import sys
+
+
+def to_bytes(v, unit):
+    return float(v.replace(",", "")) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+
+
+def main(src, dst):
+    rows = list(csv.reader(open(src)))
+    hdr, units = rows[0], rows[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    per = []
+    for r in rows[2:]:
+        if "k_bounce" not in r[col["Kernel Name"]]:
+            continue
+        rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
+        wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
+        per.append({"read": rd, "write": wr, "us": float(r[col["gpu__time_duration.sum"]].replace(",", ""))})
+    out = {"kernel": "k_bounce", "launches": len(per),
+           "bytes_per_launch": sum(p["read"] + p["write"] for p in per) / len(per),
+           "per_launch": per, "source": src,
+           "how": "ncu --set full --clock-control none, dram__bytes_read.sum + dram__bytes_write.sum, mean over the "
+                  "consecutive launches of one batch (bounce 0..depth-1)"}
+    json.dump(out, open(dst, "w"), indent=1)
+    print(json.dumps({k: out[k] for k in ("launches", "bytes_per_launch")}))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2])

@@ -29,7 +29,7 @@ def diff_report(name, a, b):
 def main():
     scene_name, it = sys.argv[1], int(sys.argv[2])
     flags = sys.argv[3:]
-    scene_bin = os.path.join(REPO, "tests/golden", scene_name + ".scene.bin")
+    scene_bin = scene_name if scene_name.endswith(".bin") else os.path.join(REPO, "tests/golden", scene_name + ".scene.bin")
     sc = pt.Scene.from_pod_file(scene_bin)
     r = pt.Renderer(sc)
     g = pt.GuiDataContainer()

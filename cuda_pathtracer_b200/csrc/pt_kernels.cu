@@ -641,26 +641,16 @@ struct alignas(16) PersistShared {
 };
 static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it must stay 16-byte aligned");
 
+// Four CTAs per SM (64 registers; ptxas spills 12 words into the otherwise unused local frame) instead of the
+// three that the natural 74 registers allow: +4.8 % path segments/s on the Cornell box (profiles/r5_ab_variants.txt).
+// A cp.async prefetch of the next tile's paths, tried at the same time, changed nothing at 3 CTAs and lost 1 % at 4.
 #ifndef PT_BOUNCE_MIN_CTAS
-#define PT_BOUNCE_MIN_CTAS 1
+#define PT_BOUNCE_MIN_CTAS 4
 #endif
 #ifndef PT_LB_K
 #define PT_LB_K 1
 #endif
-// PT_PREFETCH: the paths of the CTA's next tile are fetched into shared memory with cp.async (LDGSTS: no
-// registers held while in flight) as soon as the next work item is known, i.e. during the write-out of the
-// previous tile's survivors; every thread fetches and later reads only its own three words, so no
-// barrier is involved.  The second 3 * PT_PTILE float4 of the stash area hold them.
-#ifndef PT_PREFETCH
-#define PT_PREFETCH 1
-#endif
-constexpr size_t PT_STASH_BYTES = (size_t)(PT_PREFETCH ? 6 : 3) * PT_PTILE * sizeof(float4);
-
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+constexpr size_t PT_STASH_BYTES = (size_t)3 * PT_PTILE * sizeof(float4);
 
 
 // work item w -> (slot, tile); one thread
@@ -736,7 +726,6 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
 
     // ---- the compute warps ----
     float4* my_stash = stash + warp * 32;            // + k * PT_PTILE for word k of the path
-    float4* pre = stash + 3 * PT_PTILE;              // prefetched paths of the next tile (PT_PREFETCH)
     int prev_cnt = 0, prev_off = 0, prev_slot = 0;
     int it = 0;
     for (;; ++it) {
@@ -745,16 +734,7 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
         const int n_live = sh.n_live[slot];
         const int idx = tile * PT_PTILE + threadIdx.x;
         const bool active = idx < n_live;
-        PathState s;
-        if (PT_PREFETCH && it > 0) {
-            cp_async_wait_all();                      // this thread's own copies, issued one tile ago
-            const float4 a = pre[threadIdx.x], b = pre[PT_PTILE + threadIdx.x], c = pre[2 * PT_PTILE + threadIdx.x];
-            s.o = v3(a.x, a.y, a.z);  s.pixel = __float_as_int(a.w);
-            s.d = v3(b.x, b.y, b.z);  s.remaining = __float_as_int(b.w);
-            s.c = v3(c.x, c.y, c.z);  s.bounces = __float_as_int(c.w);
-        } else {
-            s = load_path(p.in, (size_t)slot * p.P + (active ? idx : 0));
-        }
+        PathState s = load_path(p.in, (size_t)slot * p.P + (active ? idx : 0));
 
         HitRec h;
         if (CACHE == 2) {
@@ -787,16 +767,6 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
         if (lane == 0) sh.warp_cnt[it & 1][warp] = cnt;
         if (threadIdx.x == 0) put_item(sh, next_w, (it + 1) & 1);
         asm volatile("bar.sync 1, %0;" ::"n"(PT_PTILE) : "memory");
-        if (PT_PREFETCH) {                            // the next tile's paths, now that the work item is known
-            const int nslot = sh.item[(it + 1) & 1][0], ntile = sh.item[(it + 1) & 1][1];
-            if (nslot >= 0) {
-                const int nidx = ntile * PT_PTILE + threadIdx.x;
-                const size_t at = (size_t)nslot * p.P + (nidx < sh.n_live[nslot] ? nidx : 0);
-                cp_async16(&pre[threadIdx.x], &p.in.a[at]);
-                cp_async16(&pre[PT_PTILE + threadIdx.x], &p.in.b[at]);
-                cp_async16(&pre[2 * PT_PTILE + threadIdx.x], &p.in.c[at]);
-            }
-        }
         int warp_prefix = 0, aggregate = 0;
 #pragma unroll
         for (int w = 0; w < PT_PWARPS; ++w) {
