@@ -142,6 +142,249 @@ static void run_compact(Env& e)
 }
 
 
+namespace b200 {
+namespace sct {
+// ------------------------------------------------------------------------------------------------
+// EXPERIMENT (kept in the tuner only, not in the library): persistent, software-pipelined forms of the two
+// single-pass kernels.  Result on a B200 at 2^28 (profiles/r8_sc_tune_persist.jsonl): bit-exact but SLOWER than
+// one tile per CTA -- scan 0.42 ms vs 0.39, compact 0.53 vs 0.40: the static round-robin keeps all CTAs in
+// lockstep (everybody loads, then everybody stores), and a CTA still has at most one tile in flight.
+//
+// In the one-tile-per-CTA kernels above a CTA's life is load -> local scan -> look-back -> store, and
+// nothing of that CTA is in flight from HBM while its warp 0 waits for the predecessors' descriptors
+// (the predecessors started at about the same time, so that wait is a sizeable part of the life:
+// the same scan WITHOUT the look-back streams at 6.8 TB/s, with it at 5.4, profiles/r1_sc_tune_v3).
+// Here the grid is as many CTAs as are resident at once and CTA c owns tiles c, c + G, c + 2G, ...
+// The input of the CTA's NEXT tile is fetched with cp.async (LDGSTS: no registers held while in
+// flight) into one of two shared-memory landing buffers at the top of every iteration, so the whole
+// iteration -- look-back wait included -- overlaps that fetch.  Every thread fetches, and later
+// reads, only its own vectors of the landing buffer: no barrier is involved in the hand-over.
+// Forward progress: a tile's predecessors are owned by CTAs that are all resident and work their own
+// tiles off in ascending order, and a CTA publishes the aggregate of a tile before it looks back.
+// The last (partial) tile, and unaligned pointers, take the guarded synchronous load instead.
+// dynamic shared memory: 2 * C::tile ints.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <class C>
+constexpr size_t persist_smem_bytes() { return (size_t)2 * C::tile * sizeof(int); }
+
+// fetch of `tile` (known to be full, pointers 16-byte aligned) into landing buffer `buf`
+template <class C>
+__device__ __forceinline__ void prefetch_tile(const int* __restrict__ in, unsigned tile, int warp, int lane, int4* buf)
+{
+    const int4* p = reinterpret_cast<const int4*>(in + (unsigned long long)tile * C::tile + warp * (32 * C::items)) + lane;
+#pragma unroll
+    for (int j = 0; j < C::vec; ++j) cp_async16(buf + j * C::threads + threadIdx.x, p + j * 32);
+}
+
+template <class C, bool VEC_OK, int LBW, int BACKOFF = LB_DEFAULT_BACKOFF_NS, int STRIDE = 1>
+__global__ void __launch_bounds__(C::threads)
+k_scan_persist(const int* __restrict__ in, int* __restrict__ out, unsigned n,
+               unsigned long long* __restrict__ desc, unsigned epoch, const int* __restrict__ d_seed,
+               int* __restrict__ d_total)
+{
+    extern __shared__ __align__(16) int4 landing[];          // [2][C::vec][C::threads]
+    __shared__ ScanSmem<C> sm;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + C::tile - 1) / C::tile);
+    const int seed = d_seed ? __ldg(d_seed) : 0;
+    bool fetched = false;
+    int cur = 0;
+    for (unsigned tile = blockIdx.x; tile < tiles; tile += gridDim.x, cur ^= 1) {
+        int4 v[C::vec];
+        if (fetched) {
+            cp_async_wait_all();
+            const int4* b = landing + cur * (C::vec * C::threads);
+#pragma unroll
+            for (int j = 0; j < C::vec; ++j) v[j] = b[j * C::threads + threadIdx.x];
+        } else {
+            load_tile<C, VEC_OK>(in, n, tile, warp, lane, v);
+        }
+        const unsigned long long next = (unsigned long long)tile + gridDim.x;
+        fetched = VEC_OK && (next + 1ull) * C::tile <= n;
+        if (fetched) prefetch_tile<C>(in, (unsigned)next, warp, lane, landing + (cur ^ 1) * (C::vec * C::threads));
+
+        int s[C::vec], excl[C::vec];
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j) s[j] = v[j].x + v[j].y + v[j].z + v[j].w;
+        tile_warp_totals<C>(s, sm.warp_sums, warp, lane);
+        __syncthreads();
+        if (warp == 0) {                 // publish + look back first; the other warps scan meanwhile
+            int aggregate = 0;
+#pragma unroll
+            for (int w = 0; w < C::warps; ++w) aggregate += sm.warp_sums[w];
+            const int e = lb_exclusive_prefix_cfg<LBW, BACKOFF, STRIDE>(desc, tile, epoch, aggregate, seed, lane);
+            if (lane == 0) {
+                sm.tile_exclusive = e;
+                if (d_total && tile == tiles - 1) *d_total = e + aggregate;
+            }
+        }
+        tile_exclusive_from_totals<C>(s, excl, sm.warp_sums, warp, lane);
+        __syncthreads();
+        const int tile_exclusive = sm.tile_exclusive;
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j) v[j] = scan_vec(v[j], tile_exclusive + excl[j]);
+        store_tile<C, VEC_OK>(out, n, tile, warp, lane, v);
+    }
+}
+
+// dynamic shared memory: 2 * C::tile ints (landing buffers) + C::tile ints (the packed survivors)
+template <class C>
+constexpr size_t compact_persist_smem_bytes() { return (size_t)3 * C::tile * sizeof(int); }
+
+template <class C, bool VEC_OK, int LBW, int BACKOFF = LB_DEFAULT_BACKOFF_NS, int STRIDE = 1>
+__global__ void __launch_bounds__(C::threads)
+k_compact_persist(const int* __restrict__ in, int* __restrict__ out, unsigned n,
+                  unsigned long long* __restrict__ desc, unsigned epoch, int* __restrict__ d_count)
+{
+    extern __shared__ __align__(16) int4 landing[];          // [2][C::vec][C::threads], then packed[C::tile]
+    int* packed = reinterpret_cast<int*>(landing + 2 * C::vec * C::threads);
+    __shared__ ScanSmem<C> sm;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + C::tile - 1) / C::tile);
+    bool fetched = false;
+    int cur = 0;
+    for (unsigned tile = blockIdx.x; tile < tiles; tile += gridDim.x, cur ^= 1) {
+        int4 v[C::vec];
+        if (fetched) {
+            cp_async_wait_all();
+            const int4* b = landing + cur * (C::vec * C::threads);
+#pragma unroll
+            for (int j = 0; j < C::vec; ++j) v[j] = b[j * C::threads + threadIdx.x];
+        } else {
+            load_tile<C, VEC_OK>(in, n, tile, warp, lane, v);   // out-of-range reads as 0 == dropped
+        }
+        const unsigned long long next = (unsigned long long)tile + gridDim.x;
+        fetched = VEC_OK && (next + 1ull) * C::tile <= n;
+        if (fetched) prefetch_tile<C>(in, (unsigned)next, warp, lane, landing + (cur ^ 1) * (C::vec * C::threads));
+
+        int s[C::vec], excl[C::vec];
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j)
+            s[j] = (v[j].x != 0) + (v[j].y != 0) + (v[j].z != 0) + (v[j].w != 0);
+        tile_warp_totals<C>(s, sm.warp_sums, warp, lane);
+        __syncthreads();                                     // (also: everybody is done with the previous tile's `packed`)
+        int kept = 0;
+#pragma unroll
+        for (int w = 0; w < C::warps; ++w) kept += sm.warp_sums[w];
+        if (warp == 0) {
+            const int e = lb_exclusive_prefix_cfg<LBW, BACKOFF, STRIDE>(desc, tile, epoch, kept, 0, lane);
+            if (lane == 0) {
+                sm.tile_exclusive = e;
+                if (tile == tiles - 1) *d_count = e + kept;
+            }
+        }
+        tile_exclusive_from_totals<C>(s, excl, sm.warp_sums, warp, lane);
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j) {
+            int p = excl[j];
+            if (v[j].x != 0) packed[p++] = v[j].x;
+            if (v[j].y != 0) packed[p++] = v[j].y;
+            if (v[j].z != 0) packed[p++] = v[j].z;
+            if (v[j].w != 0) packed[p++] = v[j].w;
+        }
+        __syncthreads();
+        const int base = sm.tile_exclusive;
+        int* dst = out + base;
+        // head: up to 3 elements until dst + head is 16-byte aligned; body: int4; tail: scalars
+        const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
+        int head = mis ? 4 - mis : 0;
+        if (head > kept) head = kept;
+        if ((int)threadIdx.x < head) dst[threadIdx.x] = packed[threadIdx.x];
+        const int body4 = (kept - head) >> 2;
+        int4* dst4 = reinterpret_cast<int4*>(dst + head);
+        for (int q = threadIdx.x; q < body4; q += C::threads) {
+            const int* src = packed + head + 4 * q;
+            st_stream(dst4 + q, make_int4(src[0], src[1], src[2], src[3]));
+        }
+        const int done = head + 4 * body4;
+        if ((int)threadIdx.x < kept - done) dst[done + threadIdx.x] = packed[done + threadIdx.x];
+    }
+}
+
+}  // namespace sct
+}  // namespace b200
+
+// ---- persistent, software-pipelined kernels (k_scan_persist / k_compact_persist) ---------------------
+// ctas_per_sm_cap: 0 = as many as fit, else at most that many (fewer, fatter streams)
+template <int TH, int VEC, int STRIDE>
+static void run_scan_persist(Env& e, int ctas_per_sm_cap)
+{
+    using C = sct::Cfg<TH, VEC>;
+    const unsigned tiles = (unsigned)(((unsigned long long)e.n + C::tile - 1) / C::tile);
+    auto k = sct::k_scan_persist<C, true, 1, 0, STRIDE>;
+    const size_t smem = sct::persist_smem_bytes<C>();
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    int occ = 0, sms = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, TH, smem));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    int per_sm = occ;
+    if (ctas_per_sm_cap > 0 && per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
+    unsigned grid = (unsigned)(sms * per_sm);
+    if (grid > tiles) grid = tiles;
+    CK(cudaMemset(e.d_out, 0xff, (size_t)e.n * 4));
+    auto launch = [&] {
+        e.epoch += 1;
+        k<<<grid, TH, smem>>>(e.d_in, e.d_out, e.n, e.desc, e.epoch, nullptr, e.d_small);
+    };
+    const float ms = median_ms(e, launch);
+    const bool ok = same(e, e.d_out, e.d_want_scan, e.n);
+    printf("{\"op\": \"scan_persist\", \"threads\": %d, \"vec\": %d, \"tile_ints\": %d, \"desc_stride\": %d, \"regs\": %d, "
+           "\"ctas_per_sm\": %d, \"occ\": %d, \"grid\": %u, \"smem\": %zu, \"ms\": %.4f, \"gbs\": %.1f, \"ok\": %s}\n",
+           TH, VEC, C::tile, STRIDE, fa.numRegs, per_sm, occ, grid, smem, ms, 8.0 * e.n / ms / 1e6, ok ? "true" : "false");
+    fflush(stdout);
+}
+
+template <int TH, int VEC, int STRIDE>
+static void run_compact_persist(Env& e, int ctas_per_sm_cap)
+{
+    using C = sct::Cfg<TH, VEC>;
+    const unsigned tiles = (unsigned)(((unsigned long long)e.n + C::tile - 1) / C::tile);
+    auto k = sct::k_compact_persist<C, true, 1, 0, STRIDE>;
+    const size_t smem = sct::compact_persist_smem_bytes<C>();
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    int occ = 0, sms = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, TH, smem));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    int per_sm = occ;
+    if (ctas_per_sm_cap > 0 && per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
+    unsigned grid = (unsigned)(sms * per_sm);
+    if (grid > tiles) grid = tiles;
+    CK(cudaMemset(e.d_out, 0xff, (size_t)e.n * 4));
+    auto launch = [&] {
+        e.epoch += 1;
+        k<<<grid, TH, smem>>>(e.d_flags, e.d_out, e.n, e.desc, e.epoch, e.d_small);
+    };
+    const float ms = median_ms(e, launch);
+    int count = -1;
+    CK(cudaMemcpy(&count, e.d_small, 4, cudaMemcpyDeviceToHost));
+    const bool ok = count == e.want_count && same(e, e.d_out, e.d_want_compact, (unsigned)e.want_count);
+    printf("{\"op\": \"compact_persist\", \"threads\": %d, \"vec\": %d, \"tile_ints\": %d, \"desc_stride\": %d, \"regs\": %d, "
+           "\"ctas_per_sm\": %d, \"occ\": %d, \"grid\": %u, \"smem\": %zu, \"ms\": %.4f, \"gbs\": %.1f, \"ok\": %s}\n",
+           TH, VEC, C::tile, STRIDE, fa.numRegs, per_sm, occ, grid, smem, ms, (4.0 * e.n + 4.0 * e.want_count) / ms / 1e6,
+           ok ? "true" : "false");
+    fflush(stdout);
+}
+
+template <int TH, int VEC>
+static void run_persist_cfg(Env& e)
+{
+    for (int cap : {0, 4, 2}) {
+        run_scan_persist<TH, VEC, 16>(e, cap);
+        run_compact_persist<TH, VEC, 16>(e, cap);
+    }
+}
+
 // ---- phase trace of the single-pass scan: where does a tile's lifetime go? ---------------------
 __device__ __forceinline__ unsigned long long gtime()
 {
@@ -320,6 +563,18 @@ int main(int argc, char** argv)
         auto launch2 = [&] { CK(cudaMemcpyAsync(e.d_out, e.d_in, bytes, cudaMemcpyDeviceToDevice)); };
         const float ms2 = median_ms(e, launch2);
         printf("{\"op\": \"cudaMemcpyD2D\", \"ms\": %.4f, \"gbs\": %.1f}\n", ms2, 8.0 * e.n / ms2 / 1e6);
+    }
+    if (argc > 3 && std::string(argv[3]) == "persist") {      // benchmarks/sc_tune 28 10 persist
+        run_scan<128, 8, 1, false, 0, 16>(e);                 // the one-tile-per-CTA kernels the library used so far
+        run_compact<256, 8, 1, false, 0, 16>(e);
+        run_persist_cfg<128, 8>(e);
+        run_persist_cfg<256, 4>(e);
+        run_persist_cfg<256, 8>(e);
+        run_persist_cfg<128, 4>(e);
+        run_persist_cfg<512, 4>(e);
+        run_persist_cfg<64, 8>(e);
+        run_persist_cfg<128, 16>(e);
+        return 0;
     }
     if (argc > 3) {                      // trace mode: benchmarks/sc_tune 28 10 out_prefix
         const std::string pre = argv[3];
