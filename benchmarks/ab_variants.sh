@@ -24,5 +24,14 @@ except Exception as e:
     print(sys.argv[2], "no result:", e)
 PY
   done
+  if [ -n "$AB_CONFIGS" ]; then      # also the heavier configurations of benchmarks/pt_configs.py, e.g. AB_CONFIGS="config5|N3 mesh_room 1200"
+    IFS='|' read -ra cfgs <<< "$AB_CONFIGS"
+    for c in "${cfgs[@]}"; do
+      timeout 300 python benchmarks/pt_configs.py --only "$c" --no-ref 2>> $out/${tag}_ab_${v}.err | python -c "
+import json,sys
+for l in sys.stdin:
+    d=json.loads(l); print('$v', d['config'][:28], 'spp/s %.1f  Mseg/s %.1f' % (d['b200']['spp_per_s'], d['b200']['mseg_per_s']))"
+    done
+  fi
 done
 cp /tmp/libb200pt.keep cuda_pathtracer_b200/libb200pt.so
