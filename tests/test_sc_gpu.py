@@ -189,3 +189,58 @@ def test_full_size_2p28(sc, delta):
     assert int(cnt.item()) == keep.numel()
     assert torch.equal(out[: keep.numel()], keep)
     ctx.close()
+
+
+@pytest.mark.parametrize("delta", [0, 3])
+def test_max_size_2p30(sc, delta):
+    """Largest size of BASELINE config 3 (2^30 and 2^30-3 ints, 4 GiB per array): bit-exact against the
+    closed form, and the size-independent properties -- out[i+1] - out[i] == in[i] (mod 2^32) for every
+    i, total == sum, compaction keeps order and is idempotent."""
+    import torch
+    n = (1 << 30) - delta
+    g = torch.Generator(device="cuda").manual_seed(566)
+    a = torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda", generator=g)
+    out = torch.empty_like(a)
+    total = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ctx = sc.Context()
+    ctx.scan(n, out, a, sc.LOOKBACK, d_total=total)
+    torch.cuda.synchronize()
+    assert int(out[0].item()) == 0
+    assert torch.equal(out[1:] - out[:-1], a[:-1])                  # int32 arithmetic wraps on both sides
+    assert int(total.item()) == int(np.int64(a.sum(dtype=torch.int64).item()).astype(np.int32))
+    want = torch.cumsum(a, 0, dtype=torch.int64)
+    want -= a
+    assert torch.equal(out, want.to(torch.int32))
+    del want
+    a %= 4
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ctx.compact(n, out, a, cnt)
+    torch.cuda.synchronize()
+    k = int(cnt.item())
+    assert k == int((a != 0).sum().item())
+    assert torch.equal(out[:k], a[a != 0])
+    once = out[:k].clone()
+    ctx.compact(k, a, once, cnt)                                     # compacting a compacted array changes nothing
+    torch.cuda.synchronize()
+    assert int(cnt.item()) == k and torch.equal(a[:k], once)
+    ctx.close()
+
+
+def test_scan_is_linear_and_shift_consistent(sc):
+    """scan(x + y) == scan(x) + scan(y) (mod 2^32); scan of a shifted array is the shifted scan minus its head"""
+    import torch
+    n = (1 << 22) + 77
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randint(-2**31, 2**31 - 1, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    y = torch.randint(-2**31, 2**31 - 1, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    ctx = sc.Context()
+    sx, sy, sxy, sh = (torch.empty_like(x) for _ in range(4))
+    for variant in (sc.LOOKBACK, sc.EFFICIENT):
+        ctx.scan(n, sx, x, variant)
+        ctx.scan(n, sy, y, variant)
+        ctx.scan(n, sxy, x + y, variant)
+        ctx.scan(n - 5, sh, x[5:].contiguous(), variant)
+        torch.cuda.synchronize()
+        assert torch.equal(sxy, sx + sy)
+        assert torch.equal(sh[: n - 5], sx[5:] - sx[5])
+    ctx.close()
