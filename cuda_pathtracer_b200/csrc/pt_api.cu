@@ -113,6 +113,11 @@ void pack_prim(const b200pt_geom& g, PrimRec& r)
     r.material = g.materialid;
     r.pad0 = g.type == B200PT_MESH ? g.tri_start_idx : 0;     // a MESH owns the triangle ids [pad0, pad1)
     r.pad1 = g.type == B200PT_MESH ? g.tri_end_idx : 0;
+    if (g.type == B200PT_MESH)                                // its vertices are already in world space: `fwd` is free and
+        for (int a = 0; a < 3; ++a) {                         // carries the world bounds meshIntersectionTest culls with
+            r.fwd[a] = g.min_bound[a];
+            r.fwd[3 + a] = g.max_bound[a];
+        }
 }
 
 int default_batch(int P)
@@ -423,6 +428,8 @@ void b200pt_default_options(b200pt_options* o)
     o->first_bounce_cache = 0;
     o->batch = 0;
     o->geom_bvh = 0;
+    o->mesh_brute_force = 0;
+    o->mesh_no_bbox = 0;
 }
 
 int b200pt_create(const b200pt_scene* sc, b200pt** out) { return b200pt_create_ext(sc, nullptr, out); }
@@ -494,7 +501,8 @@ int b200pt_set_options(b200pt* h, const b200pt_options* o)
 {
     if (!h || !o || o->batch < 0 || o->batch > PT_MAX_BATCH || o->geom_bvh < -1 || o->geom_bvh > 1) return B200_E_BADARG;
     // the cached first-bounce hits depend on the camera rays: any change of what shapes them drops the cache
-    if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache)
+    if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache ||
+        o->mesh_brute_force != h->opt.mesh_brute_force || o->mesh_no_bbox != h->opt.mesh_no_bbox)
         h->cache_valid = false;
     h->opt = *o;
     return 0;
@@ -574,7 +582,10 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.mats = h->d_mats;
     p.n_prims = h->n_prims;
     p.n_mats = h->n_mats;
-    if (h->gb.n_nodes > 0 && (h->opt.geom_bvh > 0 || (h->opt.geom_bvh == 0 && h->n_indexed >= PT_GBVH_AUTO))) p.gb = h->gb;
+    // meshIntersectionTest instead of the BVH walk: the reference's own loop over all primitives (the geometry
+    // BVH handles MESH primitives through the one shared walk, which this mode does not have)
+    const bool brute = h->opt.mesh_brute_force != 0 && h->mesh.n_tris > 0;
+    if (!brute && h->gb.n_nodes > 0 && (h->opt.geom_bvh > 0 || (h->opt.geom_bvh == 0 && h->n_indexed >= PT_GBVH_AUTO))) p.gb = h->gb;
     p.cam = h->cam;
     p.opt.rr = h->opt.russian_roulette;
     p.opt.ssaa = h->opt.ssaa;
@@ -601,6 +612,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.hit_uv = h->d_hit_uv;
     p.cache_uv = h->d_cache_uv;
     p.mesh = h->mesh;
+    p.mesh.brute = brute ? (h->opt.mesh_no_bbox ? 2 : 1) : 0;
 
     CK(cudaEventRecord(h->ev0, s));
     for (int done = 0; done < n_iters; done += batch) {
@@ -754,7 +766,9 @@ int b200pt_debug_intersect(b200pt* h, int n, const void* d_segments, void* d_ise
 {
     if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
     if (n == 0) return 0;
-    CK(launch_debug_intersect(h->d_prims, h->n_prims, h->mesh, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
+    MeshScene mesh = h->mesh;
+    mesh.brute = h->opt.mesh_brute_force != 0 && mesh.n_tris > 0 ? (h->opt.mesh_no_bbox ? 2 : 1) : 0;
+    CK(launch_debug_intersect(h->d_prims, h->n_prims, mesh, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
     h->launches += 1;
     return 0;
 }

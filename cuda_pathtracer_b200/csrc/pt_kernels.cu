@@ -78,21 +78,52 @@ struct BounceShared {
 // closest hit over the primitives [0, n) of `sp`, global indices base..base+n-1
 // A MESH primitive's candidate is the BVH hit if the hit triangle belongs to it (pathtrace.cu:262-272).
 // `owner` records the first MESH primitive that accepted the hit.
+// M.brute (useBVHtree == false, pathtrace.cu:273-275): every MESH primitive runs meshIntersectionTest instead;
+// `last` is what tmp_normal / tmp_coord hold (written only by a mesh test that hits) and `mh` what the current
+// winner copied from them -- so a sphere / cube winner carries the texture coordinate of the LAST mesh
+// primitive before it that was hit.
 __device__ __forceinline__ void closest_in_chunk(const PrimRec* __restrict__ sp, int n, int base, const V3& o,
-                                                 const V3& d, const MeshHit& mh, float& t_min, int& hit, Cand& best,
-                                                 int& owner)
+                                                 const V3& d, const MeshScene& M, MeshHit& mh, MeshHit& last, float& t_min,
+                                                 int& hit, Cand& best, int& owner)
 {
     for (int i = 0; i < n; ++i) {
         Cand c = prim_test(sp[i], o, d);
-        if (sp[i].type == 2 && mh.any && mh.id >= sp[i].pad0 && mh.id < sp[i].pad1) {
-            c.t = mh.t;
-            if (owner < 0) owner = base + i;
+        if (sp[i].type == 2) {
+            if (M.brute) {
+                MeshHit h;
+                if (mesh_brute(M, sp[i], o, d, h)) { last = h; c.t = h.t; }
+            } else if (mh.any && mh.id >= sp[i].pad0 && mh.id < sp[i].pad1) {
+                c.t = mh.t;
+                if (owner < 0) owner = base + i;
+            }
         }
         if (c.t > 0.0f && t_min > c.t) {    // strict: the lowest index wins ties (pathtrace.cu:280)
             t_min = c.t;
             hit = base + i;
             best = c;
+            if (M.brute) mh = last;
         }
+    }
+}
+
+// normal / texture coordinate of the winner `g` (scene index `hit`), pathtrace.cu:283-296
+__device__ __forceinline__ void hit_attributes(const MeshScene& M, const PrimRec& g, int hit, const Cand& best, const MeshHit& mh,
+                                               int owner, V3& n, float& u, float& v)
+{
+    if (M.brute) {
+        if (g.type == 2) {
+            brute_attributes(M.ta[mh.tri], mh.bx, mh.by, n, u, v);
+        } else {
+            n = prim_normal(g, best);
+            if (mh.tri >= 0) { V3 unused; brute_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
+        }
+    } else if (g.type == 2) {
+        tri_attributes(M.ta[mh.tri], mh.bx, mh.by, n, u, v);
+    } else {
+        n = prim_normal(g, best);
+        // (sic) a sphere / cube winning AFTER a mesh primitive accepted the BVH hit carries that
+        // hit's stale texture coordinate (pathtrace.cu:267,283)
+        if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
     }
 }
 
@@ -421,7 +452,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-    MeshHit mh = no_mesh_hit();
+    MeshHit mh = no_mesh_hit(), last = no_mesh_hit();
     int owner = -1;
     if (GB || p.mesh.n_nodes > 0) mbar_wait(&bar[0], 0u);     // the staged top(s) of the tree(s)
     // A ray whose direction is NaN (glm::refract past the critical angle, interactions.cu:68) hits
@@ -439,14 +470,14 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
             mh = bvh_traverse(p.mesh, snodes, o, d, cap);       // one traversal serves every MESH primitive
             closest_among_mesh_prims(p, mh, t_min, hit, owner);
         }
-    } else if (p.mesh.n_nodes > 0 && walk) {
+    } else if (p.mesh.n_nodes > 0 && walk && !p.mesh.brute) {
         mh = bvh_traverse(p.mesh, snodes, o, d);
     }
     for (int ch = 0; ch < n_chunks; ++ch) {
         mbar_wait(&bar[ch & 1], (unsigned)((ch >> 1) & 1));
         const int n = min(PT_CHUNK, p.n_prims - ch * PT_CHUNK);
         const PrimRec* sp = sprims + (n_chunks > 1 ? (ch & 1) * PT_CHUNK : 0);
-        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, mh, t_min, hit, best, owner);
+        if (active) closest_in_chunk(sp, n, ch * PT_CHUNK, o, d, p.mesh, mh, last, t_min, hit, best, owner);
         if (ch + 2 < n_chunks) {                     // refill this buffer with chunk ch + 2
             __syncthreads();
             if (threadIdx.x == 0) {
@@ -467,14 +498,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
         // (small-scene search: a MESH winner is not among the staged records -> hit_k stays behind)
         const bool staged = GB == 2 ? (hit_k >= 0 && sprims[hit_k].pad0 == hit) : (GB == 0 && n_chunks <= 1);
         const PrimRec& g = staged ? sprims[GB == 2 ? hit_k : hit] : p.prims[hit];
-        if (g.type == 2) {
-            tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, h.n, h.u, h.v);
-        } else {
-            h.n = prim_normal(g, best);
-            // (sic) a sphere / cube winning AFTER a mesh primitive accepted the BVH hit carries that
-            // hit's stale texture coordinate (pathtrace.cu:267,283)
-            if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(p.mesh.ta[mh.tri], mh.bx, mh.by, unused, h.u, h.v); }
-        }
+        hit_attributes(p.mesh, g, hit, best, mh, owner, h.n, h.u, h.v);
         h.t = t_min;
         h.mat = g.material;
     }
@@ -1027,20 +1051,16 @@ __global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restri
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
     mesh.n_smem_nodes = 0;
-    const MeshHit mh = mesh.n_nodes > 0 ? bvh_traverse(mesh, nullptr, s.o, s.d) : no_mesh_hit();
+    MeshHit mh = mesh.n_nodes > 0 && !mesh.brute ? bvh_traverse(mesh, nullptr, s.o, s.d) : no_mesh_hit();
+    MeshHit last = no_mesh_hit();
     int owner = -1;
-    closest_in_chunk(prims, n_prims, 0, s.o, s.d, mh, t_min, hit, best, owner);
+    closest_in_chunk(prims, n_prims, 0, s.o, s.d, mesh, mh, last, t_min, hit, best, owner);
     float* o = isects + 7 * (size_t)i;           // the reference memsets the record to 0 first
     V3 nn = v3(0.f, 0.f, 0.f);
     int mat = 0;
     float u = 0.f, v = 0.f;
     if (hit >= 0) {
-        if (prims[hit].type == 2) {
-            tri_attributes(mesh.ta[mh.tri], mh.bx, mh.by, nn, u, v);
-        } else {
-            nn = prim_normal(prims[hit], best);
-            if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(mesh.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
-        }
+        hit_attributes(mesh, prims[hit], hit, best, mh, owner, nn, u, v);
         mat = prims[hit].material;
     }
     o[0] = hit >= 0 ? t_min : -1.0f;

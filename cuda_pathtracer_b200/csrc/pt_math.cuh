@@ -268,7 +268,9 @@ struct MeshScene {
     const unsigned char* texels;
     int n_nodes, n_tris, n_tex, n_smem_nodes;
     int literal_walk;    // the tree is >= BVH_MAX_SEARCH_DEPTH levels deep: keep the reference's stack-overflow behaviour
-    int pad_[3];
+    int brute;           // GuiDataContainer::useBVHtree == false: 1 = meshIntersectionTest with its bounding-box cull
+                         // (useBBox), 2 = without; 0 = the BVH walk
+    int pad_[2];
 };
 
 struct MeshHit {
@@ -434,6 +436,42 @@ __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec
     }
     if (h.tri >= 0) h.id = M.tv[h.tri].id;
     return h;
+}
+
+// meshIntersectionTest (intersections.cu:120-167): what computeIntersections calls for a MESH primitive when
+// settings->use_BVHtree is false (pathtrace.cu:273-275).  Optional slab test against the primitive's world
+// bounds (kept in the otherwise unused `fwd` words of a MESH PrimRec), then EVERY triangle at positions
+// [pad0, pad1) of the (BVH-reordered, sic) triangle array: nearest positive distance, first one on a tie.
+// Arithmetic order from the reference build's SASS (_Z20meshIntersectionTest...): rcp.rn for 1/d, the slabs
+// as FADD then FMUL, the same ray / triangle code as the BVH path.
+__device__ __forceinline__ bool mesh_brute(const MeshScene& M, const PrimRec& g, const V3& o, const V3& d, MeshHit& h)
+{
+    if (M.brute == 1) {
+        const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+        float entry;
+        if (!bbox_hit(g.fwd, g.fwd + 3, o, inv, entry)) return false;
+    }
+    h.any = false; h.t = 3.402823466e+38f; h.tri = -1; h.id = -1; h.bx = 0.f; h.by = 0.f;
+    const int end = g.pad1 < M.n_tris ? g.pad1 : M.n_tris;
+    for (int at = g.pad0; at < end; ++at) {
+        float bx, by, bt;
+        if (tri_test(M.tv[at], o, d, bx, by, bt) && bt > 0.0f && bt < h.t) {
+            h.any = true; h.t = bt; h.tri = at; h.bx = bx; h.by = by;
+        }
+    }
+    return h.any;
+}
+
+// its attribute blend (sic, intersections.cu:160-164): actual_z * a0 + a1 + a2 -- not a barycentric one
+__device__ __forceinline__ void brute_attributes(const TriAttr& A, float bx, float by, V3& n, float& u, float& v)
+{
+    const float w = __fsub_rn(__fsub_rn(1.0f, bx), by);
+    const V3 m = v3(__fadd_rn(__fmaf_rn(w, A.n[0][0], A.n[1][0]), A.n[2][0]),
+                    __fadd_rn(__fmaf_rn(w, A.n[0][1], A.n[1][1]), A.n[2][1]),
+                    __fadd_rn(__fmaf_rn(w, A.n[0][2], A.n[1][2]), A.n[2][2]));
+    n = normalize_exact(m);
+    u = __fadd_rn(__fmaf_rn(w, A.uv[0][0], A.uv[1][0]), A.uv[2][0]);
+    v = __fadd_rn(__fmaf_rn(w, A.uv[0][1], A.uv[1][1]), A.uv[2][1]);
 }
 
 // Triangle::intersect's attribute interpolation for the closest hit (sceneStructs.h:152-154):

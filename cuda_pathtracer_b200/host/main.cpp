@@ -15,6 +15,8 @@
 //   --no-ssaa            SSAA = false                     --no-dof      DoF = false
 //   --aperture A         (default 0.1)                    --focal F     focal_len (default 10.0)
 //   --first-bounce-cache reuse bounce 0's hits (honoured only with --no-ssaa --no-dof)
+//   --no-bvh             useBVHtree = false: meshes through meshIntersectionTest (every triangle of a mesh)
+//   --no-bbox            useBBox = false: ... without its bounding-box cull
 //   --geom-bvh on|off|auto   closest hit over spheres / cubes through a BVH instead of the linear scan
 //                        (same image either way; auto = on)
 //   --batch B            iterations in flight (0 = library default, 1 = the reference's exact
@@ -115,6 +117,8 @@ int main(int argc, char** argv)
         else if (a == "--aperture") opt.aperture = (float)std::atof(next());
         else if (a == "--focal") opt.focal_len = (float)std::atof(next());
         else if (a == "--first-bounce-cache") opt.first_bounce_cache = 1;
+        else if (a == "--no-bvh") opt.mesh_brute_force = 1;       // GuiDataContainer::useBVHtree = false
+        else if (a == "--no-bbox") opt.mesh_no_bbox = 1;          // GuiDataContainer::useBBox = false
         else if (a == "--batch") opt.batch = std::atoi(next());
         else if (a == "--geom-bvh") {
             const std::string v = next();

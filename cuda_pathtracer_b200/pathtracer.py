@@ -77,7 +77,8 @@ class _OptionsC(ctypes.Structure):
     _fields_ = [("russian_roulette", ctypes.c_int32), ("sort_by_material", ctypes.c_int32),
                 ("ssaa", ctypes.c_int32), ("dof", ctypes.c_int32), ("aperture", ctypes.c_float),
                 ("focal_len", ctypes.c_float), ("first_bounce_cache", ctypes.c_int32),
-                ("batch", ctypes.c_int32), ("geom_bvh", ctypes.c_int32)]
+                ("batch", ctypes.c_int32), ("geom_bvh", ctypes.c_int32),
+                ("mesh_brute_force", ctypes.c_int32), ("mesh_no_bbox", ctypes.c_int32)]
 
 
 class _StatsC(ctypes.Structure):
@@ -226,7 +227,7 @@ class Renderer:
     def set_options(self, gui):
         o = _OptionsC(int(gui.russianRoulette), int(gui.sortbyMaterial), int(gui.SSAA), int(gui.DoF),
                       float(gui.aperture), float(gui.focal_len), int(gui.firstBounceCache), int(gui.batch),
-                      int(getattr(gui, "geomBVH", 0)))
+                      int(getattr(gui, "geomBVH", 0)), int(not gui.useBVHtree), int(not gui.useBBox))
         check(_lib().b200pt_set_options(self._h, ctypes.byref(o)))
 
     def reset(self):

@@ -148,6 +148,14 @@ typedef struct b200pt_options {
                                    (pathtrace.cu:247-290).  It only prunes primitives a ray cannot touch:
                                    the hit found -- hence the image -- is bit-identical either way.
                                    0 = automatic (on), 1 = always, -1 = never (the reference's loop). */
+    int32_t mesh_brute_force;   /* !GuiDataContainer::useBVHtree (utilities.h:24; default 0 = walk the BVH).
+                                   1: every MESH primitive runs the reference's meshIntersectionTest
+                                   (intersections.cu:120-167, pathtrace.cu:273-275) -- all triangles at positions
+                                   [tri_start_idx, tri_end_idx), its own (non-barycentric, sic) normal / uv blend.
+                                   The reference's GUI toggle for it is compiled out (preview.cpp:247-253); a host
+                                   that sets the field gets the reference's result for it, bit for bit. */
+    int32_t mesh_no_bbox;       /* !GuiDataContainer::useBBox (utilities.h:25; default 0): with mesh_brute_force,
+                                   skip the slab test against Geom::min_bound / max_bound */
 } b200pt_options;
 
 typedef struct b200pt b200pt;

@@ -82,6 +82,8 @@ void pathtrace(uchar4* pbo, int /*frame*/, int iter)
         o.dof = guiData->DoF;
         o.aperture = guiData->aperture;
         o.focal_len = guiData->focal_len;
+        o.mesh_brute_force = !guiData->useBVHtree;   // pathtrace.cu:49-50
+        o.mesh_no_bbox = !guiData->useBBox;
     }
     o.batch = 1;                          // one iteration per call, the reference's accumulation order
     check(b200pt_set_options(renderer, &o), "options");

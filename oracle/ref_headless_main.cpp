@@ -58,6 +58,8 @@ int main(int argc, char** argv)
         else if (a == "--sort") gui->sortbyMaterial = true;
         else if (a == "--thrust-partition") gui->useThrustPartition = true;
         else if (a == "--no-rr") gui->russianRoulette = false;
+        else if (a == "--no-bvh") gui->useBVHtree = false;
+        else if (a == "--no-bbox") gui->useBBox = false;
         else if (a == "--no-ssaa") gui->SSAA = false;
         else if (a == "--no-dof") gui->DoF = false;
         else if (a == "--aperture" && i + 1 < argc) gui->aperture = (float)atof(argv[++i]);

@@ -9,7 +9,7 @@
 //   ref_stage_probe raygen    SCENE.bin ITER OUT_segments.bin            [flags]
 //   ref_stage_probe intersect SCENE.bin IN_segments.bin OUT_isects.bin   [flags]
 //   ref_stage_probe shade     SCENE.bin ITER IN_segments.bin IN_isects.bin OUT_segments.bin [flags]
-//   flags: --no-ssaa --no-dof --no-rr --aperture A --focal F
+//   flags: --no-ssaa --no-dof --no-rr --no-bvh --no-bbox --aperture A --focal F
 // SCENE.bin is a "B2PTSCN1" dump (oracle/ref_scene_dump.cpp); segments are the reference's
 // 48-byte PathSegment, isects its 28-byte ShadeableIntersection.
 #include <cstdio>
@@ -137,6 +137,8 @@ int main(int argc, char** argv)
         if (a == "--no-ssaa") st.enable_SSAA = false;
         else if (a == "--no-dof") st.enable_DoF = false;
         else if (a == "--no-rr") st.enable_RussianRoulette = false;
+        else if (a == "--no-bvh") st.use_BVHtree = false;
+        else if (a == "--no-bbox") st.use_BoundingBoxTest = false;
         else if (a == "--aperture" && i + 1 < argc) st.aperture = (float)atof(argv[++i]);
         else if (a == "--focal" && i + 1 < argc) st.focal_dist = (float)atof(argv[++i]);
         else { fprintf(stderr, "unknown flag %s\n", a.c_str()); return 1; }

@@ -232,7 +232,7 @@ def mesh_assets():
     write_ppm("gradient.ppm", 48, 32, lambda x, y: (5 * x + 10, 7 * y + 20, (x * y) % 256))
 
 
-def mesh_room(res, iters, depth, name):
+def mesh_room(res, iters, depth, name, textured=True):
     mats = {
         "light": {"TYPE": "Emitting", "RGB": [1.0, 1.0, 1.0], "EMITTANCE": 12.0},
         "diffuse_white": {"TYPE": "Diffuse", "RGB": [0.98, 0.98, 0.98]},
@@ -244,6 +244,13 @@ def mesh_room(res, iters, depth, name):
         "mirror": {"TYPE": "Specular", "RGB": [0.98, 0.98, 0.98], "REFLECTIVE": 1.0},
         "plain_green": {"TYPE": "Diffuse", "RGB": [0.35, 0.85, 0.35]},
     }
+
+    if not textured:
+        # useBVHtree = false blends texture coordinates as az*uv0 + uv1 + uv2 (intersections.cu:164): they leave
+        # [0, 1] and the reference's Texture::get_color then reads outside the image (sceneStructs.h:175-188) --
+        # whole renders of that mode are only comparable without textures
+        for m in mats.values():
+            m.pop("TEXTURE_FILE", None)
 
     def mesh(mat, obj, t, r, s):
         return {"TYPE": "mesh", "MATERIAL": mat, "TRANS": t, "ROTAT": r, "SCALE": s, "OBJ_FILE": obj}
@@ -342,6 +349,7 @@ def main():
     mesh_assets()
     write("mesh_room.json", mesh_room((1200, 1200), 2000, 8, "mesh_room"))
     write("mesh_room_small.json", mesh_room((160, 160), 32, 8, "mesh_room_small"))
+    write("mesh_room_small_notex.json", mesh_room((160, 160), 32, 8, "mesh_room_small_notex", textured=False))
     stress_assets()
     write("mesh_stress.json", mesh_stress())
 

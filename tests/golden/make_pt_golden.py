@@ -28,6 +28,7 @@ SCENES = {
     "cornell_glass_1080p": ["--refract", "4", "1.5"],
     "synthetic_600_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
     "mesh_room_small": [],
+    "mesh_room_small_notex": [],
     "mesh_room": [],
     "mesh_stress": [],      # loader / BVH-builder stress (scenes/make_scenes.py stress_assets)
     "jpeg_textures": [],    # JPEG decoding parity with stb_image (scenes/make_jpeg_fixtures.py)
@@ -47,6 +48,10 @@ RENDERS = [
     # triangle meshes + BVH + textures (the room.json path)
     ("mesh_room_small", 8, [], "default"),
     ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
+    # useBVHtree = false (and useBBox = false): meshIntersectionTest instead of the BVH walk
+    # (untextured: that mode's texture coordinates leave [0, 1] and the reference then reads outside the image)
+    ("mesh_room_small_notex", 8, ["--no-bvh"], "nobvh"),
+    ("mesh_room_small_notex", 8, ["--no-bvh", "--no-bbox", "--sort", "--no-ssaa", "--no-dof"], "nobvhsort"),
 ]
 
 

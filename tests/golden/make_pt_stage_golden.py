@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(os.path.dirname(HERE))
 PROBE = os.path.join(REPO, "oracle", "_ref", "ref_stage_probe")
 CASES = [("cornell_tiny", 3, [], "default", 4), ("cornell_tiny", 5, ["--no-ssaa", "--no-dof", "--no-rr"], "plain", 3),
-         ("cornell_glass_small", 2, [], "default", 3), ("mesh_room_small", 2, [], "default", 4)]
+         ("cornell_glass_small", 2, [], "default", 3), ("mesh_room_small", 2, [], "default", 4),
+         ("mesh_room_small", 2, ["--no-bvh"], "nobvh", 2)]
 
 
 def probe(*args):

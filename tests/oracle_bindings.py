@@ -87,8 +87,13 @@ class PtOracle:
         self.lib = ctypes.CDLL(_ensure_built("_build/liboracle_pt.so"))
         self.lib.pt_oracle_render.restype = ctypes.c_ulonglong
 
-    def _set_mesh(self, scene):
-        """hand the scene's triangles / BVH / textures to the oracle (kept alive on self)"""
+    def _set_mesh(self, scene, gui=None):
+        """hand the scene's triangles / BVH / textures to the oracle (kept alive on self); gui.useBVHtree /
+        useBBox select the BVH walk (default) or meshIntersectionTest with / without its bounding-box cull"""
+        brute = 0
+        if gui is not None and not getattr(gui, "useBVHtree", True):
+            brute = 1 if getattr(gui, "useBBox", True) else 2
+        self.lib.pt_oracle_set_mesh_mode(brute)
         tris, bvh, texs = getattr(scene, "triangles", ()), getattr(scene, "bvh", ()), getattr(scene, "textures", [])
         dims = (ctypes.c_int * max(1, 3 * len(texs)))(*[v for t in texs for v in (t.width, t.height, t.components)])
         ptrs = (ctypes.c_void_p * max(1, len(texs)))(*[t.pixels.ctypes.data for t in texs])
@@ -121,10 +126,10 @@ class PtOracle:
                                   seg.ctypes.data_as(ctypes.c_void_p))
         return seg
 
-    def intersect(self, scene, segments):
+    def intersect(self, scene, segments, gui=None):
         segments = np.ascontiguousarray(segments, dtype=np.float32)
         out = np.zeros((len(segments), 7), dtype=np.float32)
-        self._set_mesh(scene)
+        self._set_mesh(scene, gui)
         self.lib.pt_oracle_intersect(scene.geoms, len(scene.geoms), len(segments),
                                      segments.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
         return out
@@ -144,7 +149,7 @@ class PtOracle:
             out = np.zeros((scene.height, scene.width, 3), dtype=np.float32)
         if threads is None:
             threads = os.cpu_count() or 1
-        self._set_mesh(scene)
+        self._set_mesh(scene, gui)
         seg = self.lib.pt_oracle_render(ctypes.byref(scene.camera), scene.traceDepth, scene.geoms, len(scene.geoms),
                                         scene.materials, o5, o2, int(first_iter), int(n_iters), int(stride),
                                         out.ctypes.data_as(ctypes.c_void_p), int(threads))

@@ -16,6 +16,7 @@ RENDERS = [
     ("cornell_glass_small", 16, [], "default"),
     ("synthetic_600_small", 4, [], "default"),
     ("mesh_room_small", 8, [], "default"),                # triangle meshes, BVH, textures
+    ("mesh_room_small_notex", 8, ["--no-bvh"], "nobvh"),  # useBVHtree = false: meshIntersectionTest
 ]
 # material sort on (thrust::sort_by_key in the reference, pathtrace.cu:479-491): the paths differ
 # from the unsorted ones because the shading seed is the slot index AFTER sorting
@@ -24,10 +25,12 @@ SORT_RENDERS = [
     ("synthetic_600_small", 4, ["--sort"], "sort"),
     ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
     ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
+    ("mesh_room_small_notex", 8, ["--no-bvh", "--no-bbox", "--sort", "--no-ssaa", "--no-dof"], "nobvhsort"),
 ]
 # per-stage vectors from the reference's own kernels (tests/golden/make_pt_stage_golden.py)
 STAGES = [("cornell_tiny", "default", []), ("cornell_tiny", "plain", ["--no-ssaa", "--no-dof", "--no-rr"]),
-          ("cornell_glass_small", "default", []), ("mesh_room_small", "default", [])]
+          ("cornell_glass_small", "default", []), ("mesh_room_small", "default", []),
+          ("mesh_room_small", "nobvh", ["--no-bvh"])]
 
 
 def load_scene(name):
@@ -40,8 +43,33 @@ def gui_from_flags(flags, batch=0):
     g.DoF = "--no-dof" not in flags
     g.russianRoulette = "--no-rr" not in flags
     g.sortbyMaterial = "--sort" in flags
+    g.useBVHtree = "--no-bvh" not in flags
+    g.useBBox = "--no-bbox" not in flags
     g.batch = batch
     return g
+
+
+def texture_reads_in_bounds(scene, isects):
+    """Rows of ShadeableIntersection records whose shading does NOT make the reference's Texture::get_color
+    read outside the image (sceneStructs.h:175-188 has no bounds check; this library clamps the index).  With
+    useBVHtree = false the texture coordinate is az*uv0 + uv1 + uv2 (intersections.cu:164), which leaves
+    [0, 1] -- what the reference shades there is whatever lies next to the texture in device memory."""
+    isects = np.ascontiguousarray(isects, dtype=np.float32)
+    ok = np.ones(len(isects), dtype=bool)
+    mat = isects[:, 4].view(np.int32)
+    for m, material in enumerate(scene.materials):
+        tid = material.texture_id
+        rows = (mat == m) & (isects[:, 0] > 0)
+        if tid < 0 or not rows.any():
+            continue
+        t = scene.textures[tid]
+        w, h = np.float32(t.width), np.float32(t.height)
+        u, v = isects[rows, 5], isects[rows, 6]
+        x = np.minimum(w * u, w - np.float32(1)).astype(np.int64)
+        y = np.minimum(h * (np.float32(1) - v), h - np.float32(1)).astype(np.int64)
+        idx = y * t.width + x
+        ok[rows] = (idx >= 0) & (idx < t.width * t.height)
+    return ok
 
 
 def ref_sum(scene, iters, tag, shape):

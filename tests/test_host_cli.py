@@ -22,7 +22,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
 SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
           "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096",
-          "mesh_room", "mesh_room_small", "mesh_stress",   # OBJ meshes + BVH + textures ("B2PTSCN2")
+          "mesh_room", "mesh_room_small", "mesh_room_small_notex", "mesh_stress",   # OBJ meshes + BVH + textures ("B2PTSCN2")
           "jpeg_textures"]   # twelve baseline JPEGs (scenes/make_jpeg_fixtures.py) decoded by host/jpeg.cpp vs stb_image
 
 
