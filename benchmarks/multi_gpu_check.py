@@ -8,6 +8,8 @@
   the exclusive prefix of the totals becomes the device-side seed of the rank's single-pass scan.
   Everything is stream-ordered on the device (no host round trip inside the timed region).
   Checked bit for bit against torch.cumsum (int32 wrap) of the whole array.
+* compact, rebalanced: the kept elements are then moved into evenly sized shards of the global output with
+  point-to-point NCCL copies (cuda_pathtracer_b200.distributed.rebalance_compacted).
 * render: iterations split with stride N, ONE NCCL all-reduce of the float SUM image; compared with
   the same iterations rendered on rank 0 alone.
 Timing: CUDA events on the launching stream, max over ranks.  Rank 0 prints one JSON line.
@@ -116,6 +118,21 @@ def main():
     ok = torch.equal(kept[:k], want_c[off:off + k]) and sum(offs) == want_c.numel()
     out["compact"] = {"n": n, "ms": ms, "gbs": (4.0 * n + 4.0 * want_c.numel()) / ms / 1e6, "bit_exact": bool(ok),
                       "kept": int(want_c.numel())}
+    # ... and, optionally, the survivors moved into evenly sized destination shards (NCCL send / recv over NVLink:
+    # a source shard overlaps at most two destination shards)
+    if world > 1:
+        cl = counts.cpu().tolist()
+
+        def rebalance():
+            return D.rebalance_compacted(kept[:k], cl, rank, world, dist,
+                                         lambda m: torch.empty(m, dtype=torch.int32, device="cuda"))
+
+        mine, my_b, tot = rebalance()
+        ob, oe = D.scan_shard(want_c.numel(), rank, world)
+        ok_r = my_b == ob and tot == want_c.numel() and torch.equal(mine, want_c[ob:oe])
+        ms_r = timed(rebalance, args.reps, stream, world)
+        out["compact_rebalance"] = {"ms": ms_r, "bit_exact": bool(ok_r),
+                                    "moved_gbs": 4.0 * want_c.numel() / ms_r / 1e6}
     del full, flags, want_c
 
     # ---- iteration-split render -----------------------------------------------------------------------
@@ -145,7 +162,8 @@ def main():
                      "max_abs_diff_vs_single_gpu": float((got - solo).abs().max()),
                      "allclose": bool(torch.allclose(got, solo, rtol=2e-6, atol=1e-6))}
     r.close()
-    oks = torch.tensor([int(out["scan"]["bit_exact"] and out["compact"]["bit_exact"] and out["render"]["allclose"])],
+    oks = torch.tensor([int(out["scan"]["bit_exact"] and out["compact"]["bit_exact"] and out["render"]["allclose"]
+                            and out.get("compact_rebalance", {"bit_exact": True})["bit_exact"])],
                        device="cuda")
     if world > 1:
         dist.all_reduce(oks, op=dist.ReduceOp.MIN)

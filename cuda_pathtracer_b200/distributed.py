@@ -8,7 +8,10 @@
   totals, and each rank scans its shard seeded with the exclusive prefix of the totals before it
   (int32 wrap-around adds are associative, so the result is bit-exact).
 * Compact -- same shards; ONE all-gather of the per-shard kept counts gives every shard's offset
-  in the global output.
+  in the global output.  Optionally (rebalance_compacted) the survivors are then moved into evenly
+  sized destination shards of the global output: a source shard overlaps at most two of them when the
+  input was sharded evenly, so the exchange is a handful of point-to-point copies over NVLink
+  (NCCL send / recv), not an all-to-all.
 
 The compute callables are injected, so the same logic runs on the B200 library (NCCL, device
 tensors) and -- in the CPU test-suite -- under gloo with the oracle standing in for the kernels.
@@ -80,6 +83,70 @@ def sharded_compact(local_in, rank, world, dist, compact_fn, device="cpu"):
     counts = _all_gather_ints(dist, len(kept), world, device)
     offsets, total = exclusive_prefix_i32(counts)
     return kept, offsets[rank], total
+
+
+def overlap(b0, e0, b1, e1):
+    """[begin, end) of the intersection of two half-open ranges (empty: begin == end)"""
+    b, e = max(b0, b1), min(e0, e1)
+    return (b, e) if b < e else (b, b)
+
+
+def rebalance_plan(counts, rank, world, align=4):
+    """What rank `rank` sends and receives to turn 'survivors of shard r at global offset off[r]' into
+    'rank d owns [scan_shard(total, d, world))' of the global output.
+    Returns (sends, recvs, my_begin, my_end, total): sends = [(dst, local_begin, local_end)] into my kept
+    array, recvs = [(src, out_begin, out_end)] into my destination slice (both in rank order, empty ones
+    dropped, the local piece included as dst == src == rank)."""
+    offsets, total = [], 0
+    for c in counts:
+        offsets.append(total)
+        total += int(c)
+    my_b, my_e = scan_shard(total, rank, world, align)
+    src_b, src_e = offsets[rank], offsets[rank] + int(counts[rank])
+    sends, recvs = [], []
+    for d in range(world):
+        db, de = scan_shard(total, d, world, align)
+        b, e = overlap(src_b, src_e, db, de)
+        if b < e:
+            sends.append((d, b - src_b, e - src_b))
+    for r in range(world):
+        b, e = overlap(offsets[r], offsets[r] + int(counts[r]), my_b, my_e)
+        if b < e:
+            recvs.append((r, b - my_b, e - my_b))
+    return sends, recvs, my_b, my_e, total
+
+
+def rebalance_compacted(kept, counts, rank, world, dist, empty_like):
+    """Moves the survivors into evenly sized destination shards (see rebalance_plan).  kept: this rank's
+    survivors (torch tensor); counts: every rank's kept count (from sharded_compact's all-gather);
+    empty_like(n) -> uninitialised tensor of n elements on kept's device.  Returns (my_slice, my_begin, total)."""
+    sends, recvs, my_b, my_e, total = rebalance_plan(counts, rank, world)
+    out = empty_like(my_e - my_b)
+    ops = []
+    for d, b, e in sends:
+        if d == rank:
+            continue
+        ops.append(dist.P2POp(dist.isend, kept[b:e], d))
+    for r, b, e in recvs:
+        if r == rank:
+            continue
+        ops.append(dist.P2POp(dist.irecv, out[b:e], r))
+    reqs = dist.batch_isend_irecv(ops) if ops else []
+    for d, b, e in sends:                                  # the piece that stays on this rank
+        if d == rank:
+            (rb, re) = next((x[1], x[2]) for x in recvs if x[0] == rank)
+            out[rb:re].copy_(kept[b:e])
+    for q in reqs:
+        q.wait()
+    return out, my_b, total
+
+
+def sharded_compact_counts(local_in, rank, world, dist, compact_fn, device="cpu"):
+    """sharded_compact that also returns every rank's kept count (the input of rebalance_compacted)"""
+    kept = compact_fn(local_in)
+    counts = _all_gather_ints(dist, len(kept), world, device)
+    offsets, total = exclusive_prefix_i32(counts)
+    return kept, offsets[rank], total, counts
 
 
 def render_split(render_fn, allreduce_fn, first_iter, n_iters, rank, world):

@@ -51,6 +51,13 @@ def _worker(rank, world, port, n, out_dir):
         kept, off, total = D.sharded_compact(c[b:e], rank, world, dist, sc_o.compact_without_scan)
         np.save(os.path.join(out_dir, f"compact{rank}.npy"), kept)
         np.save(os.path.join(out_dir, f"meta{rank}.npy"), np.array([b, e, grand, off, total], dtype=np.int64))
+        # ---- ... and the optional exchange that leaves the global output evenly sharded ------------------
+        kept2, off2, total2, counts = D.sharded_compact_counts(c[b:e], rank, world, dist, sc_o.compact_without_scan)
+        mine, my_b, total3 = D.rebalance_compacted(torch.from_numpy(kept2.copy()), counts, rank, world, dist,
+                                                   lambda m: torch.empty(m, dtype=torch.int32))
+        assert (off2, total2, total3) == (off, total, total)
+        np.save(os.path.join(out_dir, f"rebal{rank}.npy"), mine.numpy())
+        np.save(os.path.join(out_dir, f"rebalmeta{rank}.npy"), np.array([my_b], dtype=np.int64))
         # ---- render: iteration split, one all-reduce of the SUM image ----------------------------------
         scene, gui, pt_o = load_scene("cornell_tiny"), gui_from_flags([]), PtOracle()
 
@@ -86,9 +93,36 @@ def test_sharded_paths_match_single_process(tmp_path, world, n):
         got[metas[r][3]:metas[r][3] + k.size] = k
         assert metas[r][4] == want.size
     assert np.array_equal(got, want)
+    # rebalanced: rank d holds exactly scan_shard(total, d, world) of the global output
+    for r in range(world):
+        ob, oe = D.scan_shard(want.size, r, world)
+        assert int(np.load(tmp_path / f"rebalmeta{r}.npy")[0]) == ob
+        assert np.array_equal(np.load(tmp_path / f"rebal{r}.npy"), want[ob:oe])
     scene, gui = load_scene("cornell_tiny"), gui_from_flags([])
     ref, _ = PtOracle().render(scene, gui, 1, 7, threads=1)
     assert np.allclose(np.load(tmp_path / "img.npy"), ref, rtol=2e-6, atol=1e-6)
+
+
+def test_rebalance_plan_moves_every_survivor_exactly_once():
+    rng = np.random.RandomState(3)
+    for world in (1, 2, 3, 8):
+        for _ in range(20):
+            counts = [int(rng.randint(0, 50)) if rng.rand() < 0.8 else 0 for _ in range(world)]
+            total = sum(counts)
+            sent = np.zeros(total, dtype=np.int32)
+            got = np.zeros(total, dtype=np.int32)
+            offs = np.concatenate([[0], np.cumsum(counts)])
+            for r in range(world):
+                sends, recvs, my_b, my_e, t = D.rebalance_plan(counts, r, world)
+                assert t == total and (my_b, my_e) == D.scan_shard(total, r, world)
+                for d, b, e in sends:
+                    sent[offs[r] + b:offs[r] + e] += 1
+                    db, de = D.scan_shard(total, d, world)
+                    assert db <= offs[r] + b and offs[r] + e <= de        # the piece lies inside d's shard
+                for src, b, e in recvs:
+                    got[my_b + b:my_b + e] += 1
+                    assert offs[src] <= my_b + b and my_b + e <= offs[src + 1]
+            assert (sent == 1).all() and (got == 1).all()
 
 
 def test_iteration_shards_partition_the_iterations():
