@@ -1113,6 +1113,10 @@ cudaError_t configure_kernels()
     const int pcap = (int)persist_smem_bytes(PT_CHUNK, PT_SMEM_MATS, PT_SMEM_NODES, 0);
     cudaError_t e = allow_smem(k_bounce_tile<0, 0>, cap);
     if (e == cudaSuccess) e = allow_smem(k_bounce_tile<1, 0>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce_tile<0, 1>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce_tile<1, 1>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce_tile<0, 2>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce_tile<1, 2>, cap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 0>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 0>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<2, 0>, pcap);
@@ -1135,7 +1139,9 @@ cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
 
 bool bounce_is_persistent(const RenderParams& p)
 {
-    return p.cache_mode == 2 || p.gb.n_nodes > 0 || p.n_prims <= PT_CHUNK;
+    if (p.cache_mode == 2) return true;
+    if (p.gb.n_nodes > 0) return p.gb.n_small > 0 && p.mesh.n_nodes == 0;   // tree walks run one tile per CTA (launch_bounce)
+    return p.n_prims <= PT_CHUNK;
 }
 
 // CTAs of a persistent launch: as many as are resident at once (more would only queue up behind them)
@@ -1182,6 +1188,25 @@ static int search_mode(const RenderParams& p) { return p.gb.n_nodes > 0 ? (p.gb.
 cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
 {
     const int mode = search_mode(p);
+    // Scenes whose tiles are long and uneven -- a tree walk per ray: the geometry BVH of a many-primitive scene --
+    // run one tile per CTA and leave the balancing to the hardware's CTA scheduler: the persistent kernel's CTA
+    // holds its SM share for the slowest warp of every tile in turn (config 5: 85.3 vs 77.3 spp/s,
+    // profiles/r5_ab_variants.txt).  The short, even tiles of a small scene are where the persistent form pays.
+    if (mode == 1 && p.cache_mode != 2) {
+        const dim3 grid(p.tiles, p.batch);
+        const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, 0);
+        if (p.cache_mode == 1) k_bounce_tile<1, 1><<<grid, PT_THREADS, smem, s>>>(p);
+        else k_bounce_tile<0, 1><<<grid, PT_THREADS, smem, s>>>(p);
+        return cudaGetLastError();
+    }
+    // ... and so does a small scene with triangle meshes: the mesh BVH walk dominates its tiles (+4 % on the mesh room)
+    if (mode == 2 && p.mesh.n_nodes > 0 && p.cache_mode != 2) {
+        const dim3 grid(p.tiles, p.batch);
+        const size_t smem = bounce_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
+        if (p.cache_mode == 1) k_bounce_tile<1, 2><<<grid, PT_THREADS, smem, s>>>(p);
+        else k_bounce_tile<0, 2><<<grid, PT_THREADS, smem, s>>>(p);
+        return cudaGetLastError();
+    }
     if (bounce_is_persistent(p)) {
         const size_t smem = persist_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
         if (p.cache_mode == 2) return launch_persistent<2, 0>(p, persist_smem_bytes(0, p.n_mats, 0, 0), s);
