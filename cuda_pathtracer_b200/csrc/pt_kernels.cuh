@@ -15,7 +15,10 @@ constexpr int PT_MAX_BATCH = 64;           // iterations in flight (b200pt_optio
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
 constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
-constexpr int PT_SMEM_GNODES = 192;        // geometry-BVH nodes kept in shared memory (12 KB): breadth-first order => the top levels
+#ifndef PT_SMEM_GNODES_N
+#define PT_SMEM_GNODES_N 192
+#endif
+constexpr int PT_SMEM_GNODES = PT_SMEM_GNODES_N;        // geometry-BVH nodes kept in shared memory (12 KB): breadth-first order => the top levels
 constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
 constexpr int PT_GBVH_AUTO = 1;            // geom_bvh = auto: use the BVH from this many sphere / cube primitives (with fewer
                                            // than a leaf's worth the tree is one node and the per-primitive boxes do the culling)
