@@ -315,9 +315,10 @@ def run_own(args, rank, world, local_rank):
         if world > 1:
             dist.destroy_process_group()
         return
-    traffic = None      # DRAM bytes per k_bounce launch from the committed ncu capture of this workload
+    traffic, ncu = None, {}  # DRAM bytes / warp instructions per k_bounce launch from the committed ncu capture of this workload
     try:
-        traffic = json.load(open(os.path.join(REPO, "profiles", "k_bounce_traffic.json")))["bytes_per_launch"]
+        ncu = json.load(open(os.path.join(REPO, "profiles", "k_bounce_traffic.json")))
+        traffic = ncu["bytes_per_launch"]
     except Exception:
         pass
     alg_bytes = st["path_segments"] * ALG_BYTES_PER_SEGMENT + st["iterations"] * P * ALG_BYTES_PER_PIXEL_ITER
@@ -346,6 +347,19 @@ def run_own(args, rank, world, local_rank):
                              "is FP32-issue bound at this scene size (IEEE div/sqrt sequences kept for bit parity), "
                              "see DESIGN.md"},
     }
+    if ncu.get("warp_inst_per_launch") and bounce_n and clocks.get("sm_mhz"):
+        # the ceiling that actually binds k_bounce: warp-instruction issue slots (4 schedulers per SM, one instruction
+        # per clock each).  Instructions per launch come from the committed ncu capture (same workload, same batch
+        # structure), the launch time and the SM clock are measured live.
+        sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+        peak_issue = sms * 4 * float(clocks["sm_mhz"]) * 1e6 / 1e9
+        ach_issue = ncu["warp_inst_per_launch"] / (bounce_ms * 1e-3 / bounce_n) / 1e9
+        line["roofline_issue"] = {"kernel": "k_bounce", "bound": "issue", "achieved": ach_issue, "peak": peak_issue,
+                                  "unit": "Gwarp-inst/s", "frac": ach_issue / peak_issue,
+                                  "warp_inst_per_launch": ncu["warp_inst_per_launch"],
+                                  "ncu_issue_active_pct": ncu.get("issue_active_pct_time_weighted"),
+                                  "ncu_threads_per_warp_inst": ncu.get("threads_per_inst_inst_weighted"),
+                                  "source": "profiles/k_bounce_traffic.json (ncu --set full) x live CUDA-event launch time"}
     if world == 1 and not args.skip_extras:
         line["cpu_baseline"] = cpu_baseline(args.cpu_iters)
         ref = reference_cuda_build(args.ref_cuda_iters)

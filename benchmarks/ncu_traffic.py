@@ -24,14 +24,24 @@ def main(src, dst):
             continue
         rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
         wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
-        per.append({"read": rd, "write": wr, "us": float(r[col["gpu__time_duration.sum"]].replace(",", ""))})
+        num = lambda name: float(r[col[name]].replace(",", "")) if name in col and r[col[name]] else None
+        per.append({"read": rd, "write": wr, "us": num("gpu__time_duration.sum"),
+                    "warp_inst": num("smsp__inst_executed.sum"),
+                    "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                    "threads_per_inst": num("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                    "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active")})
     out = {"kernel": "k_bounce", "launches": len(per),
            "bytes_per_launch": sum(p["read"] + p["write"] for p in per) / len(per),
+           "warp_inst_per_launch": sum(p["warp_inst"] or 0 for p in per) / len(per),
+           "issue_active_pct_time_weighted": sum((p["issue_active_pct"] or 0) * p["us"] for p in per) / sum(p["us"] for p in per),
+           "threads_per_inst_inst_weighted": sum((p["threads_per_inst"] or 0) * (p["warp_inst"] or 0) for p in per)
+                                             / max(1.0, sum(p["warp_inst"] or 0 for p in per)),
            "per_launch": per, "source": src,
            "how": "ncu --set full --clock-control none, dram__bytes_read.sum + dram__bytes_write.sum, mean over the "
                   "consecutive launches of one batch (bounce 0..depth-1)"}
     json.dump(out, open(dst, "w"), indent=1)
-    print(json.dumps({k: out[k] for k in ("launches", "bytes_per_launch")}))
+    print(json.dumps({k: out[k] for k in ("launches", "bytes_per_launch", "warp_inst_per_launch",
+                                          "issue_active_pct_time_weighted", "threads_per_inst_inst_weighted")}))
 
 
 if __name__ == "__main__":

@@ -16,9 +16,13 @@ constexpr int PT_CHUNK = 256;              // primitives staged per shared-memor
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
 constexpr int PT_SMEM_NODES = 256;         // BVH nodes kept in shared memory (12 KB): DFS order => the top of the tree
 #ifndef PT_SMEM_GNODES_N
-#define PT_SMEM_GNODES_N 192
+#define PT_SMEM_GNODES_N 32
 #endif
-constexpr int PT_SMEM_GNODES = PT_SMEM_GNODES_N;        // geometry-BVH nodes kept in shared memory (12 KB): breadth-first order => the top levels
+constexpr int PT_SMEM_GNODES = PT_SMEM_GNODES_N;   // geometry-BVH nodes staged in shared memory (2 KB): breadth-first order => the top
+                                           // 5 levels, which every ray visits.  More costs more than it saves now that these scenes run
+                                           // one tile per CTA (every tile re-stages them): config 5 89.4 spp/s with 32, 87.2 with 64,
+                                           // 85.2 with 192, 83.5 with 512, 63.2 with 1024 (profiles/r5_ab_variants.txt); the rest of
+                                           // the tree is served by L1 / L2
 constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
 constexpr int PT_GBVH_AUTO = 1;            // geom_bvh = auto: use the BVH from this many sphere / cube primitives (with fewer
                                            // than a leaf's worth the tree is one node and the per-primitive boxes do the culling)

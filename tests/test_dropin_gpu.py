@@ -24,7 +24,10 @@ def need(name):
 @pytest.mark.parametrize("scene,flags", [("cornell_tiny", []), ("cornell_small", ["--no-ssaa", "--no-dof"]),
                                          ("cornell_glass_small", ["--refract", "4", "1.5"]),
                                          # OBJ meshes + BVH + textures built by the reference's own loader
-                                         ("mesh_room_small", []), ("mesh_room_small", ["--sort"])])
+                                         ("mesh_room_small", []), ("mesh_room_small", ["--sort"]),
+                                         # guiData->useBVHtree = false (and useBBox = false) through the binding
+                                         ("mesh_room_small_notex", ["--no-bvh"]),
+                                         ("mesh_room_small_notex", ["--no-bvh", "--no-bbox", "--sort"])])
 def test_pathtrace_h_dropin_is_bit_identical(tmp_path, scene, flags):
     ref, mine = need("ref_pathtracer"), need("dropin_pathtracer")
     scene_json = os.path.join(REPO, "scenes", scene + ".json")
