@@ -600,8 +600,19 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.stride = iter_stride;
 
     const bool sort_on = h->opt.sort_by_material != 0;
+    // Scenes whose closest hit is a tree walk (triangle meshes; the geometry BVH proper of a many-primitive
+    // scene) run closest hit and shading as TWO kernels, the hit records going through HBM (36 B per path) --
+    // the material-sort pipeline without the sort.  The walk alone needs fewer registers than the fused
+    // kernel and its long, uneven loops no longer hold the shading state hostage: config 5 89.5 -> 102.3
+    // spp/s, mesh room 355 -> 411 (profiles/r5_ab_variants.txt).  Same hits, same slot order, same seeds: the
+    // image does not change.  Small mesh-free scenes (Cornell) keep the fused persistent kernel.
+#ifndef PT_SPLIT_MODE
+#define PT_SPLIT_MODE 2      // 0 = never, 1 = scenes with meshes, 2 = + geometry BVH proper, 3 = always (experiment)
+#endif
+    const bool split_only = !sort_on && ((PT_SPLIT_MODE >= 1 && h->mesh.n_nodes > 0) ||
+                                         (PT_SPLIT_MODE >= 2 && p.gb.n_nodes > 0 && p.gb.n_small == 0) || PT_SPLIT_MODE >= 3);
     const bool cache_on = h->opt.first_bounce_cache && !h->opt.ssaa && !h->opt.dof;
-    if (sort_on) { r = ensure_sort(h, batch); if (r) return r; }
+    if (sort_on || split_only) { r = ensure_sort(h, batch); if (r) return r; }
     if (cache_on) { r = ensure_cache(h); if (r) return r; }
     p.hit_n = h->d_hit_n;
     p.hit_k = h->d_hit_k;
@@ -637,7 +648,12 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             }
             p.epoch = h->epoch;
             p.cache_mode = (b == 0 && cache_on) ? (h->cache_valid ? 2 : 1) : 0;
-            if (!sort_on) {
+            if (split_only) {
+                if (p.cache_mode != 2) { CK(launch_isect(p, s)); h->launches += 1; }
+                p.perm_in = nullptr;
+                CK(launch_shade(p, s));
+                h->launches += 1;
+            } else if (!sort_on) {
                 CK(launch_bounce(p, s));
                 h->launches += 1;
             } else {
