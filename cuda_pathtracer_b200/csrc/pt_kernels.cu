@@ -878,6 +878,198 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_isect_dyn: closest hit through the geometry BVH with DYNAMIC RAY FETCH (mesh-free scenes).
+//
+// After the first bounce the rays of a warp have nothing in common, and how far each one walks the
+// tree varies by orders of magnitude: in k_isect<1> a warp keeps running until its unluckiest ray is done
+// (ncu, config 5, bounce 1: 6 of 32 threads active per instruction in the walk, profiles/r19_config5_*).
+// The hit record of a ray goes to the ray's own index, so -- unlike shading, whose random numbers are
+// seeded by the slot -- closest hit may take the rays in ANY order.  Here the kernel is persistent, every
+// warp is its own worker, and a lane whose ray is finished gets a new one from a global ticket counter
+// as soon as PT_DYN_REFILL lanes of the warp are idle; the lanes in between keep their state (stack,
+// candidate list, current hit) in registers / local memory.  A round is: refill, up to PT_DYN_STEPS node
+// visits per lane, the exact tests of the listed candidates once some lane needs them (list nearly full or
+// walk finished; every lane with candidates joins in), write-out of finished rays.  The search itself --
+// box tests, candidate pruning, lexicographic (t, index) winner -- is closest_in_gbvh's.
+#ifndef PT_DYN_REFILL
+#define PT_DYN_REFILL 8
+#endif
+#ifndef PT_DYN_STEPS
+#define PT_DYN_STEPS 8
+#endif
+#ifndef PT_DYN_GNODES
+#define PT_DYN_GNODES 64           // staged nodes (4 KB); more takes L1 capacity away from the rest of the tree (512: 137 spp/s, 64: 142)
+#endif
+
+struct DynShared {
+    unsigned long long bar[2];
+    int total;                        // live rays of all slots entering this bounce
+    int pad_;
+    int base[PT_MAX_BATCH + 2];       // exclusive prefix of the slots' live counts
+};
+
+__global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    DynShared& sh = *reinterpret_cast<DynShared*>(smem_raw);
+    const float4* snodes_g = reinterpret_cast<const float4*>(smem_raw + sizeof(DynShared));
+    const int lane = threadIdx.x & 31;
+    const int n_staged = p.gb.n_nodes < PT_DYN_GNODES ? p.gb.n_nodes : PT_DYN_GNODES;
+    bounce_barriers_init(sh.bar);
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int sl = 0; sl < p.batch; ++sl) {
+            sh.base[sl] = run;
+            run += p.counts[p.bounce * p.batch + sl];
+        }
+        sh.base[p.batch] = run;
+        sh.total = run;
+        if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
+        const unsigned bytes = (unsigned)(n_staged * 4 * sizeof(float4));
+        mbar_expect_tx(&sh.bar[0], bytes);
+        bulk_g2s(const_cast<float4*>(snodes_g), p.gb.nodes, bytes, &sh.bar[0]);
+    }
+    __syncthreads();
+    mbar_wait(&sh.bar[0], 0u);
+    const int total = sh.total;
+    int* ticket = p.tickets + p.bounce;
+
+    // per-lane state of the ray in flight
+    bool has = false, walking = false;
+    int slot = 0, idx = 0;
+    V3 o = v3(0.f, 0.f, 0.f), d = o, inv = o;
+    float t_min = 3.402823466e+38f;
+    int hit = -1;
+    Cand best;
+    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+    int stack[64];
+    int cand_prim[PT_GCAND];
+    float cand_t[PT_GCAND];
+    int sp = 0, nc = 0, node = 0;
+    bool exhausted = false;                           // warp-uniform: the ticket counter has run past the last ray
+
+    for (;;) {
+        // ---- refill ----
+        unsigned idle = __ballot_sync(FULL_MASK, !has);
+        if (!exhausted && __popc(idle) >= PT_DYN_REFILL) {
+            const int n = __popc(idle);
+            int base = 0;
+            if (lane == 0) base = atomicAdd(ticket, n);
+            base = __shfl_sync(FULL_MASK, base, 0);
+            if (!has) {
+                const int w = base + __popc(idle & ((1u << lane) - 1u));
+                if (w < total) {
+                    slot = 0;
+                    while (w >= sh.base[slot + 1]) ++slot;
+                    idx = w - sh.base[slot];
+                    const size_t at = (size_t)slot * p.P + idx;
+                    const float4 a = p.in.a[at], b = p.in.b[at];
+                    o = v3(a.x, a.y, a.z);
+                    d = v3(b.x, b.y, b.z);
+                    inv = v3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
+                    t_min = 3.402823466e+38f;
+                    hit = -1;
+                    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+                    sp = 0; nc = 0; node = 0;
+                    // a NaN direction (glm::refract past the critical angle) hits nothing in the reference
+                    walking = d.x == d.x && d.y == d.y && d.z == d.z;
+                    has = true;
+                }
+            }
+            if (base + n >= total) exhausted = true;
+            idle = __ballot_sync(FULL_MASK, !has);
+        }
+        if (idle == FULL_MASK) break;                 // only once exhausted: nothing in flight, nothing to fetch
+
+        // ---- walk: box tests only, candidates listed ----
+        for (int step = 0; step < PT_DYN_STEPS; ++step) {
+            const bool go = has && walking && nc <= PT_GCAND - 16;
+            if (!__any_sync(FULL_MASK, go)) break;
+            if (go) {
+                const float t_lim = fmaf(t_min, 1.0001f, 1e-4f);
+                const float4* q = node < n_staged ? snodes_g + 4 * node : p.gb.nodes + 4 * (size_t)node;
+                const float4 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+                const float tl = gbox_entry(q0, q1, o, inv, t_lim), tr = gbox_entry(q2, q3, o, inv, t_lim);
+                int ref_near = __float_as_int(q0.w), ref_far = __float_as_int(q1.w);
+                bool near_ok = tl >= 0.0f, far_ok = tr >= 0.0f;
+                if (far_ok && (!near_ok || tr < tl)) {
+                    const int r = ref_near; ref_near = ref_far; ref_far = r;
+                    const bool bb = near_ok; near_ok = far_ok; far_ok = bb;
+                }
+                int next = -1;
+#pragma unroll
+                for (int side = 0; side < 2; ++side) {
+                    const int ref = side == 0 ? ref_near : ref_far;
+                    const bool ok = side == 0 ? near_ok : far_ok;
+                    if (!ok) continue;
+                    if (ref < 0) {
+                        const int v = ~ref, first = v >> 3, count = (v & 7) + 1;
+                        for (int k = 0; k < count; ++k) {
+                            const float te = gbox_entry(p.gb.boxes[2 * (first + k)], p.gb.boxes[2 * (first + k) + 1], o, inv, t_lim);
+                            if (te >= 0.0f) { cand_prim[nc] = first + k; cand_t[nc] = te; ++nc; }
+                        }
+                    } else if (next < 0) {
+                        next = ref;
+                    } else {
+                        stack[sp++] = ref;
+                    }
+                }
+                if (next >= 0) node = next;
+                else if (sp > 0) node = stack[--sp];
+                else walking = false;
+            }
+        }
+
+        // ---- exact tests of the listed candidates, once some lane needs them ----
+        const bool need = has && nc > 0 && (!walking || nc > PT_GCAND - 16);
+        if (__any_sync(FULL_MASK, need)) {
+            if (has && nc > 0) {
+                int k = 0;
+                while (true) {
+                    const float lim = fmaf(t_min, 1.0001f, 1e-4f);
+                    while (k < nc && cand_t[k] > lim) ++k;
+                    if (k >= nc) break;
+                    const PrimRec& g = p.gb.prims[cand_prim[k]];
+                    ++k;
+                    const Cand c = prim_test(g, o, d);
+                    const int gi = g.pad0;
+                    // lexicographic minimum of (t, index): what the ascending loop with strict `<` finds
+                    if (c.t > 0.0f && (t_min > c.t || (t_min == c.t && gi < hit))) {
+                        t_min = c.t;
+                        hit = gi;
+                        best = c;
+                    }
+                }
+                nc = 0;
+            }
+        }
+
+        // ---- finished rays: the hit record goes to the ray's own index ----
+        if (has && !walking && nc == 0) {
+            float ht = -1.0f;
+            V3 hn = v3(0.f, 0.f, 0.f);
+            int hm = 0;
+            if (hit >= 0) {
+                const PrimRec& g = p.prims[hit];
+                hn = prim_normal(g, best);
+                ht = t_min;
+                hm = g.material;
+            }
+            const size_t at = (size_t)slot * p.P + idx;
+            p.hit_n[at] = make_float4(ht, hn.x, hn.y, hn.z);
+            p.hit_k[at] = hm;
+            p.hit_uv[at] = make_float2(0.f, 0.f);
+            if (p.cache_mode == 1 && slot == 0) {
+                p.cache_n[idx] = make_float4(ht, hn.x, hn.y, hn.z);
+                p.cache_k[idx] = hm;
+                p.cache_uv[idx] = make_float2(0.f, 0.f);
+            }
+            has = false;
+        }
+    }
+}
+
 // digit of the sort key of the element at sorted position j of this pass
 __device__ __forceinline__ int sort_digit(const RenderParams& p, int slot, int j, int pass, int& src)
 {
@@ -1124,6 +1316,7 @@ cudaError_t configure_kernels()
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 1>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 2>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 2>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_isect_dyn, (int)(sizeof(DynShared) + (size_t)PT_DYN_GNODES * 4 * sizeof(float4)));
     if (e == cudaSuccess) e = allow_smem(k_isect<0>, cap);
     if (e == cudaSuccess) e = allow_smem(k_isect<1>, cap);
     if (e == cudaSuccess) e = allow_smem(k_isect<2>, cap);
@@ -1222,9 +1415,26 @@ cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
     return cudaGetLastError();
 }
 
+static size_t dyn_smem_bytes(int n_gnodes)
+{
+    return sizeof(DynShared) + (size_t)(n_gnodes < PT_DYN_GNODES ? n_gnodes : PT_DYN_GNODES) * 4 * sizeof(float4);
+}
+
 cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
 {
     const int mode = search_mode(p);
+#ifndef PT_NO_DYN
+    if (mode == 1 && p.mesh.n_nodes == 0) {           // geometry BVH proper, no meshes: dynamic ray fetch
+        static int grid = 0;
+        const size_t smem = dyn_smem_bytes(p.gb.n_nodes);
+        if (grid == 0) {
+            const cudaError_t e = persistent_grid(k_isect_dyn, dyn_smem_bytes(1 << 30), 1 << 30, grid);
+            if (e != cudaSuccess) return e;
+        }
+        k_isect_dyn<<<grid, PT_THREADS, smem, s>>>(p);
+        return cudaGetLastError();
+    }
+#endif
     const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
     const dim3 grid(p.tiles, p.batch);
     if (mode == 2) k_isect<2><<<grid, PT_THREADS, smem, s>>>(p);
