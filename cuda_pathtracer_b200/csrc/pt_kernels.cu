@@ -899,7 +899,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
 #define PT_DYN_STEPS 8
 #endif
 #ifndef PT_DYN_GNODES
-#define PT_DYN_GNODES 64           // staged nodes (4 KB); more takes L1 capacity away from the rest of the tree (512: 137 spp/s, 64: 142)
+#define PT_DYN_GNODES 16           // staged nodes (1 KB); more takes L1 capacity away from the rest of the tree (512: 137 spp/s, 64: 142, 16: 144)
 #endif
 
 struct DynShared {
@@ -1064,6 +1064,165 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                 p.cache_n[idx] = make_float4(ht, hn.x, hn.y, hn.z);
                 p.cache_k[idx] = hm;
                 p.cache_uv[idx] = make_float2(0.f, 0.f);
+            }
+            has = false;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_isect_dyn_mesh: the same dynamic ray fetch for small scenes WITH triangle meshes (the room.json shape:
+// a handful of spheres / cubes searched by closest_small, then the walk of the mesh BVH, which dominates and
+// diverges just as badly: 7 of 32 threads per instruction at bounce 1, profiles/r19_N3_mesh_room_*).
+// Per-lane state is bvh_traverse's (visit stack, listed leaves, nearest triangle so far); the walk visits the
+// nodes in the reference's order and the listed triangles are tested in the order met, so the "first one
+// met wins a tie" rule is untouched.  Trees deep enough for the reference's stack-overflow drop
+// (literal_walk) and the useBVHtree = false mode stay with k_isect.
+#ifndef PT_DYNM_REFILL
+#define PT_DYNM_REFILL 12
+#endif
+
+__global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    DynShared& sh = *reinterpret_cast<DynShared*>(smem_raw);
+    BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(DynShared));
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
+    const float4* crecs = reinterpret_cast<const float4*>(sprims + p.gb.n_small);
+    const MeshScene& M = p.mesh;
+    const int lane = threadIdx.x & 31;
+    bounce_barriers_init(sh.bar);
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int sl = 0; sl < p.batch; ++sl) {
+            sh.base[sl] = run;
+            run += p.counts[p.bounce * p.batch + sl];
+        }
+        sh.base[p.batch] = run;
+        sh.total = run;
+        if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
+    }
+    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
+    __syncthreads();
+    mbar_wait(&sh.bar[0], 0u);
+    const int total = sh.total;
+    int* ticket = p.tickets + p.bounce;
+
+    bool has = false, walking = false;
+    int slot = 0, idx = 0;
+    V3 o = v3(0.f, 0.f, 0.f), d = o, minv = o;
+    float t_min = 3.402823466e+38f, t_cap = 3.402823466e+38f;
+    int hit = -1, hit_k = -1;
+    Cand best;
+    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+    MeshHit mh = no_mesh_hit();
+    int to_visit[BVH_MAX_SEARCH_DEPTH];
+    int leaf_first[PT_MLEAVES], leaf_count[PT_MLEAVES];
+    float leaf_entry[PT_MLEAVES];
+    int sp = 0, cur = 0, nl = 0;
+    bool exhausted = false;
+
+    for (;;) {
+        // ---- refill: new rays first run the sphere / cube search, whose hit caps the mesh walk ----
+        unsigned idle = __ballot_sync(FULL_MASK, !has);
+        if (!exhausted && __popc(idle) >= PT_DYNM_REFILL) {
+            const int n = __popc(idle);
+            int base = 0;
+            if (lane == 0) base = atomicAdd(ticket, n);
+            base = __shfl_sync(FULL_MASK, base, 0);
+            if (!has) {
+                const int w = base + __popc(idle & ((1u << lane) - 1u));
+                if (w < total) {
+                    slot = 0;
+                    while (w >= sh.base[slot + 1]) ++slot;
+                    idx = w - sh.base[slot];
+                    const size_t at = (size_t)slot * p.P + idx;
+                    const float4 a = p.in.a[at], b = p.in.b[at];
+                    o = v3(a.x, a.y, a.z);
+                    d = v3(b.x, b.y, b.z);
+                    t_min = 3.402823466e+38f;
+                    hit = -1; hit_k = -1;
+                    best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+                    mh = no_mesh_hit();
+                    sp = 0; cur = 0; nl = 0;
+                    walking = d.x == d.x && d.y == d.y && d.z == d.z;      // a NaN direction hits nothing
+                    if (walking) {
+                        closest_small(sprims, crecs, p.gb.n_small, o, d, t_min, hit, hit_k, best);
+                        minv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+                        t_cap = p.gb.cap_mesh_walk ? prune_limit(t_min) : 3.402823466e+38f;
+                    }
+                    has = true;
+                }
+            }
+            if (base + n >= total) exhausted = true;
+            idle = __ballot_sync(FULL_MASK, !has);
+        }
+        if (idle == FULL_MASK) break;
+
+        // ---- walk of the mesh BVH: box tests only, leaves listed ----
+        for (int step = 0; step < PT_DYN_STEPS; ++step) {
+            const bool go = has && walking && nl < PT_MLEAVES;
+            if (!__any_sync(FULL_MASK, go)) break;
+            if (go) {
+                const float lim = fminf(prune_limit(mh.t), t_cap);
+                const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
+                float entry;
+                bool descend = false;
+                if (bbox_hit(nd.lo, nd.hi, o, minv, entry) && !(entry > lim)) {
+                    if (nd.sub_areas > 0) {
+                        leaf_first[nl] = nd.first; leaf_count[nl] = nd.sub_areas; leaf_entry[nl] = entry; ++nl;
+                    } else {
+                        descend = true;
+                        if ((nd.axis == 0 ? d.x : nd.axis == 1 ? d.y : d.z) < 0.0f) { to_visit[sp++] = cur + 1; cur = nd.rchild; }
+                        else { to_visit[sp++] = nd.rchild; cur = cur + 1; }
+                    }
+                }
+                if (!descend) {
+                    if (sp == 0) walking = false;
+                    else cur = to_visit[--sp];
+                }
+            }
+        }
+
+        // ---- the listed triangles, in the order met, once some lane needs them ----
+        const bool need = has && nl > 0 && (!walking || nl == PT_MLEAVES);
+        if (__any_sync(FULL_MASK, need)) {
+            if (has && nl > 0) {
+                int k = 0, i = 0;
+                while (true) {
+                    const float lim2 = fminf(prune_limit(mh.t), t_cap);
+                    while (k < nl && (i >= leaf_count[k] || leaf_entry[k] > lim2)) { ++k; i = 0; }
+                    if (k >= nl) break;
+                    tri_candidate(M, leaf_first[k] + i, o, d, mh);
+                    ++i;
+                }
+                nl = 0;
+            }
+        }
+
+        // ---- finished rays ----
+        if (has && !walking && nl == 0) {
+            if (mh.tri >= 0) mh.id = M.tv[mh.tri].id;
+            int owner = -1;
+            closest_among_mesh_prims(p, mh, t_min, hit, owner);
+            float ht = -1.0f, hu = 0.0f, hv = 0.0f;
+            V3 hn = v3(0.f, 0.f, 0.f);
+            int hm = 0;
+            if (hit >= 0) {
+                const bool staged = hit_k >= 0 && sprims[hit_k].pad0 == hit;
+                const PrimRec& g = staged ? sprims[hit_k] : p.prims[hit];
+                hit_attributes(M, g, hit, best, mh, owner, hn, hu, hv);
+                ht = t_min;
+                hm = g.material;
+            }
+            const size_t at = (size_t)slot * p.P + idx;
+            p.hit_n[at] = make_float4(ht, hn.x, hn.y, hn.z);
+            p.hit_k[at] = hm;
+            p.hit_uv[at] = make_float2(hu, hv);
+            if (p.cache_mode == 1 && slot == 0) {
+                p.cache_n[idx] = make_float4(ht, hn.x, hn.y, hn.z);
+                p.cache_k[idx] = hm;
+                p.cache_uv[idx] = make_float2(hu, hv);
             }
             has = false;
         }
@@ -1317,6 +1476,7 @@ cudaError_t configure_kernels()
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 2>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 2>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_isect_dyn, (int)(sizeof(DynShared) + (size_t)PT_DYN_GNODES * 4 * sizeof(float4)));
+    if (e == cudaSuccess) e = allow_smem(k_isect_dyn_mesh, cap);
     if (e == cudaSuccess) e = allow_smem(k_isect<0>, cap);
     if (e == cudaSuccess) e = allow_smem(k_isect<1>, cap);
     if (e == cudaSuccess) e = allow_smem(k_isect<2>, cap);
@@ -1432,6 +1592,21 @@ cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
             if (e != cudaSuccess) return e;
         }
         k_isect_dyn<<<grid, PT_THREADS, smem, s>>>(p);
+        return cudaGetLastError();
+    }
+#endif
+#ifndef PT_NO_DYN_MESH
+    if (mode == 2 && p.mesh.n_nodes > 0 && !p.mesh.literal_walk && !p.mesh.brute) {   // small scene + meshes
+        static int mgrid = 0;
+        static size_t mgrid_smem = ~(size_t)0;
+        const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small)
+                            - sizeof(BounceShared) + sizeof(DynShared);
+        if (mgrid_smem != smem) {
+            const cudaError_t e = persistent_grid(k_isect_dyn_mesh, smem, 1 << 30, mgrid);
+            if (e != cudaSuccess) return e;
+            mgrid_smem = smem;
+        }
+        k_isect_dyn_mesh<<<mgrid, PT_THREADS, smem, s>>>(p);
         return cudaGetLastError();
     }
 #endif
