@@ -947,6 +947,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
     int cand_prim[PT_GCAND];
     float cand_t[PT_GCAND];
     int sp = 0, nc = 0, node = 0;
+    int lp_first = 0, lp_left = 0;                    // primitives of the leaf at hand whose own boxes are still to be tested
     bool exhausted = false;                           // warp-uniform: the ticket counter has run past the last ray
 
     for (;;) {
@@ -971,7 +972,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                     t_min = 3.402823466e+38f;
                     hit = -1;
                     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-                    sp = 0; nc = 0; node = 0;
+                    sp = 0; nc = 0; node = 0; lp_left = 0;
                     // a NaN direction (glm::refract past the critical angle) hits nothing in the reference
                     walking = d.x == d.x && d.y == d.y && d.z == d.z;
                     has = true;
@@ -983,41 +984,58 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
         if (idle == FULL_MASK) break;                 // only once exhausted: nothing in flight, nothing to fetch
 
         // ---- walk: box tests only, candidates listed ----
+        // A step tests TWO boxes whatever the lane stands at: the two child boxes of an inner node, or the own
+        // boxes of the next two primitives of a leaf (both are four consecutive float4: lo, hi, lo, hi) -- so the
+        // lanes at leaves and the lanes at inner nodes run the same instructions.  (Looping over a leaf's
+        // primitives inside the node visit ran at 3 of 32 threads and was a third of all instructions,
+        // profiles/r25_config5_k_isect_dyn_raw.csv.)
         for (int step = 0; step < PT_DYN_STEPS; ++step) {
             const bool go = has && walking && nc <= PT_GCAND - 16;
             if (!__any_sync(FULL_MASK, go)) break;
             if (go) {
                 const float t_lim = fmaf(t_min, 1.0001f, 1e-4f);
-                const float4* q = node < n_staged ? snodes_g + 4 * node : p.gb.nodes + 4 * (size_t)node;
-                const float4 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+                const bool leaf = lp_left > 0;
+                const float4* q = leaf ? p.gb.boxes + 2 * (size_t)lp_first
+                                       : (node < n_staged ? snodes_g + 4 * node : p.gb.nodes + 4 * (size_t)node);
+                const float4* q2p = (leaf && lp_left == 1) ? q : q + 2;      // a leaf's last odd primitive: no second box
+                const float4 q0 = q[0], q1 = q[1], q2 = q2p[0], q3 = q2p[1];
                 const float tl = gbox_entry(q0, q1, o, inv, t_lim), tr = gbox_entry(q2, q3, o, inv, t_lim);
-                int ref_near = __float_as_int(q0.w), ref_far = __float_as_int(q1.w);
-                bool near_ok = tl >= 0.0f, far_ok = tr >= 0.0f;
-                if (far_ok && (!near_ok || tr < tl)) {
-                    const int r = ref_near; ref_near = ref_far; ref_far = r;
-                    const bool bb = near_ok; near_ok = far_ok; far_ok = bb;
-                }
-                int next = -1;
-#pragma unroll
-                for (int side = 0; side < 2; ++side) {
-                    const int ref = side == 0 ? ref_near : ref_far;
-                    const bool ok = side == 0 ? near_ok : far_ok;
-                    if (!ok) continue;
-                    if (ref < 0) {
-                        const int v = ~ref, first = v >> 3, count = (v & 7) + 1;
-                        for (int k = 0; k < count; ++k) {
-                            const float te = gbox_entry(p.gb.boxes[2 * (first + k)], p.gb.boxes[2 * (first + k) + 1], o, inv, t_lim);
-                            if (te >= 0.0f) { cand_prim[nc] = first + k; cand_t[nc] = te; ++nc; }
-                        }
-                    } else if (next < 0) {
-                        next = ref;
-                    } else {
-                        stack[sp++] = ref;
+                int ref = 0;
+                bool have_ref = false;
+                if (leaf) {
+                    if (tl >= 0.0f) { cand_prim[nc] = lp_first; cand_t[nc] = tl; ++nc; }
+                    if (lp_left > 1 && tr >= 0.0f) { cand_prim[nc] = lp_first + 1; cand_t[nc] = tr; ++nc; }
+                    const int done = lp_left > 1 ? 2 : 1;
+                    lp_first += done;
+                    lp_left -= done;
+                    if (lp_left > 0) continue;                     // more primitives of this leaf
+                } else {
+                    int ref_near = __float_as_int(q0.w), ref_far = __float_as_int(q1.w);
+                    bool near_ok = tl >= 0.0f, far_ok = tr >= 0.0f;
+                    if (far_ok && (!near_ok || tr < tl)) {
+                        const int r = ref_near; ref_near = ref_far; ref_far = r;
+                        const bool bb = near_ok; near_ok = far_ok; far_ok = bb;
+                    }
+                    if (near_ok) {
+                        ref = ref_near; have_ref = true;
+                        if (far_ok) stack[sp++] = ref_far;         // inner node or leaf: visited after the near side
+                    } else if (far_ok) {
+                        ref = ref_far; have_ref = true;
                     }
                 }
-                if (next >= 0) node = next;
-                else if (sp > 0) node = stack[--sp];
-                else walking = false;
+                if (!have_ref) {
+                    if (sp > 0) { ref = stack[--sp]; have_ref = true; }
+                    else walking = false;
+                }
+                if (have_ref) {
+                    if (ref >= 0) {
+                        node = ref;
+                    } else {                                       // a leaf: its primitives' own boxes come next
+                        const int v = ~ref;
+                        lp_first = v >> 3;
+                        lp_left = (v & 7) + 1;
+                    }
+                }
             }
         }
 
