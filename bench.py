@@ -329,7 +329,7 @@ def run_own(args, rank, world, local_rank):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "spp_per_s": args.steps * I * world / (ms * 1e-3),
         "segments_per_sample_path": segments / (args.steps * I * world * P),
-        "config": {"workload": f"{SCENE} 800x800, trace depth 8, reference defaults (RR+SSAA+DoF)",
+        "config": {"workload": f"{SCENE} {sc.width}x{sc.height}, trace depth {sc.traceDepth}, reference defaults (RR+SSAA+DoF)",
                    "iters_per_step": I, "batch": args.batch or "library default (4M paths in flight)",
                    "l2": "no flush: the two path pools of a batch (2 x 48 B x 640000 x batch) exceed the 126 MB L2",
                    "parallelism": "replicated scene, iterations split across ranks (stride N), one NCCL "
@@ -337,7 +337,8 @@ def run_own(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": "Mpath-segments/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "clocks": clocks,
-        "roofline": {"kernel": "k_bounce (closest hit + shade + look-back compaction, one launch per bounce)",
+        "roofline": {"kernel": "k_bounce (closest hit + shade + look-back compaction, one launch per bounce)" if SCENE.startswith("cornell")
+                               else "the bounce kernels of this scene (closest hit with dynamic ray fetch + k_shade)",
                      "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic,
                      "alg_bytes_per_launch": alg_bytes / bounce_n if bounce_n else None,
@@ -347,7 +348,9 @@ def run_own(args, rank, world, local_rank):
                              "is FP32-issue bound at this scene size (IEEE div/sqrt sequences kept for bit parity), "
                              "see DESIGN.md"},
     }
-    if ncu.get("warp_inst_per_launch") and bounce_n and clocks.get("sm_mhz"):
+    if SCENE != "cornell":
+        line["roofline"]["traffic"] = None               # the committed ncu capture is of the Cornell workload
+    if SCENE == "cornell" and ncu.get("warp_inst_per_launch") and bounce_n and clocks.get("sm_mhz"):
         # the ceiling that actually binds k_bounce: warp-instruction issue slots (4 schedulers per SM, one instruction
         # per clock each).  Instructions per launch come from the committed ncu capture (same workload, same batch
         # structure), the launch time and the SM clock are measured live.
@@ -379,10 +382,15 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--iters-per-step", type=int, default=48)
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--scene", default="cornell",
+                    help="tests/golden/<scene>.scene.bin; the contract benchmark is the default (BASELINE configs[1]); "
+                         "e.g. --scene synthetic_4096 --iters-per-step 8 --skip-extras is configs[4] (per-GPU share)")
     ap.add_argument("--cpu-iters", type=int, default=8)
     ap.add_argument("--ref-cuda-iters", type=int, default=100)
     ap.add_argument("--skip-extras", action="store_true", help="no cpu_baseline / reference CUDA build / scan legs")
     args = ap.parse_args()
+    global SCENE
+    SCENE = args.scene
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
