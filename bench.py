@@ -330,7 +330,7 @@ def run_own(args, rank, world, local_rank):
         "spp_per_s": args.steps * I * world / (ms * 1e-3),
         "segments_per_sample_path": segments / (args.steps * I * world * P),
         "config": {"workload": f"{SCENE} {sc.width}x{sc.height}, trace depth {sc.traceDepth}, reference defaults (RR+SSAA+DoF)",
-                   "iters_per_step": I, "batch": args.batch or "library default (4M paths in flight)",
+                   "iters_per_step": I, "batch": args.batch or "library default (32M paths in flight, at most 32 iterations)",
                    "l2": "no flush: the two path pools of a batch (2 x 48 B x 640000 x batch) exceed the 126 MB L2",
                    "parallelism": "replicated scene, iterations split across ranks (stride N), one NCCL "
                                   "all-reduce of the float accumulation image" if world > 1 else "single GPU"},

@@ -2,8 +2,8 @@
 
     python benchmarks/ncu_traffic.py gpurun_out/r5_k_bounce_raw.csv profiles/k_bounce_traffic.json
 
-The capture (benchmarks/profile_round.sh) holds the depth consecutive launches of ONE batch -- bounce 0 to
-depth-1 of the same iterations in flight -- so their mean is the per-launch figure bench.py's
+The capture (benchmarks/profile_round.sh) holds the consecutive launches of ONE whole bench.py step -- every
+batch of its 48 iterations, bounce 0 to depth-1 each -- so their mean is the per-launch figure bench.py's
 roofline.achieved is quoted per (algorithmic bytes / launch vs dram__bytes_read.sum + dram__bytes_write.sum)."""
 import csv
 import json
@@ -38,7 +38,7 @@ def main(src, dst):
                                              / max(1.0, sum(p["warp_inst"] or 0 for p in per)),
            "per_launch": per, "source": src,
            "how": "ncu --set full --clock-control none, dram__bytes_read.sum + dram__bytes_write.sum, mean over the "
-                  "consecutive launches of one batch (bounce 0..depth-1)"}
+                  "consecutive launches of one bench.py step (all batches, bounce 0..depth-1)"}
     json.dump(out, open(dst, "w"), indent=1)
     print(json.dumps({k: out[k] for k in ("launches", "bytes_per_launch", "warp_inst_per_launch",
                                           "issue_active_pct_time_weighted", "threads_per_inst_inst_weighted")}))

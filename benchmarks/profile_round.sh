@@ -3,7 +3,8 @@
 #   bash benchmarks/profile_round.sh r2
 # 1. the program first runs WITHOUT ncu (must exit 0),
 # 2. launch list of the same command (per-launch gpu__time_duration; cold-cache, serialised),
-# 3. one `--set full` capture each of the top kernels: k_bounce (the 8 launches of one batch, bounce 0..7),
+# 3. one `--set full` capture each of the top kernels: k_bounce (the 16 launches of one whole step = 48 iterations
+#    = a batch of 32 and a batch of 16, bounce 0..7 each: their mean is the mean launch of the timed region),
 #    the single-pass scan and compact; DRAM bytes per k_bounce launch -> *_k_bounce_traffic.json.
 # Outputs land in gpurun_out/; the summaries to be judged are copied into profiles/ by hand.
 tag=${1:-rX}
@@ -13,7 +14,7 @@ cmd="python bench.py --steps 2 --warmup 1 --skip-extras"
 $cmd > $out/${tag}_prof_plain.json 2> $out/${tag}_prof_plain.err || { echo "plain run failed"; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \
     $cmd > $out/${tag}_ncu_launches.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 8 -c 8 -f -o $out/${tag}_k_bounce \
+ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 16 -c 16 -f -o $out/${tag}_k_bounce \
     python bench.py --steps 1 --warmup 1 --skip-extras > $out/${tag}_ncu_bounce.log 2>&1
 ncu --set full --clock-control none --import-source on -k 'regex:k_scan_lookback|k_compact' -s 6 -c 2 -f -o $out/${tag}_k_scan \
     python benchmarks/sc_sweep.py --lg 28 --iters 2 > $out/${tag}_ncu_scan.log 2>&1
