@@ -22,5 +22,7 @@ for k in k_bounce k_scan; do
   ncu -i $out/${tag}_${k}.ncu-rep --page raw --csv > $out/${tag}_${k}_raw.csv 2>/dev/null
 done
 python benchmarks/ncu_traffic.py $out/${tag}_k_bounce_raw.csv $out/${tag}_k_bounce_traffic.json
-ncu -i $out/${tag}_k_bounce.ncu-rep --page source --csv > $out/${tag}_k_bounce_src.csv 2>/dev/null
+# (the source page of 16 launches is > 100 MB and gpurun brings back at most 64 MiB: benchmarks/profile_config.sh
+#  captures single launches for benchmarks/ncu_lines.py; the reports themselves stay on the box)
+rm -f $out/${tag}_k_bounce.ncu-rep $out/${tag}_k_scan.ncu-rep
 ls -la $out | grep ${tag}_
