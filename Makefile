@@ -39,7 +39,7 @@ $(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
 	@mkdir -p $(BIN)
 	g++ $(CXXFLAGS) -c -o $@ $<
 
-$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/mesh.o $(BIN)/jpeg.o $(BIN)/image_io.o $(PKG)/libb200pt.so
+$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/mesh.o $(BIN)/jpeg.o $(BIN)/png.o $(BIN)/image_io.o $(PKG)/libb200pt.so
 	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200pt -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN/..'
 
 $(BIN)/stream_compaction_test: $(HOST)/sc_harness.cpp include/b200_stream_compaction.hpp include/b200_sc.h $(PKG)/libb200sc.so

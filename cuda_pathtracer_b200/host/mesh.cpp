@@ -436,9 +436,11 @@ TextureImage load_texture(const std::string& path)
     const std::string raw = buf.str();
     if (looks_like_jpeg(reinterpret_cast<const unsigned char*>(raw.data()), raw.size()))
         return decode_jpeg(reinterpret_cast<const unsigned char*>(raw.data()), raw.size(), path);
+    if (looks_like_png(reinterpret_cast<const unsigned char*>(raw.data()), raw.size()))
+        return decode_png(reinterpret_cast<const unsigned char*>(raw.data()), raw.size(), path);
     if (raw.size() < 2 || raw[0] != 'P' || (raw[1] != '5' && raw[1] != '6'))
-        throw std::runtime_error("Texture load error! (" + path + ": only baseline JPEG and binary PPM/PGM textures are "
-                                 "decoded here; convert other formats to one of them)");
+        throw std::runtime_error("Texture load error! (" + path + ": only baseline JPEG, PNG and binary PPM/PGM textures "
+                                 "are decoded here; convert other formats to one of them)");
     size_t at = 2;
     auto next_int = [&]() {
         while (at < raw.size()) {                          // white space and '#' comments

@@ -39,5 +39,8 @@ std::vector<b200pt_bvh_node> build_bvh_tree(std::vector<b200pt_triangle>& triang
 TextureImage load_texture(const std::string& path);
 bool looks_like_jpeg(const unsigned char* data, size_t size);
 TextureImage decode_jpeg(const unsigned char* data, size_t size, const std::string& name);
+// PNG (png.cpp: 1/2/4/8 bits per channel, all colour types, Adam7; components as stb_image reports them)
+bool looks_like_png(const unsigned char* data, size_t size);
+TextureImage decode_png(const unsigned char* data, size_t size, const std::string& name);
 
 }  // namespace b200host

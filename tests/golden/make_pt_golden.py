@@ -31,7 +31,8 @@ SCENES = {
     "mesh_room_small_notex": [],
     "mesh_room": [],
     "mesh_stress": [],      # loader / BVH-builder stress (scenes/make_scenes.py stress_assets)
-    "jpeg_textures": [],    # JPEG decoding parity with stb_image (scenes/make_jpeg_fixtures.py)
+    "jpeg_textures": [],
+    "png_textures": [],     # PNG decoding parity with stb_image (scenes/make_png_fixtures.py)    # JPEG decoding parity with stb_image (scenes/make_jpeg_fixtures.py)
     "synthetic_4096": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
 }
 # (scene, iterations, extra renderer flags, tag)
