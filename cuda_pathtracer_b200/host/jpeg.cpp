@@ -20,7 +20,10 @@
 // :3069-3070).  tests/test_host_cli.py checks the decoded texels of both reference textures byte for
 // byte against what the reference's own loader (stb_image, via oracle/ref_scene_dump) produces.
 //
-// Not decoded: progressive (SOF2), arithmetic-coded and 12-bit JPEGs -- the loader says so.
+// Progressive files (SOF2: spectral selection + successive approximation) are decoded as well: the scans fill
+// a coefficient store per component (stb_image.h:1744-1890, restated below: first and refinement passes of the
+// DC and the AC band, end-of-band runs), which is de-quantised -- with the same truncation to 16 bits -- and
+// transformed when the last scan is in (:2527-2545).  Arithmetic-coded and 12-bit JPEGs are a load error, as in stb.
 #include "mesh.hpp"
 
 #include <cstdint>
@@ -134,38 +137,50 @@ struct Component {
     int x = 0, y = 0;         // samples actually covered by the image
     int w2 = 0, h2 = 0;       // allocated (whole MCUs)
     std::vector<unsigned char> data;
+    std::vector<short> coef;  // progressive: 64 coefficients per block, (w2 / 8) blocks per row
 };
 
 inline unsigned char clamp_u8(int x) { return (unsigned char)(x < 0 ? 0 : (x > 255 ? 255 : x)); }
 
 constexpr int fix12(double x) { return (int)(x * 4096 + 0.5); }
 
+// 32-bit integer with two's-complement wrap-around: what the transform's arithmetic does on every machine this runs
+// on, spelled out so that a corrupt file (coefficients far outside what a quantiser can produce) wraps instead of
+// running into signed-overflow undefined behaviour.  Valid files never wrap.
+struct W {
+    int v;
+};
+inline W operator+(W a, W b) { return W{(int)((unsigned)a.v + (unsigned)b.v)}; }
+inline W operator-(W a, W b) { return W{(int)((unsigned)a.v - (unsigned)b.v)}; }
+inline W operator*(W a, W b) { return W{(int)((unsigned)a.v * (unsigned)b.v)}; }
+inline W K(double x) { return W{fix12(x)}; }
+
 // One 8-point pass of the ISLOW butterfly.  Returns the even part in e[0..3] and the odd part in
 // o[0..3] (both scaled by 2^12) so that out[k] = e[k] + o[3-k], out[7-k] = e[k] - o[3-k].
-inline void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7, int e[4], int o[4])
+inline void idct_1d(W s0, W s1, W s2, W s3, W s4, W s5, W s6, W s7, W e[4], W o[4])
 {
     // even part
-    int z = (s2 + s6) * fix12(0.5411961f);
-    const int a2 = z + s6 * fix12(-1.847759065f);
-    const int a3 = z + s2 * fix12(0.765366865f);
-    const int a0 = (s0 + s4) * 4096;
-    const int a1 = (s0 - s4) * 4096;
+    const W z = (s2 + s6) * K(0.5411961f);
+    const W a2 = z + s6 * K(-1.847759065f);
+    const W a3 = z + s2 * K(0.765366865f);
+    const W a0 = (s0 + s4) * W{4096};
+    const W a1 = (s0 - s4) * W{4096};
     e[0] = a0 + a3;
     e[3] = a0 - a3;
     e[1] = a1 + a2;
     e[2] = a1 - a2;
     // odd part
-    int b0 = s7, b1 = s5, b2 = s3, b3 = s1;
-    int p3 = b0 + b2, p4 = b1 + b3, p1 = b0 + b3, p2 = b1 + b2;
-    const int p5 = (p3 + p4) * fix12(1.175875602f);
-    b0 = b0 * fix12(0.298631336f);
-    b1 = b1 * fix12(2.053119869f);
-    b2 = b2 * fix12(3.072711026f);
-    b3 = b3 * fix12(1.501321110f);
-    p1 = p5 + p1 * fix12(-0.899976223f);
-    p2 = p5 + p2 * fix12(-2.562915447f);
-    p3 = p3 * fix12(-1.961570560f);
-    p4 = p4 * fix12(-0.390180644f);
+    W b0 = s7, b1 = s5, b2 = s3, b3 = s1;
+    W p3 = b0 + b2, p4 = b1 + b3, p1 = b0 + b3, p2 = b1 + b2;
+    const W p5 = (p3 + p4) * K(1.175875602f);
+    b0 = b0 * K(0.298631336f);
+    b1 = b1 * K(2.053119869f);
+    b2 = b2 * K(3.072711026f);
+    b3 = b3 * K(1.501321110f);
+    p1 = p5 + p1 * K(-0.899976223f);
+    p2 = p5 + p2 * K(-2.562915447f);
+    p3 = p3 * K(-1.961570560f);
+    p4 = p4 * K(-0.390180644f);
     o[3] = b3 + p1 + p4;
     o[2] = b2 + p2 + p3;
     o[1] = b1 + p2 + p4;
@@ -174,28 +189,28 @@ inline void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int 
 
 void idct_block(unsigned char* out, int stride, const short d[64])
 {
-    int v[64], e[4], o[4];
+    W v[64], e[4], o[4];
     for (int c = 0; c < 8; ++c) {
         if (!d[c + 8] && !d[c + 16] && !d[c + 24] && !d[c + 32] && !d[c + 40] && !d[c + 48] && !d[c + 56]) {
-            const int dc = d[c] * 4;                 // DC-only column: same scale as the general case
+            const W dc = W{d[c]} * W{4};             // DC-only column: same scale as the general case
             for (int r = 0; r < 8; ++r) v[c + 8 * r] = dc;
             continue;
         }
-        idct_1d(d[c], d[c + 8], d[c + 16], d[c + 24], d[c + 32], d[c + 40], d[c + 48], d[c + 56], e, o);
+        idct_1d(W{d[c]}, W{d[c + 8]}, W{d[c + 16]}, W{d[c + 24]}, W{d[c + 32]}, W{d[c + 40]}, W{d[c + 48]}, W{d[c + 56]}, e, o);
         for (int k = 0; k < 4; ++k) {
-            const int x = e[k] + 512;                // keep two extra bits: >> 10 instead of >> 12
-            v[c + 8 * k] = (x + o[3 - k]) >> 10;
-            v[c + 8 * (7 - k)] = (x - o[3 - k]) >> 10;
+            const W x = e[k] + W{512};               // keep two extra bits: >> 10 instead of >> 12
+            v[c + 8 * k] = W{(x + o[3 - k]).v >> 10};
+            v[c + 8 * (7 - k)] = W{(x - o[3 - k]).v >> 10};
         }
     }
     for (int r = 0; r < 8; ++r) {
-        const int* s = v + 8 * r;
+        const W* s = v + 8 * r;
         idct_1d(s[0], s[1], s[2], s[3], s[4], s[5], s[6], s[7], e, o);
         unsigned char* q = out + (size_t)r * stride;
         for (int k = 0; k < 4; ++k) {
-            const int x = e[k] + 65536 + (128 << 17);   // rounding + level shift, removed by >> 17
-            q[k] = clamp_u8((x + o[3 - k]) >> 17);
-            q[7 - k] = clamp_u8((x - o[3 - k]) >> 17);
+            const W x = e[k] + W{65536 + (128 << 17)};   // rounding + level shift, removed by >> 17
+            q[k] = clamp_u8((x + o[3 - k]).v >> 17);
+            q[7 - k] = clamp_u8((x - o[3 - k]).v >> 17);
         }
     }
 }
@@ -266,6 +281,8 @@ struct Decoder {
     int width = 0, height = 0, n_comp = 0;
     int h_max = 1, v_max = 1, mcus_x = 0, mcus_y = 0;
     int restart_interval = 0;
+    bool progressive = false;
+    int spec_start = 0, spec_end = 0, succ_high = 0, succ_low = 0, eob_run = 0;
     unsigned char quant[4][64] = {{0}};
     HuffTable dc_tab[4], ac_tab[4];
     Component comp[4];
@@ -337,6 +354,105 @@ struct Decoder {
             c.w2 = mcus_x * c.h * 8;
             c.h2 = mcus_y * c.v * 8;
             c.data.assign((size_t)c.w2 * c.h2, 0);
+            if (progressive) c.coef.assign((size_t)(c.w2 / 8) * (c.h2 / 8) * 64, 0);
+        }
+    }
+
+    // progressive, DC band (stb_image.h:1747-1770): first pass = prediction + point transform, later passes add one bit
+    void prog_dc(BitReader& br, Component& c, short* d)
+    {
+        if (spec_end != 0) throw JpegError("can't merge dc and ac");
+        if (succ_high == 0) {
+            const HuffTable& hd = dc_tab[c.td];
+            if (!hd.present) throw JpegError("missing huffman table");
+            std::memset(d, 0, 64 * sizeof(short));
+            const int t = br.decode(hd);
+            if (t > 15) throw JpegError("bad DC code");
+            c.dc_pred += br.receive_extend(t);
+            d[0] = (short)(c.dc_pred * (1 << succ_low));
+        } else if (br.bit()) {
+            d[0] = (short)(d[0] + (short)(1 << succ_low));
+        }
+    }
+
+    // progressive, AC band [spec_start, spec_end] of one block (stb_image.h:1774-1890)
+    void prog_ac(BitReader& br, Component& c, short* d)
+    {
+        if (spec_start == 0) throw JpegError("can't merge dc and ac");
+        const HuffTable& ha = ac_tab[c.ta];
+        if (!ha.present) throw JpegError("missing huffman table");
+        if (succ_high == 0) {
+            if (eob_run) { --eob_run; return; }
+            int k = spec_start;
+            do {
+                const int rs = br.decode(ha), sbits = rs & 15, r = rs >> 4;
+                if (sbits == 0) {
+                    if (r < 15) {
+                        eob_run = 1 << r;
+                        if (r) eob_run += br.receive(r);
+                        --eob_run;
+                        break;
+                    }
+                    k += 16;
+                } else {
+                    k += r;
+                    if (k > 63) throw JpegError("bad AC run");
+                    d[kNatural[k++]] = (short)(br.receive_extend(sbits) * (1 << succ_low));
+                }
+            } while (k <= spec_end);
+            return;
+        }
+        const short bit = (short)(1 << succ_low);
+        auto refine = [&](short* p) {
+            if (br.bit() && (*p & bit) == 0) *p = (short)(*p > 0 ? *p + bit : *p - bit);
+        };
+        if (eob_run) {
+            --eob_run;
+            for (int k = spec_start; k <= spec_end; ++k) {
+                short* p = &d[kNatural[k]];
+                if (*p != 0) refine(p);
+            }
+            return;
+        }
+        int k = spec_start;
+        do {
+            const int rs = br.decode(ha);
+            int sv = rs & 15, r = rs >> 4;
+            if (sv == 0) {
+                if (r < 15) {
+                    eob_run = (1 << r) - 1;
+                    if (r) eob_run += br.receive(r);
+                    r = 64;                                   // force the end of the block
+                }                                             // r == 15: sixteen zeros, nothing to place
+            } else {
+                if (sv != 1) throw JpegError("bad huffman code");
+                sv = br.bit() ? bit : -bit;
+            }
+            while (k <= spec_end) {                           // skip r zero coefficients, refining the others on the way
+                short* p = &d[kNatural[k++]];
+                if (*p != 0) {
+                    refine(p);
+                } else {
+                    if (r == 0) { *p = (short)sv; break; }
+                    --r;
+                }
+            }
+        } while (k <= spec_end);
+    }
+
+    // progressive: every scan is in -- de-quantise and transform the blocks that cover the image (stb_image.h:2527-2545)
+    void finish_progressive()
+    {
+        for (int n = 0; n < n_comp; ++n) {
+            Component& c = comp[n];
+            const int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3, stride = c.w2 / 8;
+            const unsigned char* q = quant[c.tq];
+            for (int j = 0; j < bh; ++j)
+                for (int i = 0; i < bw; ++i) {
+                    short* d = c.coef.data() + 64 * ((size_t)i + (size_t)j * stride);
+                    for (int k = 0; k < 64; ++k) d[k] = (short)(d[k] * q[k]);
+                    idct_block(c.data.data() + (size_t)c.w2 * j * 8 + i * 8, c.w2, d);
+                }
         }
     }
 
@@ -383,8 +499,14 @@ struct Decoder {
             order[i] = which;
         }
         const int ss = u8(), se = u8(), ahl = u8();
-        if (ss != 0 || ahl != 0) throw JpegError("bad SOS");      // baseline only (stb ignores `se` here too)
-        (void)se;
+        if (progressive) {
+            spec_start = ss; spec_end = se; succ_high = ahl >> 4; succ_low = ahl & 15;
+            if (ss > 63 || se > 63 || ss > se || succ_high > 13 || succ_low > 13) throw JpegError("bad SOS");
+            if (ss != 0 && n != 1) throw JpegError("bad SOS");    // an AC band is never interleaved
+            eob_run = 0;
+        } else if (ss != 0 || ahl != 0) {
+            throw JpegError("bad SOS");                           // baseline (stb ignores `se` here too)
+        }
 
         BitReader br(base + at, base + size);
         for (int i = 0; i < n_comp; ++i) comp[i].dc_pred = 0;
@@ -402,8 +524,20 @@ struct Decoder {
                 return false;
             }
             for (int i = 0; i < n_comp; ++i) comp[i].dc_pred = 0;
+            eob_run = 0;
             todo = restart_interval ? restart_interval : 0x7fffffff;
             return true;
+        };
+        // one block of this scan: straight to samples (baseline) or into the coefficient store (progressive)
+        auto block = [&](Component& c, int bx, int by) {
+            if (!progressive) {
+                decode_block(br, c, d);
+                idct_block(c.data.data() + (size_t)c.w2 * by * 8 + bx * 8, c.w2, d);
+                return;
+            }
+            short* cd = c.coef.data() + 64 * ((size_t)bx + (size_t)by * (c.w2 / 8));
+            if (spec_start == 0) prog_dc(br, c, cd);
+            else prog_ac(br, c, cd);
         };
         bool go = true;
         if (n == 1) {
@@ -412,8 +546,7 @@ struct Decoder {
             const int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3;
             for (int j = 0; j < bh && go; ++j)
                 for (int i = 0; i < bw && go; ++i) {
-                    decode_block(br, c, d);
-                    idct_block(c.data.data() + (size_t)c.w2 * j * 8 + i * 8, c.w2, d);
+                    block(c, i, j);
                     go = restart_if_due();
                 }
         } else {
@@ -423,9 +556,7 @@ struct Decoder {
                         Component& c = comp[order[k]];
                         for (int y = 0; y < c.v; ++y)
                             for (int x = 0; x < c.h; ++x) {
-                                decode_block(br, c, d);
-                                const int x2 = (i * c.h + x) * 8, y2 = (j * c.v + y) * 8;
-                                idct_block(c.data.data() + (size_t)c.w2 * y2 + x2, c.w2, d);
+                                block(c, i * c.h + x, j * c.v + y);
                             }
                     }
                     go = restart_if_due();
@@ -464,7 +595,10 @@ struct Decoder {
                 read_sof(u16());
                 have_sof = true;
             } else if (m == 0xC2) {
-                throw JpegError("progressive JPEG is not decoded here (baseline only)");
+                if (have_sof) throw JpegError("two SOF markers");
+                progressive = true;
+                read_sof(u16());
+                have_sof = true;
             } else if (m == 0xC3 || (m >= 0xC5 && m <= 0xCF && m != 0xC8 && m != 0xCC)) {
                 throw JpegError("unsupported JPEG coding process");
             } else if (m == 0xC4) {
@@ -489,6 +623,7 @@ struct Decoder {
             }
         }
         if (!have_scan) throw JpegError("no image data");
+        if (progressive) finish_progressive();
 
         TextureImage t;
         t.width = width;

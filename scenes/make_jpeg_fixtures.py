@@ -7,7 +7,7 @@ They cover what the host decoder (cuda_pathtracer_b200/host/jpeg.cpp) must repro
 against stb_image, the reference's texture reader (sceneStructs.h:170-175): every chroma layout with
 its own upsampling filter (4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1 -> the generic path), grayscale, widths
 and heights that are not multiples of the MCU, one-pixel-wide images, restart intervals, optimised
-(non-default) Huffman tables, and low quality (large quantisers -> clamping in the inverse DCT).
+(non-default) Huffman tables, low quality (large quantisers -> clamping in the inverse DCT), and progressive files.
 tests/golden/jpeg_textures.scene.bin is the dump of the reference's own loader for the scene
 (tests/golden/make_pt_golden.py); tests/test_host_cli.py compares this repo's loader with it."""
 import json
@@ -45,6 +45,13 @@ CASES = [
     ("j_1wide.jpg", 1, 9, "RGB", dict(quality=90, subsampling="4:2:0")),
     ("j_1high.jpg", 19, 1, "RGB", dict(quality=90, subsampling="4:2:0")),
     ("j_2wide_422.jpg", 2, 5, "RGB", dict(quality=90, subsampling="4:2:2")),
+    # progressive (SOF2): spectral selection + successive approximation, end-of-band runs, restart intervals
+    ("j_prog_420.jpg", 53, 41, "RGB", dict(quality=80, subsampling="4:2:0", progressive=True)),
+    ("j_prog_444.jpg", 37, 21, "RGB", dict(quality=92, subsampling="4:4:4", progressive=True)),
+    ("j_prog_422_opt.jpg", 50, 19, "RGB", dict(quality=60, subsampling="4:2:2", progressive=True, optimize=True)),
+    ("j_prog_gray.jpg", 23, 17, "L", dict(quality=85, progressive=True)),
+    ("j_prog_rst.jpg", 64, 48, "RGB", dict(quality=75, subsampling="4:2:0", progressive=True, restart_marker_blocks=2)),
+    ("j_prog_lowq.jpg", 40, 40, "RGB", dict(quality=8, subsampling="4:2:0", progressive=True)),
 ]
 
 

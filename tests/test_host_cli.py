@@ -23,7 +23,7 @@ EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
 SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
           "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096",
           "mesh_room", "mesh_room_small", "mesh_room_small_notex", "mesh_stress",   # OBJ meshes + BVH + textures ("B2PTSCN2")
-          "jpeg_textures",
+          "jpeg_textures",   # + six progressive ones
           "png_textures"]    # 25 PNGs (scenes/make_png_fixtures.py) decoded by host/png.cpp vs stb_image   # twelve baseline JPEGs (scenes/make_jpeg_fixtures.py) decoded by host/jpeg.cpp vs stb_image
 
 
@@ -95,8 +95,8 @@ def test_reference_room_scene_loads_unmodified(tmp_path):
 
 
 def test_texture_decoders_reject_what_they_do_not_decode(tmp_path):
-    """progressive JPEG, 16-bit PNG (stb_image 2.06 refuses it too), truncated data: a load error naming the file
-    (exit 255 as for any load error), never garbage texels"""
+    """arithmetic-coded JPEG, 16-bit PNG (stb_image 2.06 refuses both too), truncated data: a load error naming the
+    file (exit 255 as for any load error), never garbage texels; a progressive JPEG loads"""
     from PIL import Image
     tex = tmp_path / "Textures"
     tex.mkdir()
@@ -105,11 +105,14 @@ def test_texture_decoders_reject_what_they_do_not_decode(tmp_path):
     img.save(str(tex / "ok.jpg"), "JPEG")
     whole = (tex / "ok.jpg").read_bytes()
     (tex / "cut.jpg").write_bytes(whole[:len(whole) // 3])
+    sof = whole.index(b"\xff\xc0")
+    (tex / "arith.jpg").write_bytes(whole[:sof] + b"\xff\xc9" + whole[sof + 2:])      # SOF9: arithmetic coding
     Image.fromarray((np.arange(12 * 10 * 3) * 97 % 65536).astype(np.uint16).reshape(10, 12 * 3)[:, :12]).save(str(tex / "deep.png"))   # 16-bit grey
     img.save(str(tex / "ok.png"), "PNG")
     whole_png = (tex / "ok.png").read_bytes()
     (tex / "cut.png").write_bytes(whole_png[:len(whole_png) // 2])
-    for name, code in (("ok.jpg", 0), ("prog.jpg", 255), ("cut.jpg", 255), ("ok.png", 0), ("deep.png", 255), ("cut.png", 255)):
+    for name, code in (("ok.jpg", 0), ("prog.jpg", 0), ("cut.jpg", 255), ("arith.jpg", 255), ("ok.png", 0), ("deep.png", 255),
+                       ("cut.png", 255)):
         scene = {"Materials": {"m": {"TYPE": "Diffuse", "RGB": [1, 1, 1], "TEXTURE_FILE": name}},
                  "Camera": {"RES": [8, 8], "FOVY": 45.0, "ITERATIONS": 1, "DEPTH": 1, "FILE": "t", "EYE": [0, 0, 5],
                             "LOOKAT": [0, 0, 0], "UP": [0, 1, 0]},
