@@ -83,6 +83,7 @@ struct b200pt {
     size_t prof_used = 0;              // events in use (2 per batch)
     double bounce_ms = 0.0;
     uint64_t bounce_launches = 0;
+    LaunchCfg cfg;                     // SM count / resident grids of the persistent kernels on h->device
 };
 
 namespace {
@@ -92,6 +93,27 @@ namespace {
         cudaError_t e__ = (x);                   \
         if (e__ != cudaSuccess) return (int)e__; \
     } while (0)
+
+// Every entry point runs on the device the handle was created on, whatever device the calling thread has
+// current (renderers on several GPUs, or driven from several host threads, may coexist in one process);
+// the caller's current device is restored on return.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int device)
+    {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != device) {
+            err = cudaSetDevice(device);
+            switched = err == cudaSuccess;
+        }
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
+#define ON_DEVICE(h)                                       \
+    DeviceGuard guard__((h)->device);                       \
+    if (guard__.err != cudaSuccess) return (int)guard__.err
 
 int dev_alloc(void** p, size_t bytes)
 {
@@ -321,7 +343,7 @@ int validate_scene(const b200pt_scene* sc, const b200pt_scene_ext* ext)
     for (int i = 0; i < n_nodes; ++i) {
         const b200pt_bvh_node& nd = ext->bvh[i];
         if (nd.sub_areas > 0) {
-            if (nd.first_area_idx < 0 || nd.first_area_idx + nd.sub_areas > n_tris) return B200_E_BADARG;
+            if (nd.first_area_idx < 0 || nd.first_area_idx > n_tris || nd.sub_areas > n_tris - nd.first_area_idx) return B200_E_BADARG;   // (no int overflow)
         } else if (nd.axis < 0 || nd.axis > 2 || nd.rchild_idx <= i || nd.rchild_idx >= n_nodes || i + 1 >= n_nodes) {
             return B200_E_BADARG;
         }
@@ -378,6 +400,7 @@ int upload_meshes(b200pt* h, const b200pt_scene_ext* ext)
             const b200pt_texture& t = ext->textures[i];
             const size_t bytes = (size_t)t.width * t.height * t.components;
             recs[i].w = t.width; recs[i].h = t.height; recs[i].comp = t.components;
+            if (pool.size() + bytes > 0xffffffffull) return B200_E_BADARG;     // TexRec::offset is 32 bits
             recs[i].offset = (unsigned)pool.size();
             pool.insert(pool.end(), t.pixels, t.pixels + bytes);
             while (pool.size() % 16) pool.push_back(0);
@@ -435,6 +458,7 @@ void b200pt_default_options(b200pt_options* o)
     o->geom_bvh = 0;
     o->mesh_brute_force = 0;
     o->mesh_no_bbox = 0;
+    o->use_thrust_partition = 0;
 }
 
 int b200pt_create(const b200pt_scene* sc, b200pt** out) { return b200pt_create_ext(sc, nullptr, out); }
@@ -449,8 +473,10 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
 
     b200pt* h = new (std::nothrow) b200pt();
     if (!h) return B200_E_NOMEM;
-    CK(cudaGetDevice(&h->device));
-    CK(configure_kernels());
+    // (from here on every failure goes through b200pt_destroy: nothing allocated so far is leaked)
+    int r = (int)cudaGetDevice(&h->device);
+    if (!r) r = (int)configure_kernels();
+    if (r) { b200pt_destroy(h); return r; }
     h->W = sc->camera.resolution[0];
     h->H = sc->camera.resolution[1];
     h->P = h->W * h->H;
@@ -464,18 +490,17 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
 
     std::vector<PrimRec> prims(sc->n_geoms);
     for (int i = 0; i < sc->n_geoms; ++i) pack_prim(sc->geoms[i], prims[i]);
-    int r = dev_alloc((void**)&h->d_prims, sizeof(PrimRec) * prims.size());
+    r = dev_alloc((void**)&h->d_prims, sizeof(PrimRec) * prims.size());
     if (!r) r = dev_alloc((void**)&h->d_mats, sizeof(MatRec) * (size_t)sc->n_materials);
     if (!r) r = dev_alloc((void**)&h->d_image, sizeof(float) * 3 * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_segments, sizeof(unsigned long long));
     if (!r) r = dev_alloc((void**)&h->d_tickets, sizeof(int) * (size_t)(h->depth > 0 ? h->depth : 1));
-    if (r) { b200pt_destroy(h); return r; }
-    CK(cudaMemcpy(h->d_prims, prims.data(), sizeof(PrimRec) * prims.size(), cudaMemcpyHostToDevice));
     static_assert(sizeof(b200pt_material) == sizeof(MatRec), "material layouts must agree");
-    CK(cudaMemcpy(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice));
-    CK(cudaEventCreate(&h->ev0));
-    CK(cudaEventCreate(&h->ev1));
-    r = b200pt_reset(h);
+    if (!r) r = (int)cudaMemcpy(h->d_prims, prims.data(), sizeof(PrimRec) * prims.size(), cudaMemcpyHostToDevice);
+    if (!r) r = (int)cudaMemcpy(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice);
+    if (!r) r = (int)cudaEventCreate(&h->ev0);
+    if (!r) r = (int)cudaEventCreate(&h->ev1);
+    if (!r) r = b200pt_reset(h);
     if (!r && ext) r = upload_meshes(h, ext);
     if (!r) r = upload_geom_bvh(h, sc, prims, nullptr);
     if (!r && cudaStreamSynchronize(nullptr) != cudaSuccess) r = (int)cudaGetLastError();
@@ -487,6 +512,7 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
 int b200pt_destroy(b200pt* h)
 {
     if (!h) return 0;
+    DeviceGuard guard(h->device);
     cudaFree(h->d_prims); cudaFree(h->d_mats); cudaFree(h->d_pool); cudaFree(h->d_counts);
     cudaFree(h->d_desc); cudaFree(h->d_tickets); cudaFree(h->d_segments); cudaFree(h->d_image);
     cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
@@ -516,6 +542,7 @@ int b200pt_set_options(b200pt* h, const b200pt_options* o)
 int b200pt_reset(b200pt* h)
 {
     if (!h) return B200_E_BADARG;
+    ON_DEVICE(h);
     CK(cudaMemset(h->d_image, 0, sizeof(float) * 3 * (size_t)h->P));
     CK(cudaMemset(h->d_segments, 0, sizeof(unsigned long long)));
     h->iterations = 0;
@@ -532,6 +559,7 @@ int b200pt_reset(b200pt* h)
 int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
 {
     if (!h) return B200_E_BADARG;
+    ON_DEVICE(h);
     {   // triangles, BVH and textures stay as uploaded: validate against their counts
         const int bad = validate_scene_counts(sc, h->mesh.n_tris, h->mesh.n_nodes, h->mesh.n_tex);
         if (bad) return bad;
@@ -557,6 +585,7 @@ int b200pt_update_scene(b200pt* h, const b200pt_scene* sc, void* stream)
 int b200pt_set_profiling(b200pt* h, int enable)
 {
     if (!h) return B200_E_BADARG;
+    ON_DEVICE(h);
     int r = collect_profile(h);
     if (r) return r;
     h->profiling = enable != 0;
@@ -566,10 +595,39 @@ int b200pt_set_profiling(b200pt* h, int enable)
 int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void* stream, int sync)
 {
     if (!h || n_iters < 0 || iter_stride < 1 || first_iter < 0) return B200_E_BADARG;
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t)stream;
-    const int batch = h->opt.batch > 0 ? h->opt.batch : default_batch(h->P);
-    int r = ensure_batch(h, batch);
+    // meshIntersectionTest instead of the BVH walk: the reference's own loop over all primitives (the geometry
+    // BVH handles MESH primitives through the one shared walk, which this mode does not have)
+    const bool brute = h->opt.mesh_brute_force != 0 && h->mesh.n_tris > 0;
+    const bool use_gb = !brute && h->gb.n_nodes > 0 && (h->opt.geom_bvh > 0 || (h->opt.geom_bvh == 0 && h->n_indexed >= PT_GBVH_AUTO));
+    const bool sort_on = h->opt.sort_by_material != 0;
+    // Scenes whose closest hit is a tree walk (triangle meshes; the geometry BVH proper of a many-primitive
+    // scene) run closest hit and shading as TWO kernels, the hit records going through HBM (36 B per path) --
+    // the material-sort pipeline without the sort.  The walk alone needs fewer registers than the fused
+    // kernel and its long, uneven loops no longer hold the shading state hostage: config 5 89.5 -> 102.3
+    // spp/s, mesh room 355 -> 411 (profiles/r5_ab_variants.txt).  Same hits, same slot order, same seeds: the
+    // image does not change.  Small mesh-free scenes (Cornell) keep the fused persistent kernel.
+#ifndef PT_SPLIT_MODE
+#define PT_SPLIT_MODE 2      // 0 = never, 1 = scenes with meshes, 2 = + geometry BVH proper, 3 = always (experiment)
+#endif
+    const bool split_only = !sort_on && ((PT_SPLIT_MODE >= 1 && h->mesh.n_nodes > 0) ||
+                                         (PT_SPLIT_MODE >= 2 && use_gb && h->gb.n_small == 0) || PT_SPLIT_MODE >= 3);
+    const bool cache_on = h->opt.first_bounce_cache && !h->opt.ssaa && !h->opt.dof;
+
+    // iterations in flight: never more than this call traces (a one-iteration call, e.g. the reference-shaped
+    // pathtrace(), then allocates one slot, not 32), and halved until the pools fit into device memory
+    int batch = h->opt.batch > 0 ? h->opt.batch : default_batch(h->P);
+    if (n_iters > 0 && batch > n_iters) batch = n_iters;
+    int r = 0;
+    for (;;) {
+        r = ensure_batch(h, batch);
+        if (!r && (sort_on || split_only)) r = ensure_sort(h, batch);
+        if (r != B200_E_NOMEM || batch == 1) break;
+        batch = (batch + 1) / 2;
+    }
     if (r) return r;
+    if (cache_on) { r = ensure_cache(h); if (r) return r; }
 
     RenderParams p{};
     const size_t plane = (size_t)h->batch_cap * h->P;
@@ -587,10 +645,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.mats = h->d_mats;
     p.n_prims = h->n_prims;
     p.n_mats = h->n_mats;
-    // meshIntersectionTest instead of the BVH walk: the reference's own loop over all primitives (the geometry
-    // BVH handles MESH primitives through the one shared walk, which this mode does not have)
-    const bool brute = h->opt.mesh_brute_force != 0 && h->mesh.n_tris > 0;
-    if (!brute && h->gb.n_nodes > 0 && (h->opt.geom_bvh > 0 || (h->opt.geom_bvh == 0 && h->n_indexed >= PT_GBVH_AUTO))) p.gb = h->gb;
+    if (use_gb) p.gb = h->gb;
     p.cam = h->cam;
     p.opt.rr = h->opt.russian_roulette;
     p.opt.ssaa = h->opt.ssaa;
@@ -604,21 +659,6 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     p.tickets = h->d_tickets;
     p.stride = iter_stride;
 
-    const bool sort_on = h->opt.sort_by_material != 0;
-    // Scenes whose closest hit is a tree walk (triangle meshes; the geometry BVH proper of a many-primitive
-    // scene) run closest hit and shading as TWO kernels, the hit records going through HBM (36 B per path) --
-    // the material-sort pipeline without the sort.  The walk alone needs fewer registers than the fused
-    // kernel and its long, uneven loops no longer hold the shading state hostage: config 5 89.5 -> 102.3
-    // spp/s, mesh room 355 -> 411 (profiles/r5_ab_variants.txt).  Same hits, same slot order, same seeds: the
-    // image does not change.  Small mesh-free scenes (Cornell) keep the fused persistent kernel.
-#ifndef PT_SPLIT_MODE
-#define PT_SPLIT_MODE 2      // 0 = never, 1 = scenes with meshes, 2 = + geometry BVH proper, 3 = always (experiment)
-#endif
-    const bool split_only = !sort_on && ((PT_SPLIT_MODE >= 1 && h->mesh.n_nodes > 0) ||
-                                         (PT_SPLIT_MODE >= 2 && p.gb.n_nodes > 0 && p.gb.n_small == 0) || PT_SPLIT_MODE >= 3);
-    const bool cache_on = h->opt.first_bounce_cache && !h->opt.ssaa && !h->opt.dof;
-    if (sort_on || split_only) { r = ensure_sort(h, batch); if (r) return r; }
-    if (cache_on) { r = ensure_cache(h); if (r) return r; }
     p.hit_n = h->d_hit_n;
     p.hit_k = h->d_hit_k;
     p.hist = h->d_hist;
@@ -654,16 +694,16 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             p.epoch = h->epoch;
             p.cache_mode = (b == 0 && cache_on) ? (h->cache_valid ? 2 : 1) : 0;
             if (split_only) {
-                if (p.cache_mode != 2) { CK(launch_isect(p, s)); h->launches += 1; }
+                if (p.cache_mode != 2) { CK(launch_isect(p, h->cfg, s)); h->launches += 1; }
                 p.perm_in = nullptr;
                 CK(launch_shade(p, s));
                 h->launches += 1;
             } else if (!sort_on) {
-                CK(launch_bounce(p, s));
+                CK(launch_bounce(p, h->cfg, s));
                 h->launches += 1;
             } else {
                 // computeIntersections -> sort_by_key(materialId) -> shadeMaterials (pathtrace.cu:470-497)
-                if (p.cache_mode != 2) { CK(launch_isect(p, s)); h->launches += 1; }
+                if (p.cache_mode != 2) { CK(launch_isect(p, h->cfg, s)); h->launches += 1; }
                 const int bins = sort_bins(h), passes = sort_passes(h);
                 for (int pass = 0; pass < passes; ++pass) {
                     p.perm_in = pass == 0 ? nullptr : h->d_perm[(pass - 1) & 1];
@@ -703,6 +743,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
 int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream)
 {
     if (!h || !dev_rgba8 || iter_divisor <= 0) return B200_E_BADARG;
+    ON_DEVICE(h);
     CK(launch_tonemap(h->d_image, h->P, iter_divisor, (uchar4*)dev_rgba8, (cudaStream_t)stream));
     h->launches += 1;
     return 0;
@@ -711,6 +752,7 @@ int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream
 int b200pt_read_sum(b200pt* h, float* host_rgb)
 {
     if (!h || !host_rgb) return B200_E_BADARG;
+    ON_DEVICE(h);
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(host_rgb, h->d_image, sizeof(float) * 3 * (size_t)h->P, cudaMemcpyDeviceToHost));
     return 0;
@@ -719,6 +761,7 @@ int b200pt_read_sum(b200pt* h, float* host_rgb)
 int b200pt_write_sum(b200pt* h, const float* host_rgb)
 {
     if (!h || !host_rgb) return B200_E_BADARG;
+    ON_DEVICE(h);
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(h->d_image, host_rgb, sizeof(float) * 3 * (size_t)h->P, cudaMemcpyHostToDevice));
     return 0;
@@ -735,6 +778,7 @@ int b200pt_sum_device_ptr(b200pt* h, void** dev_ptr, size_t* n_floats)
 int b200pt_get_stats(b200pt* h, b200pt_stats* st)
 {
     if (!h || !st) return B200_E_BADARG;
+    ON_DEVICE(h);
     CK(cudaDeviceSynchronize());
     unsigned long long seg = 0;
     CK(cudaMemcpy(&seg, h->d_segments, sizeof(seg), cudaMemcpyDeviceToHost));
@@ -776,6 +820,7 @@ static void fill_params(const b200pt* h, RenderParams& p)
 int b200pt_debug_raygen(b200pt* h, int iter, void* d_segments, void* stream)
 {
     if (!h || !d_segments) return B200_E_BADARG;
+    ON_DEVICE(h);
     RenderParams p{};
     fill_params(h, p);
     CK(launch_debug_raygen(p, iter, (float*)d_segments, (cudaStream_t)stream));
@@ -787,6 +832,7 @@ int b200pt_debug_intersect(b200pt* h, int n, const void* d_segments, void* d_ise
 {
     if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
     if (n == 0) return 0;
+    ON_DEVICE(h);
     MeshScene mesh = h->mesh;
     mesh.brute = h->opt.mesh_brute_force != 0 && mesh.n_tris > 0 ? (h->opt.mesh_no_bbox ? 2 : 1) : 0;
     CK(launch_debug_intersect(h->d_prims, h->n_prims, mesh, n, (const float*)d_segments, (float*)d_isects, (cudaStream_t)stream));
@@ -798,6 +844,7 @@ int b200pt_debug_shade(b200pt* h, int iter, int n, const void* d_isects, void* d
 {
     if (!h || n < 0 || (n > 0 && (!d_segments || !d_isects))) return B200_E_BADARG;
     if (n == 0) return 0;
+    ON_DEVICE(h);
     RenderParams p{};
     fill_params(h, p);
     CK(launch_debug_shade(h->d_mats, h->mesh, p.opt, iter, n, (const float*)d_isects, (float*)d_segments, (cudaStream_t)stream));

@@ -1518,46 +1518,42 @@ bool bounce_is_persistent(const RenderParams& p)
 
 // CTAs of a persistent launch: as many as are resident at once (more would only queue up behind them)
 template <typename K>
-static cudaError_t persistent_grid(K kernel, size_t smem, int work_items, int& grid)
+static cudaError_t persistent_grid(K kernel, LaunchCfg& cfg, size_t smem, int& grid)
 {
-    static int sm_count = 0;
-    if (sm_count == 0) {
+    if (cfg.sm_count == 0) {
         int dev = 0;
         cudaError_t e = cudaGetDevice(&dev);
-        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&cfg.sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
     }
     int per_sm = 0;
     const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PT_THREADS, smem);
     if (e != cudaSuccess) return e;
-    grid = sm_count * (per_sm > 0 ? per_sm : 1);
-    if (grid > work_items) grid = work_items;
+    grid = cfg.sm_count * (per_sm > 0 ? per_sm : 1);
     if (grid < 1) grid = 1;
     return cudaSuccess;
 }
 
 template <int CACHE, int GB>
-static cudaError_t launch_persistent(const RenderParams& p, size_t smem, cudaStream_t s)
+static cudaError_t launch_persistent(const RenderParams& p, LaunchCfg& cfg, size_t smem, cudaStream_t s)
 {
-    // the occupancy query is a host-side table lookup, but cache it anyway per shared-memory size
-    static size_t cached_smem = ~(size_t)0;
-    static int cached_grid = 0;
-    if (cached_smem != smem) {
+    // the occupancy query is a host-side table lookup, but cache it anyway per shared-memory size (per handle)
+    if (cfg.bounce_smem[CACHE][GB] != smem + 1) {
         int g = 0;
-        const cudaError_t e = persistent_grid(k_bounce<CACHE, GB>, smem, 1 << 30, g);
+        const cudaError_t e = persistent_grid(k_bounce<CACHE, GB>, cfg, smem, g);
         if (e != cudaSuccess) return e;
-        cached_grid = g;
-        cached_smem = smem;
+        cfg.bounce_grid[CACHE][GB] = g;
+        cfg.bounce_smem[CACHE][GB] = smem + 1;
     }
-    const int items = p.batch * p.ptiles;
-    k_bounce<CACHE, GB><<<cached_grid < items ? cached_grid : items, PT_THREADS, smem, s>>>(p);
+    const int items = p.batch * p.ptiles, grid = cfg.bounce_grid[CACHE][GB];
+    k_bounce<CACHE, GB><<<grid < items ? grid : items, PT_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
 // which closest-hit search a launch uses: 0 = linear scan, 1 = geometry BVH, 2 = small-scene search
 static int search_mode(const RenderParams& p) { return p.gb.n_nodes > 0 ? (p.gb.n_small > 0 ? 2 : 1) : 0; }
 
-cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
+cudaError_t launch_bounce(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
 {
     const int mode = search_mode(p);
     // Scenes whose tiles are long and uneven -- a tree walk per ray: the geometry BVH of a many-primitive scene --
@@ -1581,10 +1577,10 @@ cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s)
     }
     if (bounce_is_persistent(p)) {
         const size_t smem = persist_smem_bytes(p.n_prims, p.n_mats, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
-        if (p.cache_mode == 2) return launch_persistent<2, 0>(p, persist_smem_bytes(0, p.n_mats, 0, 0), s);
+        if (p.cache_mode == 2) return launch_persistent<2, 0>(p, cfg, persist_smem_bytes(0, p.n_mats, 0, 0), s);
         if (p.cache_mode == 1)
-            return mode == 2 ? launch_persistent<1, 2>(p, smem, s) : mode == 1 ? launch_persistent<1, 1>(p, smem, s) : launch_persistent<1, 0>(p, smem, s);
-        return mode == 2 ? launch_persistent<0, 2>(p, smem, s) : mode == 1 ? launch_persistent<0, 1>(p, smem, s) : launch_persistent<0, 0>(p, smem, s);
+            return mode == 2 ? launch_persistent<1, 2>(p, cfg, smem, s) : mode == 1 ? launch_persistent<1, 1>(p, cfg, smem, s) : launch_persistent<1, 0>(p, cfg, smem, s);
+        return mode == 2 ? launch_persistent<0, 2>(p, cfg, smem, s) : mode == 1 ? launch_persistent<0, 1>(p, cfg, smem, s) : launch_persistent<0, 0>(p, cfg, smem, s);
     }
     // linear scan over more than one chunk of primitives (geom_bvh off): one CTA per tile, chunks streamed by TMA
     const dim3 grid(p.tiles, p.batch);
@@ -1599,28 +1595,25 @@ static size_t dyn_smem_bytes(int n_gnodes)
     return sizeof(DynShared) + (size_t)(n_gnodes < PT_DYN_GNODES ? n_gnodes : PT_DYN_GNODES) * 4 * sizeof(float4);
 }
 
-cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
+cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
 {
     const int mode = search_mode(p);
 #ifndef PT_NO_DYN
     if (mode == 1 && p.mesh.n_nodes == 0) {           // geometry BVH proper, no meshes: dynamic ray fetch
-        static int grid = 0;
         const size_t smem = dyn_smem_bytes(p.gb.n_nodes);
-        if (grid == 0) {
-            const cudaError_t e = persistent_grid(k_isect_dyn, dyn_smem_bytes(1 << 30), 1 << 30, grid);
+        if (cfg.dyn_grid == 0) {
+            const cudaError_t e = persistent_grid(k_isect_dyn, cfg, dyn_smem_bytes(1 << 30), cfg.dyn_grid);
             if (e != cudaSuccess) return e;
         }
-        k_isect_dyn<<<grid, PT_THREADS, smem, s>>>(p);
+        k_isect_dyn<<<cfg.dyn_grid, PT_THREADS, smem, s>>>(p);
         return cudaGetLastError();
     }
 #endif
 #ifndef PT_NO_DYN_MESH
     if (mode == 2 && p.mesh.n_nodes > 0 && !p.mesh.literal_walk && !p.mesh.brute) {   // small scene + meshes
-        static int mgrid = 0;
-        static size_t mgrid_smem = ~(size_t)0;
         const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small)
                             - sizeof(BounceShared) + sizeof(DynShared);
-        if (mgrid_smem != smem) {
+        if (cfg.dyn_mesh_smem != smem) {
             // The walk lives on L1 hits: ask for no more shared-memory carve-out than the four resident CTAs need
             // (+ 1 KB each that the system reserves).  The driver's own choice is larger: mesh room 661 -> 693 spp/s
             // with the 25 % this comes to there.  (For k_isect_dyn, whose CTAs use 1.3 KB, the same hint LOSES 7 %.)
@@ -1632,11 +1625,11 @@ cudaError_t launch_isect(const RenderParams& p, cudaStream_t s)
             if (pct > 100) pct = 100;
             e = cudaFuncSetAttribute(k_isect_dyn_mesh, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
             if (e != cudaSuccess) return e;
-            e = persistent_grid(k_isect_dyn_mesh, smem, 1 << 30, mgrid);
+            e = persistent_grid(k_isect_dyn_mesh, cfg, smem, cfg.dyn_mesh_grid);
             if (e != cudaSuccess) return e;
-            mgrid_smem = smem;
+            cfg.dyn_mesh_smem = smem;
         }
-        k_isect_dyn_mesh<<<mgrid, PT_THREADS, smem, s>>>(p);
+        k_isect_dyn_mesh<<<cfg.dyn_mesh_grid, PT_THREADS, smem, s>>>(p);
         return cudaGetLastError();
     }
 #endif

@@ -100,11 +100,26 @@ struct RenderParams {
     GeomBvh gb;
 };
 
+// Launch configuration of ONE renderer handle: SM count of its device and the resident-CTA grids of the
+// persistent kernels, computed on first use for the device the handle was created on.  Kept per handle (not in
+// function-local statics) so that renderers on different GPUs, or driven from different host threads, of one
+// process do not share or race on it (include/b200_pt.h: several renderers may coexist).
+struct LaunchCfg {
+    int sm_count = 0;
+    size_t bounce_smem[3][3] = {};     // [CACHE][GB]: shared memory the cached grid was computed for (0 = not yet)
+    int bounce_grid[3][3] = {};
+    int dyn_grid = 0;                  // k_isect_dyn
+    int dyn_mesh_grid = 0;             // k_isect_dyn_mesh
+    size_t dyn_mesh_smem = ~(size_t)0;
+    int bucket_grid = 0;               // k_isect_bucket / k_shade_bucket (one-pass material bucketing)
+    size_t bucket_smem = ~(size_t)0;
+};
+
 size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0, int n_small = 0);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
-cudaError_t launch_bounce(const RenderParams& p, cudaStream_t s);           // fused (honours p.cache_mode)
+cudaError_t launch_bounce(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);   // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
-cudaError_t launch_isect(const RenderParams& p, cudaStream_t s);
+cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);
 cudaError_t launch_sort_hist(const RenderParams& p, int pass, int bins, cudaStream_t s);
 cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaStream_t s);
 cudaError_t launch_shade(const RenderParams& p, cudaStream_t s);

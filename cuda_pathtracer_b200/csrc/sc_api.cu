@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <new>
 #include <vector>
 
 #include "../../include/b200_sc.h"
@@ -64,11 +65,16 @@ int ensure_lookback(b200_sc_ctx* c, unsigned n)
     return 0;
 }
 
-unsigned next_epoch(b200_sc_ctx* c)
+// A context is used from one stream at a time (launches sharing its workspace must be stream-ordered, b200_sc.h);
+// the wrap-around wipe is therefore enqueued on the launch stream, behind the launches that still use the old epochs.
+unsigned next_epoch(b200_sc_ctx* c, cudaStream_t s)
 {
     c->epoch += 1;
     if (c->epoch >= (1u << 30)) {   // wrap: wipe descriptors once every 2^30 launches
-        cudaMemset(c->desc, 0, c->desc_cap * sizeof(unsigned long long));
+        cudaMemsetAsync(c->desc, 0, c->desc_cap * sizeof(unsigned long long), s);
+        // ... and BOTH ticket counters: 2^30 - 1 and 1 are both odd, so the first launch after the wrap would
+        // otherwise reuse the counter the last launch before it has just run up (SC_LB_TICKET builds only)
+        cudaMemsetAsync(c->tickets, 0, 2 * sizeof(unsigned), s);
         c->epoch = 1;
     }
     return c->epoch;
@@ -139,14 +145,20 @@ int b200_sc_ctx_create(b200_sc_ctx** out)
     if (!out) return B200_E_BADARG;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { cudaGetLastError(); return B200_E_NODEVICE; }
-    b200_sc_ctx* c = new b200_sc_ctx();
-    CK(cudaGetDevice(&c->device));
-    CK(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device));
-    CK(cudaMalloc((void**)&c->tickets, 2 * sizeof(unsigned)));
-    CK(cudaMemset(c->tickets, 0, 2 * sizeof(unsigned)));
-    CK(cudaMalloc((void**)&c->small, 4 * sizeof(int)));
-    CK(cudaEventCreate(&c->ev0));
-    CK(cudaEventCreate(&c->ev1));
+    b200_sc_ctx* c = new (std::nothrow) b200_sc_ctx();
+    if (!c) return B200_E_NOMEM;
+    cudaError_t e = cudaGetDevice(&c->device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->tickets, 2 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(c->tickets, 0, 2 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->small, 4 * sizeof(int));
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
+    if (e != cudaSuccess) {          // nothing allocated so far is leaked
+        cudaGetLastError();
+        b200_sc_ctx_destroy(c);
+        return e == cudaErrorMemoryAllocation ? B200_E_NOMEM : (int)e;
+    }
     *out = c;
     return 0;
 }
@@ -181,7 +193,7 @@ int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int va
     case B200_SCAN_LOOKBACK: {
         int r = ensure_lookback(c, un);
         if (r) return r;
-        CK(launch_scan_lookback(d_in, d_out, un, c->desc, c->tickets, next_epoch(c), d_seed, d_total, s));
+        CK(launch_scan_lookback(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, s));
         c->last_launches = 1;
         return 0;
     }
@@ -227,7 +239,7 @@ int b200_compact_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int
     if (n == 0) { CK(cudaMemsetAsync(d_count, 0, sizeof(int), s)); return 0; }
     int r = ensure_lookback(c, (unsigned)n);
     if (r) return r;
-    CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c), d_count, s));
+    CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, s));
     c->last_launches = 1;
     return 0;
 }

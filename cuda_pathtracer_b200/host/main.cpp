@@ -13,6 +13,7 @@
 //   --iters N            override Camera.ITERATIONS
 //   --no-rr              russianRoulette = false          --sort        sortbyMaterial = true
 //   --no-ssaa            SSAA = false                     --no-dof      DoF = false
+//   --thrust-partition   useThrustPartition = true (pathtrace.cu:499-503): the same stable partition, the same image
 //   --aperture A         (default 0.1)                    --focal F     focal_len (default 10.0)
 //   --first-bounce-cache reuse bounce 0's hits (honoured only with --no-ssaa --no-dof)
 //   --no-bvh             useBVHtree = false: meshes through meshIntersectionTest (every triangle of a mesh)
@@ -111,7 +112,7 @@ int main(int argc, char** argv)
         if (a == "--iters") iters = std::atoi(next());
         else if (a == "--no-rr") opt.russian_roulette = 0;
         else if (a == "--sort" || a == "--sort-material") opt.sort_by_material = 1;
-        else if (a == "--thrust-partition") { /* both partitions give the same stable result here */ }
+        else if (a == "--thrust-partition") opt.use_thrust_partition = 1;   // useThrustPartition: same stable partition, same image
         else if (a == "--no-ssaa") opt.ssaa = 0;
         else if (a == "--no-dof") opt.dof = 0;
         else if (a == "--aperture") opt.aperture = (float)std::atof(next());

@@ -57,7 +57,9 @@ struct Inflater {
     uint32_t acc = 0;
     int bits = 0;
     std::vector<uint8_t> out;
+    size_t cap = ~(size_t)0;          // the image needs no more output than this: a small file must not expand without bound
 
+    void grew() { if (out.size() > cap) throw PngError("too much pixel data"); }
     int bit()
     {
         if (bits == 0) {
@@ -98,7 +100,7 @@ struct Inflater {
         static const uint8_t dext[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
         for (;;) {
             const int s = decode(lit);
-            if (s < 256) { out.push_back((uint8_t)s); continue; }
+            if (s < 256) { out.push_back((uint8_t)s); grew(); continue; }
             if (s == 256) return;
             if (s > 285) throw PngError("bad length code");
             const int len = lbase[s - 257] + take(lext[s - 257]);
@@ -108,6 +110,7 @@ struct Inflater {
             if (d > out.size()) throw PngError("bad distance");
             const size_t from = out.size() - d;
             for (int i = 0; i < len; ++i) out.push_back(out[from + (size_t)i]);
+            grew();
         }
     }
     void run()
@@ -127,6 +130,7 @@ struct Inflater {
                 at += 4;
                 if ((len ^ 0xffffu) != nlen || at + len > n) throw PngError("bad stored block");
                 out.insert(out.end(), in + at, in + at + len);
+                grew();
                 at += len;
             } else if (type == 1) {
                 uint8_t l[288];
@@ -286,6 +290,9 @@ TextureImage decode_png(const unsigned char* data, size_t size, const std::strin
         z.in = idat.data();
         z.n = idat.size();
         z.out.reserve(((size_t)w * img_n * depth / 8 + 2) * (size_t)h);
+        // upper bound of what any layout of this image inflates to (Adam7: at most 7 extra filter bytes per row of
+        // the 8-row pattern and 7 partial rows): more is a corrupt or hostile file
+        z.cap = (((size_t)w * img_n * depth + 7) / 8 + 8) * ((size_t)h + 8) + 64;
         z.run();
 
         // samples of the file: img_n per pixel, unpacked (grey scaled, palette indices not)

@@ -78,7 +78,8 @@ class _OptionsC(ctypes.Structure):
                 ("ssaa", ctypes.c_int32), ("dof", ctypes.c_int32), ("aperture", ctypes.c_float),
                 ("focal_len", ctypes.c_float), ("first_bounce_cache", ctypes.c_int32),
                 ("batch", ctypes.c_int32), ("geom_bvh", ctypes.c_int32),
-                ("mesh_brute_force", ctypes.c_int32), ("mesh_no_bbox", ctypes.c_int32)]
+                ("mesh_brute_force", ctypes.c_int32), ("mesh_no_bbox", ctypes.c_int32),
+                ("use_thrust_partition", ctypes.c_int32)]
 
 
 class _StatsC(ctypes.Structure):
@@ -101,7 +102,7 @@ class GuiDataContainer:
         self.useBVHtree = True
         self.useBBox = True
         self.sortbyMaterial = False
-        self.useThrustPartition = False     # both partitions give the same stable result here
+        self.useThrustPartition = False     # pathtrace.cu:499-503: same stable partition, same image (b200_pt.h)
         self.SSAA = True
         self.DoF = True
         self.aperture = 0.1
@@ -227,7 +228,8 @@ class Renderer:
     def set_options(self, gui):
         o = _OptionsC(int(gui.russianRoulette), int(gui.sortbyMaterial), int(gui.SSAA), int(gui.DoF),
                       float(gui.aperture), float(gui.focal_len), int(gui.firstBounceCache), int(gui.batch),
-                      int(getattr(gui, "geomBVH", 0)), int(not gui.useBVHtree), int(not gui.useBBox))
+                      int(getattr(gui, "geomBVH", 0)), int(not gui.useBVHtree), int(not gui.useBBox),
+                      int(getattr(gui, "useThrustPartition", False)))
         check(_lib().b200pt_set_options(self._h, ctypes.byref(o)))
 
     def reset(self):

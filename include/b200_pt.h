@@ -156,6 +156,12 @@ typedef struct b200pt_options {
                                    that sets the field gets the reference's result for it, bit for bit. */
     int32_t mesh_no_bbox;       /* !GuiDataContainer::useBBox (utilities.h:25; default 0): with mesh_brute_force,
                                    skip the slab test against Geom::min_bound / max_bound */
+    int32_t use_thrust_partition; /* GuiDataContainer::useThrustPartition (utilities.h:27; default 0).  The reference
+                                   removes terminated paths either with its own mark / scan / scatter
+                                   (pathtrace.cu:377-407) or with thrust::stable_partition (:416-420,499-503); both are
+                                   a STABLE live-first partition with the same result.  This library has one
+                                   implementation of exactly that (single-pass look-back); the flag is accepted
+                                   and recorded so that a host which sets it gets the reference's image for it. */
 } b200pt_options;
 
 typedef struct b200pt b200pt;

@@ -32,6 +32,7 @@ static_assert(sizeof(Geom) == sizeof(b200pt_geom) && sizeof(Material) == sizeof(
 static Scene* hst_scene = NULL;
 static GuiDataContainer* guiData = NULL;
 static b200pt* renderer = NULL;
+static void* pinned_image = NULL;
 
 static void check(int code, const char* what)
 {
@@ -63,10 +64,18 @@ void pathtraceInit(Scene* scene)
     e.n_textures = (int)tex.size();
     e.textures = tex.data();
     check(b200pt_create_ext(&s, &e, &renderer), "pathtraceInit");
+    // The interface copies the SUM image back on EVERY call (pathtrace.cu:524): page-lock the caller's vector once so
+    // that copy runs at PCIe speed (a pageable 7.68 MB copy per iteration would dominate the call).  Best effort.
+    pinned_image = scene->state.image.data();
+    if (cudaHostRegister(pinned_image, scene->state.image.size() * sizeof(glm::vec3), cudaHostRegisterDefault) != cudaSuccess) {
+        cudaGetLastError();
+        pinned_image = NULL;
+    }
 }
 
 void pathtraceFree()
 {
+    if (pinned_image) { cudaHostUnregister(pinned_image); pinned_image = NULL; }
     b200pt_destroy(renderer);            // no-op on NULL, like cudaFree(NULL) in the reference
     renderer = NULL;
 }
@@ -84,6 +93,7 @@ void pathtrace(uchar4* pbo, int /*frame*/, int iter)
         o.focal_len = guiData->focal_len;
         o.mesh_brute_force = !guiData->useBVHtree;   // pathtrace.cu:49-50
         o.mesh_no_bbox = !guiData->useBBox;
+        o.use_thrust_partition = guiData->useThrustPartition;   // pathtrace.cu:499-503: same stable partition, same image
     }
     o.batch = 1;                          // one iteration per call, the reference's accumulation order
     check(b200pt_set_options(renderer, &o), "options");

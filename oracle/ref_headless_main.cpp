@@ -29,25 +29,53 @@
 #include "scene.h"
 #include "pathtrace.h"
 #include "utilities.h"
+#include "image.h"
 
 // The reference declares but never defines the destructor (scene.h:24).
 Scene::~Scene() {}
 
+// saveImage() of the reference (path_tracer/src/main.cpp:88-112), its loop restated on the reference's OWN Image
+// class (image.cpp:22-44 is compiled in unmodified): mean = sum / samples, x mirrored, clamp * 255 truncated, PNG
+// through stb_image_write.  `base` replaces the time-stamped name.  Used to pin host/image_io.cpp to the reference.
+static void ref_save_image(const glm::vec3* sum, int width, int height, float samples, const std::string& base, bool hdr)
+{
+    Image img(width, height);
+    for (int x = 0; x < width; x++)
+        for (int y = 0; y < height; y++) {
+            int index = x + (y * width);
+            glm::vec3 pix = sum[index];
+            img.setPixel(width - 1 - x, y, glm::vec3(pix) / samples);
+        }
+    img.savePNG(base);
+    if (hdr) img.saveHDR(base);
+}
+
 static void usage(const char* a0)
 {
     fprintf(stderr,
-        "usage: %s SCENE.json [--iters N] [--out sum.bin] [--pbo pbo.bin] [--sort] [--thrust-partition]\n"
+        "usage: %s SCENE.json [--iters N] [--out sum.bin] [--pbo pbo.bin] [--save-png BASE] [--sort] [--thrust-partition]\n"
+        "       %s --convert SUM.bin W H SAMPLES BASE [--hdr]   (the reference's saveImage on a stored SUM image)\n"
         "       [--no-rr] [--no-ssaa] [--no-dof] [--aperture A] [--focal F]\n"
         "       [--refract MATERIAL_ID IOR]...  (patches Material after load: the reference\n"
-        "        loader has no key for hasRefractive/indexOfRefraction)\n", a0);
+        "        loader has no key for hasRefractive/indexOfRefraction)\n", a0, a0);
 }
 
 int main(int argc, char** argv)
 {
     if (argc < 2) { usage(argv[0]); return 1; }
+    if (std::string(argv[1]) == "--convert") {      // SUM.bin W H SAMPLES BASE [--hdr]: saveImage only, no GPU involved
+        if (argc < 7) { usage(argv[0]); return 1; }
+        const int w = atoi(argv[3]), h = atoi(argv[4]);
+        std::vector<glm::vec3> sum((size_t)w * h);
+        FILE* f = fopen(argv[2], "rb");
+        if (!f || fread(sum.data(), sizeof(glm::vec3), sum.size(), f) != sum.size()) { fprintf(stderr, "cannot read %s\n", argv[2]); return 1; }
+        fclose(f);
+        ref_save_image(sum.data(), w, h, (float)atof(argv[5]), argv[6], argc > 7 && std::string(argv[7]) == "--hdr");
+        return 0;
+    }
     const char* sceneFile = argv[1];
     int iters = -1;
-    std::string out, pbo_out;
+    std::string out, pbo_out, save_png;
     GuiDataContainer* gui = new GuiDataContainer();
     std::vector<std::pair<int, float>> refract;
     for (int i = 2; i < argc; ++i) {
@@ -55,6 +83,7 @@ int main(int argc, char** argv)
         if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
         else if (a == "--out" && i + 1 < argc) out = argv[++i];
         else if (a == "--pbo" && i + 1 < argc) pbo_out = argv[++i];
+        else if (a == "--save-png" && i + 1 < argc) save_png = argv[++i];
         else if (a == "--sort") gui->sortbyMaterial = true;
         else if (a == "--thrust-partition") gui->useThrustPartition = true;
         else if (a == "--no-rr") gui->russianRoulette = false;
@@ -134,6 +163,7 @@ int main(int argc, char** argv)
         fwrite(rs->image.data(), sizeof(glm::vec3), (size_t)width * height, f);
         fclose(f);
     }
+    if (!save_png.empty()) ref_save_image(rs->image.data(), width, height, (float)iters, save_png, false);
     if (!pbo_out.empty()) {
         std::vector<uchar4> h((size_t)width * height);
         cudaMemcpy(h.data(), pbo, h.size() * sizeof(uchar4), cudaMemcpyDeviceToHost);

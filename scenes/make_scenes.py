@@ -12,6 +12,7 @@ cornell_glass_1080p.json   config 4: 1920x1080, depth 12, mirror + glass + diffu
                     The glass material is marked by the extension keys REFRACTIVE / IOR which the
                     reference loader ignores: the reference baseline patches material id
                     `glass` after load (oracle/ref_headless_main.cpp --refract).
+synthetic_4096_small.json the same scene at 480x270 (parity fixture of config 5).
 synthetic_4096.json config 5: 4096 random spheres/cubes, 64 materials, 3840x2160, depth 8.
 mesh_room*.json     triangle meshes + textures in the layout of the reference's scenes/room.json
                     (cube walls, "mesh" objects with OBJ_FILE under Models/, materials with
@@ -346,6 +347,9 @@ def main():
     write("cornell_glass_small.json", cornell_glass((192, 108), 64, 12, "cornell_glass_small"))
     write("synthetic_4096.json", synthetic(4096, (3840, 2160), 256, 8, "synthetic_4096"))
     write("synthetic_600_small.json", synthetic(600, (128, 72), 16, 8, "synthetic_600_small"))
+    # config 5's 4096 primitives (same seed, same scene) at a resolution the reference build and the CPU oracle finish
+    # in seconds: the parity case of that configuration (tests/pt_cases.py)
+    write("synthetic_4096_small.json", synthetic(4096, (480, 270), 16, 8, "synthetic_4096_small"))
     mesh_assets()
     write("mesh_room.json", mesh_room((1200, 1200), 2000, 8, "mesh_room"))
     write("mesh_room_small.json", mesh_room((160, 160), 32, 8, "mesh_room_small"))

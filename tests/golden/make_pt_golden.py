@@ -34,6 +34,7 @@ SCENES = {
     "jpeg_textures": [],
     "png_textures": [],     # PNG decoding parity with stb_image (scenes/make_png_fixtures.py)    # JPEG decoding parity with stb_image (scenes/make_jpeg_fixtures.py)
     "synthetic_4096": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
+    "synthetic_4096_small": sum((["--refract", str(i), "1.5"] for i in range(24, 32)), []),
 }
 # (scene, iterations, extra renderer flags, tag)
 RENDERS = [
@@ -53,6 +54,12 @@ RENDERS = [
     # (untextured: that mode's texture coordinates leave [0, 1] and the reference then reads outside the image)
     ("mesh_room_small_notex", 8, ["--no-bvh"], "nobvh"),
     ("mesh_room_small_notex", 8, ["--no-bvh", "--no-bbox", "--sort", "--no-ssaa", "--no-dof"], "nobvhsort"),
+    # BASELINE config 5's scene (4096 primitives, 64 materials) at 480x270, plain and sorted
+    ("synthetic_4096_small", 2, [], "default"),
+    ("synthetic_4096_small", 2, ["--sort"], "sort"),
+    # useThrustPartition = true (pathtrace.cu:416-420,499-503): thrust::stable_partition instead of mark / scan / keep
+    ("cornell_small", 16, ["--thrust-partition"], "thrustpart"),
+    ("cornell_glass_small", 16, ["--thrust-partition", "--sort"], "thrustpartsort"),
 ]
 
 

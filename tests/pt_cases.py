@@ -17,6 +17,8 @@ RENDERS = [
     ("synthetic_600_small", 4, [], "default"),
     ("mesh_room_small", 8, [], "default"),                # triangle meshes, BVH, textures
     ("mesh_room_small_notex", 8, ["--no-bvh"], "nobvh"),  # useBVHtree = false: meshIntersectionTest
+    ("synthetic_4096_small", 2, [], "default"),           # BASELINE config 5's scene at 480x270 (k_isect_dyn, 1383-node tree)
+    ("cornell_small", 16, ["--thrust-partition"], "thrustpart"),   # useThrustPartition
 ]
 # material sort on (thrust::sort_by_key in the reference, pathtrace.cu:479-491): the paths differ
 # from the unsorted ones because the shading seed is the slot index AFTER sorting
@@ -26,6 +28,8 @@ SORT_RENDERS = [
     ("cornell_small", 16, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
     ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain"),
     ("mesh_room_small_notex", 8, ["--no-bvh", "--no-bbox", "--sort", "--no-ssaa", "--no-dof"], "nobvhsort"),
+    ("synthetic_4096_small", 2, ["--sort"], "sort"),      # config 5's 64 materials through the material bucketing
+    ("cornell_glass_small", 16, ["--thrust-partition", "--sort"], "thrustpartsort"),
 ]
 # per-stage vectors from the reference's own kernels (tests/golden/make_pt_stage_golden.py)
 STAGES = [("cornell_tiny", "default", []), ("cornell_tiny", "plain", ["--no-ssaa", "--no-dof", "--no-rr"]),
@@ -45,6 +49,7 @@ def gui_from_flags(flags, batch=0):
     g.sortbyMaterial = "--sort" in flags
     g.useBVHtree = "--no-bvh" not in flags
     g.useBBox = "--no-bbox" not in flags
+    g.useThrustPartition = "--thrust-partition" in flags
     g.batch = batch
     return g
 

@@ -27,7 +27,10 @@ def need(name):
                                          ("mesh_room_small", []), ("mesh_room_small", ["--sort"]),
                                          # guiData->useBVHtree = false (and useBBox = false) through the binding
                                          ("mesh_room_small_notex", ["--no-bvh"]),
-                                         ("mesh_room_small_notex", ["--no-bvh", "--no-bbox", "--sort"])])
+                                         ("mesh_room_small_notex", ["--no-bvh", "--no-bbox", "--sort"]),
+                                         # guiData->useThrustPartition = true (pathtrace.cu:499-503) on both sides
+                                         ("cornell_small", ["--thrust-partition"]),
+                                         ("cornell_glass_small", ["--refract", "4", "1.5", "--thrust-partition", "--sort"])])
 def test_pathtrace_h_dropin_is_bit_identical(tmp_path, scene, flags):
     ref, mine = need("ref_pathtracer"), need("dropin_pathtracer")
     scene_json = os.path.join(REPO, "scenes", scene + ".json")

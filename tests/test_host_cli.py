@@ -21,7 +21,7 @@ from pt_cases import GOLD, bits_equal, ref_sum
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
 SCENES = ["cornell", "cornell_mirror", "cornell_small", "cornell_small_mirror", "cornell_tiny",
-          "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096",
+          "cornell_glass_small", "cornell_glass_1080p", "synthetic_600_small", "synthetic_4096", "synthetic_4096_small",
           "mesh_room", "mesh_room_small", "mesh_room_small_notex", "mesh_stress",   # OBJ meshes + BVH + textures ("B2PTSCN2")
           "jpeg_textures",   # + six progressive ones
           "png_textures"]    # 25 PNGs (scenes/make_png_fixtures.py) decoded by host/png.cpp vs stb_image   # twelve baseline JPEGs (scenes/make_jpeg_fixtures.py) decoded by host/jpeg.cpp vs stb_image
@@ -197,10 +197,66 @@ def test_png_writer_pixels(tmp_path):
     assert hdr.startswith(b"#?RADIANCE\n") and hdr.endswith(hdr[-4 * w * h:]) and len(hdr) > 4 * w * h
 
 
+def decode_hdr(path):
+    """Radiance RGBE, flat or new-style run-length scanlines -> (h, w, 4) bytes (r, g, b, e)"""
+    raw = open(path, "rb").read()
+    assert raw.startswith(b"#?RADIANCE\n")
+    head_end = raw.index(b"\n\n") + 2
+    assert b"FORMAT=32-bit_rle_rgbe" in raw[:head_end]
+    line_end = raw.index(b"\n", head_end)
+    dims = raw[head_end:line_end].split()
+    assert dims[0] == b"-Y" and dims[2] == b"+X"
+    h, w = int(dims[1]), int(dims[3])
+    at, out = line_end + 1, np.zeros((h, w, 4), dtype=np.uint8)
+    for y in range(h):
+        if 8 <= w < 32768 and raw[at] == 2 and raw[at + 1] == 2 and (raw[at + 2] << 8 | raw[at + 3]) == w:
+            at += 4
+            for c in range(4):
+                x = 0
+                while x < w:
+                    n = raw[at]; at += 1
+                    if n > 128:
+                        out[y, x:x + n - 128, c] = raw[at]; at += 1; x += n - 128
+                    else:
+                        out[y, x:x + n, c] = np.frombuffer(raw, dtype=np.uint8, count=n, offset=at); at += n; x += n
+        else:
+            out[y] = np.frombuffer(raw, dtype=np.uint8, count=4 * w, offset=at).reshape(w, 4); at += 4 * w
+    assert at == len(raw)
+    return out
+
+
+def test_image_writer_against_the_reference_saveimage(tmp_path):
+    """N2 pinned to the reference itself: tests/golden/ref_saveimage.{png,hdr} were written by the reference's OWN
+    saveImage loop + Image::savePNG / saveHDR (main.cpp:88-112, image.cpp:22-49, stb_image_write) from the seeded SUM
+    image of tests/golden/make_image_golden.py; this repo's writer must decode to the same pixels (the files' own
+    bytes differ: other deflate / filter / run-length choices, same content).  When the reference build is present
+    (oracle/_ref) it is also run live."""
+    import sys
+    from PIL import Image
+    sys.path.insert(0, GOLD)
+    import make_image_golden as g
+    src, base = str(tmp_path / "sum.bin"), str(tmp_path / "mine")
+    g.sum_image().tofile(src)
+    subprocess.run([EXE, "--convert", src, str(g.W), str(g.H), str(g.SAMPLES), base, "--hdr"], check=True,
+                   stdout=subprocess.DEVNULL)
+    mine_png = decode_png(base + ".png")
+    assert np.array_equal(mine_png, np.array(Image.open(os.path.join(GOLD, "ref_saveimage.png"))))
+    assert np.array_equal(decode_hdr(base + ".hdr"), decode_hdr(os.path.join(GOLD, "ref_saveimage.hdr")))
+    ref_exe = os.path.join(REPO, "oracle", "_ref", "ref_pathtracer")
+    if os.path.exists(ref_exe):
+        live = str(tmp_path / "ref")
+        subprocess.run([ref_exe, "--convert", src, str(g.W), str(g.H), str(g.SAMPLES), live, "--hdr"], check=True,
+                       stdout=subprocess.DEVNULL)
+        assert np.array_equal(mine_png, np.array(Image.open(live + ".png")))
+        assert np.array_equal(decode_hdr(base + ".hdr"), decode_hdr(live + ".hdr"))
+
+
 # ---- on a B200 ---------------------------------------------------------------------------------------
 @pytest.mark.gpu
 @pytest.mark.parametrize("scene,iters,flags,tag", [("cornell_small", 16, [], "default"),
                                                     ("cornell_glass_small", 16, ["--sort"], "sort"),
+                                                    # useThrustPartition (SURVEY 8a A13): golden from the reference build run with it
+                                                    ("cornell_small", 16, ["--thrust-partition"], "thrustpart"),
                                                     # OBJ + BVH + textures through the C++ loader
                                                     ("mesh_room_small", 8, [], "default"),
                                                     ("mesh_room_small", 8, ["--sort", "--no-ssaa", "--no-dof"], "sortplain")])

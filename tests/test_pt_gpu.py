@@ -366,6 +366,32 @@ def test_full_size_cornell_properties(pt, oracle):
     r.close()
 
 
+# ---- full size: BASELINE config 4 (glass / mirror / diffuse 1920x1080, depth 12, material sort + first-bounce cache) ----
+def test_full_size_config4_sort_and_cache_vs_oracle(pt, oracle):
+    """cornell_glass_1080p as BASELINE.json states it: sort by material ON, first-bounce cache ON (hence SSAA and DoF
+    off), full resolution.  Two iterations with batch = 1: the first fills the cache, the second uses it.  Bit for bit
+    against the CPU oracle (which is pinned to the reference build's sorted renders on the small glass scene)."""
+    sc = load_scene("cornell_glass_1080p")
+    assert (sc.width, sc.height, sc.traceDepth) == (1920, 1080, 12)
+    gui = gui_from_flags(["--sort", "--no-ssaa", "--no-dof"], batch=1)
+    gui.firstBounceCache = True
+    r = pt.Renderer(sc)
+    r.set_options(gui)
+    r.render(1, 2)
+    img, seg = r.read_sum(), r.stats()["path_segments"]
+    want, segments = oracle.render(sc, gui, 1, 2)
+    assert seg == segments
+    assert bits_equal(img, want)
+    # the default batch: same paths, float addition order only
+    r.reset()
+    gui.batch = 0
+    r.set_options(gui)
+    r.render(1, 2)
+    assert r.stats()["path_segments"] == segments
+    assert np.allclose(r.read_sum(), want, rtol=2e-6, atol=1e-6)
+    r.close()
+
+
 def test_live_reference_cuda_build_if_present(pt):
     """When the reference's own CUDA build travelled with the snapshot (oracle/_ref/ref_pathtracer,
     built in the build container), run it on a case that has no committed golden."""
