@@ -16,7 +16,7 @@ all: lib host oracle
 PT_SRCS := $(CSRC)/pt_kernels.cu $(CSRC)/pt_api.cu $(CSRC)/pt_gbvh.cu
 PT_HDRS := $(CSRC)/pt_kernels.cuh $(CSRC)/pt_math.cuh $(CSRC)/pt_shade.cuh $(CSRC)/lookback.cuh include/b200_pt.h
 
-lib: $(PKG)/libb200sc.so $(PKG)/libb200pt.so
+lib: $(PKG)/libb200sc.so $(PKG)/libb200pt.so $(PKG)/libb200mg.so
 
 $(PKG)/libb200sc.so: $(SC_SRCS) $(SC_HDRS)
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(SC_SRCS)
@@ -26,6 +26,10 @@ $(PKG)/libb200sc.so: $(SC_SRCS) $(SC_HDRS)
 $(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS) $(PKG)/libb200sc.so include/b200_sc.h
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(PT_SRCS) -L$(PKG) -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN'
 
+
+# multi-GPU layer (one process, one host thread per device, NCCL): plumbing over the two libraries above
+$(PKG)/libb200mg.so: $(CSRC)/mg_api.cu include/b200_mg.h include/b200_pt.h include/b200_sc.h $(PKG)/libb200pt.so $(PKG)/libb200sc.so
+	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(CSRC)/mg_api.cu -L$(PKG) -lb200pt -lb200sc -lnccl -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 # ---- host side above the C ABI (C++): scene loader, image writer, headless CLI, scan harness ----
 HOST     := $(PKG)/host

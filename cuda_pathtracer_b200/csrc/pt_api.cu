@@ -168,6 +168,7 @@ int ensure_batch(b200pt* h, int batch)
     if (r) return r;
     CK(cudaMemset(h->d_counts, 0, sizeof(int) * (size_t)(h->depth + 1) * batch));
     CK(cudaMemset(h->d_desc, 0, sizeof(unsigned long long) * (size_t)batch * h->ptiles * PT_DESC_STRIDE));
+    CK(cudaDeviceSynchronize());       // the memsets ran on the null stream: a non-blocking caller stream is not ordered behind them
     h->epoch = 0;
     h->batch_cap = batch;
     return 0;
@@ -545,6 +546,7 @@ int b200pt_reset(b200pt* h)
     ON_DEVICE(h);
     CK(cudaMemset(h->d_image, 0, sizeof(float) * 3 * (size_t)h->P));
     CK(cudaMemset(h->d_segments, 0, sizeof(unsigned long long)));
+    CK(cudaDeviceSynchronize());       // (null-stream memsets: make them visible to launches on non-blocking streams)
     h->iterations = 0;
     h->launches = 0;
     h->prof_used = 0;
@@ -749,6 +751,15 @@ int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream
     return 0;
 }
 
+int b200pt_tonemap_buffer_u8(b200pt* h, const void* dev_sum_rgb, int iter_divisor, void* dev_rgba8, void* stream)
+{
+    if (!h || !dev_sum_rgb || !dev_rgba8 || iter_divisor <= 0) return B200_E_BADARG;
+    ON_DEVICE(h);
+    CK(launch_tonemap((const float*)dev_sum_rgb, h->P, iter_divisor, (uchar4*)dev_rgba8, (cudaStream_t)stream));
+    h->launches += 1;
+    return 0;
+}
+
 int b200pt_read_sum(b200pt* h, float* host_rgb)
 {
     if (!h || !host_rgb) return B200_E_BADARG;
@@ -764,6 +775,7 @@ int b200pt_write_sum(b200pt* h, const float* host_rgb)
     ON_DEVICE(h);
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(h->d_image, host_rgb, sizeof(float) * 3 * (size_t)h->P, cudaMemcpyHostToDevice));
+    CK(cudaDeviceSynchronize());
     return 0;
 }
 

@@ -48,7 +48,11 @@ int ensure(void** p, size_t* cap, size_t want_elems, size_t elem_bytes, bool zer
     size_t bytes = want_elems * elem_bytes;
     cudaError_t e = cudaMalloc(p, bytes);
     if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? B200_E_NOMEM : (int)e; }
-    if (zero) { e = cudaMemset(*p, 0, bytes); if (e != cudaSuccess) return (int)e; }
+    if (zero) {      // (null-stream memset: make it visible to launches on non-blocking caller streams)
+        e = cudaMemset(*p, 0, bytes);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) return (int)e;
+    }
     *cap = want_elems;
     return 0;
 }

@@ -202,6 +202,10 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
  * dev_rgba8 is a DEVICE buffer of W*H*4 bytes. */
 int b200pt_tonemap_u8(b200pt* h, int iter_divisor, void* dev_rgba8, void* stream);
 
+/* The same for ANY device float SUM image of this renderer's resolution (3*W*H floats) -- e.g. the all-reduced image
+ * of a multi-GPU render (include/b200_mg.h). */
+int b200pt_tonemap_buffer_u8(b200pt* h, const void* dev_sum_rgb, int iter_divisor, void* dev_rgba8, void* stream);
+
 /* Copy the float SUM image (3*W*H floats) to host memory; synchronises. */
 int b200pt_read_sum(b200pt* h, float* host_rgb);
 /* Replace the float SUM image by 3*W*H floats from host memory (restartable rendering: resume from a

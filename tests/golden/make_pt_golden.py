@@ -7,7 +7,7 @@ utilities.cpp compiled unmodified) for the scenes under scenes/:
 Step 2 (on a B200, under gpurun): float SUM images rendered by the reference's own CUDA build
 (oracle/_ref/ref_pathtracer, unmodified pathtrace.cu / intersections.cu / interactions.cu) on
 the small scenes, written to gpurun_out/ and then copied into tests/golden/ by
-    python tests/golden/make_pt_golden.py renders [--collect]
+    python tests/golden/make_pt_golden.py renders [--only-missing] [--collect]
 """
 import os
 import subprocess
@@ -70,13 +70,16 @@ def scenes():
         print("wrote", name + ".scene.bin")
 
 
-def renders(collect):
+def renders(collect, only_missing=False):
     out = os.path.join(REPO, "gpurun_out")
     os.makedirs(out, exist_ok=True)
     for scene, iters, flags, tag in RENDERS:
         name = f"{scene}.{tag}.{iters}it.refsum.bin"
+        if only_missing and os.path.exists(os.path.join(HERE, name)):
+            continue
         if collect:
-            os.replace(os.path.join(out, name), os.path.join(HERE, name))
+            if os.path.exists(os.path.join(out, name)):
+                os.replace(os.path.join(out, name), os.path.join(HERE, name))
             continue
         subprocess.run([os.path.join(REF, "ref_pathtracer"), os.path.join(REPO, "scenes", scene + ".json"),
                         "--iters", str(iters), "--out", os.path.join(out, name)] + flags + SCENES[scene], check=True)
@@ -86,4 +89,4 @@ if __name__ == "__main__":
     if sys.argv[1] == "scenes":
         scenes()
     else:
-        renders("--collect" in sys.argv)
+        renders("--collect" in sys.argv, "--only-missing" in sys.argv)
