@@ -29,13 +29,13 @@ $(PKG)/libb200pt.so: $(PT_SRCS) $(PT_HDRS) $(PKG)/libb200sc.so include/b200_sc.h
 
 # multi-GPU layer (one process, one host thread per device, NCCL): plumbing over the two libraries above
 $(PKG)/libb200mg.so: $(CSRC)/mg_api.cu include/b200_mg.h include/b200_pt.h include/b200_sc.h $(PKG)/libb200pt.so $(PKG)/libb200sc.so
-	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(CSRC)/mg_api.cu -L$(PKG) -lb200pt -lb200sc -lnccl -Xlinker -rpath -Xlinker '$$ORIGIN'
+	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(CSRC)/mg_api.cu -L$(PKG) -lb200pt -lb200sc -ldl -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 # ---- host side above the C ABI (C++): scene loader, image writer, headless CLI, scan harness ----
 HOST     := $(PKG)/host
 BIN      := $(PKG)/bin
 CXXFLAGS := -std=c++17 -O2 -ffp-contract=off -Wall -Iinclude -I/usr/local/cuda/include
-HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/mesh.hpp $(HOST)/image_io.hpp include/b200_pt.h
+HOST_HDRS := $(HOST)/json_min.hpp $(HOST)/linalg.hpp $(HOST)/scene.hpp $(HOST)/mesh.hpp $(HOST)/image_io.hpp include/b200_pt.h include/b200_mg.h
 
 host: $(BIN)/cuda_path_tracer $(BIN)/stream_compaction_test
 
@@ -43,12 +43,12 @@ $(BIN)/%.o: $(HOST)/%.cpp $(HOST_HDRS)
 	@mkdir -p $(BIN)
 	g++ $(CXXFLAGS) -c -o $@ $<
 
-$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/mesh.o $(BIN)/jpeg.o $(BIN)/png.o $(BIN)/image_io.o $(PKG)/libb200pt.so
-	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200pt -lb200sc -Xlinker -rpath -Xlinker '$$ORIGIN/..'
+$(BIN)/cuda_path_tracer: $(BIN)/main.o $(BIN)/scene.o $(BIN)/mesh.o $(BIN)/jpeg.o $(BIN)/png.o $(BIN)/image_io.o $(PKG)/libb200pt.so $(PKG)/libb200mg.so
+	$(NVCC) $(ARCH) -cudart static -o $@ $(filter %.o,$^) -L$(PKG) -lb200mg -lb200pt -lb200sc -ldl -Xlinker -rpath -Xlinker '$$ORIGIN/..'
 
-$(BIN)/stream_compaction_test: $(HOST)/sc_harness.cpp include/b200_stream_compaction.hpp include/b200_sc.h $(PKG)/libb200sc.so
+$(BIN)/stream_compaction_test: $(HOST)/sc_harness.cpp include/b200_stream_compaction.hpp include/b200_sc.h include/b200_mg.h $(PKG)/libb200sc.so $(PKG)/libb200mg.so
 	@mkdir -p $(BIN)
-	g++ $(CXXFLAGS) -o $@ $< -L$(PKG) -lb200sc -Wl,-rpath,'$$ORIGIN/..'
+	g++ $(CXXFLAGS) -o $@ $< -L$(PKG) -lb200mg -lb200pt -lb200sc -ldl -Wl,-rpath,'$$ORIGIN/..'
 
 oracle:
 	$(MAKE) -C oracle all

@@ -15,7 +15,8 @@
 #include <vector>
 
 #include <cuda_runtime.h>
-#include <nccl.h>
+#include <dlfcn.h>
+#include <nccl.h>            // types and prototypes only: the library is bound at run time, see NcclApi below
 
 #include "../../include/b200_mg.h"
 #include "../../include/b200_sc.h"
@@ -42,6 +43,42 @@ struct b200mg_pt {
 };
 
 namespace {
+
+// NCCL is bound with dlopen when the first multi-device group is created, not at link time: a process that already
+// carries an NCCL (a Python process that imported torch brings its own libnccl.so.2) keeps using THAT one -- dlopen finds
+// the loaded library by its SONAME -- and a process that never asks for more than one device never loads NCCL at all.
+// (A link-time dependency made `import torch` fail when this library happened to be loaded first: the system's older
+// libnccl.so.2 then shadowed the one torch is built against.)
+struct NcclApi {
+    decltype(&ncclCommInitAll) CommInitAll = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    bool ok = false;
+};
+
+NcclApi& nccl()
+{
+    static NcclApi api = [] {
+        NcclApi a;
+        void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+        if (!lib) return a;
+        a.CommInitAll = (decltype(a.CommInitAll))dlsym(lib, "ncclCommInitAll");
+        a.CommDestroy = (decltype(a.CommDestroy))dlsym(lib, "ncclCommDestroy");
+        a.GroupStart = (decltype(a.GroupStart))dlsym(lib, "ncclGroupStart");
+        a.GroupEnd = (decltype(a.GroupEnd))dlsym(lib, "ncclGroupEnd");
+        a.AllReduce = (decltype(a.AllReduce))dlsym(lib, "ncclAllReduce");
+        a.AllGather = (decltype(a.AllGather))dlsym(lib, "ncclAllGather");
+        a.GetErrorString = (decltype(a.GetErrorString))dlsym(lib, "ncclGetErrorString");
+        a.ok = a.CommInitAll && a.CommDestroy && a.GroupStart && a.GroupEnd && a.AllReduce && a.AllGather && a.GetErrorString;
+        return a;
+    }();
+    return api;
+}
 
 struct OnDevice {
     int prev = -1;
@@ -100,14 +137,14 @@ int ensure_staging(b200mg* G, int g, size_t ints)
 // ONE all-gather of one int per device: small[0] of every device -> small[4 .. 4+K) of every device
 int gather_ints(b200mg* G)
 {
-    ncclResult_t r = ncclGroupStart();
+    ncclResult_t r = nccl().GroupStart();
     for (int g = 0; g < G->K && r == ncclSuccess; ++g) {
         OnDevice on(G->dev[g]);
         cudaEventRecord(G->ev[4 * g + 2], G->stream[g]);
-        r = ncclAllGather(G->d_small[g], G->d_small[g] + 4, 1, ncclInt32, G->comm[g], G->stream[g]);
+        r = nccl().AllGather(G->d_small[g], G->d_small[g] + 4, 1, ncclInt32, G->comm[g], G->stream[g]);
         cudaEventRecord(G->ev[4 * g + 3], G->stream[g]);
     }
-    const ncclResult_t r2 = ncclGroupEnd();
+    const ncclResult_t r2 = nccl().GroupEnd();
     return nccl_code(r != ncclSuccess ? r : r2);
 }
 
@@ -157,7 +194,7 @@ int b200mg_create(int n_devices, const int* devices, b200mg** out)
     }
     if (!rc && G->K > 1) {
         G->comm.assign(K, nullptr);
-        rc = nccl_code(ncclCommInitAll(G->comm.data(), G->K, G->dev.data()));
+        rc = nccl().ok ? nccl_code(nccl().CommInitAll(G->comm.data(), G->K, G->dev.data())) : B200_E_NCCL + 99;
         if (rc) G->comm.clear();
     }
     if (rc) { b200mg_destroy(G); return rc; }
@@ -168,7 +205,7 @@ int b200mg_create(int n_devices, const int* devices, b200mg** out)
 int b200mg_destroy(b200mg* G)
 {
     if (!G) return 0;
-    for (ncclComm_t c : G->comm) if (c) ncclCommDestroy(c);
+    for (ncclComm_t c : G->comm) if (c) nccl().CommDestroy(c);
     for (int g = 0; g < G->K; ++g) {
         OnDevice on(G->dev[g]);
         if ((size_t)g < G->sc.size()) b200_sc_ctx_destroy(G->sc[g]);
@@ -273,17 +310,17 @@ int b200mg_pt_reduce_read_sum(b200mg_pt* R, float* host_rgb, float* allreduce_ms
         R->reduced = true;
         return b200pt_read_sum(R->h[0], host_rgb);
     }
-    ncclResult_t r = ncclGroupStart();
+    ncclResult_t r = nccl().GroupStart();
     for (int g = 0; g < G->K && r == ncclSuccess; ++g) {
         OnDevice on(G->dev[g]);
         void* img = nullptr;
         const int rc = b200pt_sum_device_ptr(R->h[g], &img, nullptr);
-        if (rc) { ncclGroupEnd(); return rc; }
+        if (rc) { nccl().GroupEnd(); return rc; }
         cudaEventRecord(G->ev[4 * g + 2], G->stream[g]);
-        r = ncclAllReduce(img, R->d_red[g], n, ncclFloat, ncclSum, G->comm[g], G->stream[g]);
+        r = nccl().AllReduce(img, R->d_red[g], n, ncclFloat, ncclSum, G->comm[g], G->stream[g]);
         cudaEventRecord(G->ev[4 * g + 3], G->stream[g]);
     }
-    const ncclResult_t r2 = ncclGroupEnd();
+    const ncclResult_t r2 = nccl().GroupEnd();
     if (r != ncclSuccess || r2 != ncclSuccess) return nccl_code(r != ncclSuccess ? r : r2);
     {
         OnDevice on(G->dev[0]);
@@ -429,7 +466,9 @@ int b200mg_compact_i32(b200mg* G, int n, int* odata, const int* idata, int* coun
 
 const char* b200mg_error_string(int code)
 {
-    if (code >= B200_E_NCCL && code < B200_E_NCCL + 100) return ncclGetErrorString((ncclResult_t)(code - B200_E_NCCL));
+    if (code == B200_E_NCCL + 99) return "b200mg: libnccl.so.2 could not be loaded (needed for more than one device)";
+    if (code >= B200_E_NCCL && code < B200_E_NCCL + 99)
+        return nccl().ok ? nccl().GetErrorString((ncclResult_t)(code - B200_E_NCCL)) : "b200mg: NCCL error";
     return b200pt_error_string(code);
 }
 

@@ -29,11 +29,19 @@
 //   --pbo-out FILE       raw uchar4 preview buffer (sendImageToPBO, pathtrace.cu:65-86)
 //   --dump-scene FILE    write the loaded scene as a "B2PTSCN1"/"B2PTSCN2" POD dump and exit (no GPU needed)
 //   --device D           CUDA device ordinal
+//   --gpus K             render on CUDA devices 0..K-1 of this box in ONE process (include/b200_mg.h): one host thread per
+//                        device, device g traces iterations g+1, g+1+K, ..., one ncclAllReduce of the float SUM image;
+//                        the image equals the one-GPU image up to fp32 re-association of the per-pixel sums
+//   --preview-every N    every N iterations: (all-reduce,) read the SUM image back and write
+//                        "<FILE>.<time>.<iterations so far>samp.png" -- the mid-run save of the reference's 'S' key
+//                        (main.cpp:176-182) for a headless run; rendering continues
+//   --json               one JSON line with the timing on stdout
 //   --resume-sum FILE --samples-done K   restartable rendering: start from a float SUM image that
 //                        already holds K samples (a --sum-out of an earlier run); iterations
 //                        continue at K+1 and the output is divided by K + N
 //   --convert SUM.bin W H SAMPLES BASE   (first argument) only run saveImage on a stored SUM image
 // Exit codes follow the reference: 1 on a usage error, -1 (255) when the scene cannot be read.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -44,6 +52,7 @@
 
 #include <cuda_runtime_api.h>
 
+#include "../../include/b200_mg.h"
 #include "../../include/b200_pt.h"
 #include "image_io.hpp"
 #include "scene.hpp"
@@ -69,6 +78,13 @@ void check(int code, const char* what)
     if (code == 0) return;
     std::fprintf(stderr, "b200pt (%s): %s\n", what, b200pt_error_string(code));
     std::exit(EXIT_FAILURE);              // the reference's own error convention (checkCUDAErrorFn)
+}
+
+void mg_check(int code, const char* what)
+{
+    if (code == 0) return;
+    std::fprintf(stderr, "b200mg (%s): %s\n", what, b200mg_error_string(code));
+    std::exit(EXIT_FAILURE);
 }
 
 }  // namespace
@@ -97,7 +113,8 @@ int main(int argc, char** argv)
 
     b200pt_options opt;
     b200pt_default_options(&opt);
-    int iters = -1, device = 0, iter_first = 1, iter_stride = 1;
+    int iters = -1, device = 0, iter_first = 1, iter_stride = 1, gpus = 1, preview_every = 0;
+    bool json_stats = false;
     bool want_png = true, want_hdr = false;
     int samples_done = 0;
     bool iter_first_given = false;
@@ -139,6 +156,9 @@ int main(int argc, char** argv)
         else if (a == "--pbo-out" || a == "--pbo") pbo_out = next();
         else if (a == "--dump-scene") dump_scene = next();
         else if (a == "--device") device = std::atoi(next());
+        else if (a == "--gpus") gpus = std::atoi(next());
+        else if (a == "--preview-every") preview_every = std::atoi(next());
+        else if (a == "--json") json_stats = true;
         else if (a == "--refract") {      // patch a material after load, as the test tooling does
             const int id = std::atoi(next());
             refract.emplace_back(id, (float)std::atof(next()));
@@ -169,16 +189,13 @@ int main(int argc, char** argv)
     const int width = state.camera.resolution[0], height = state.camera.resolution[1];
     const int n_iters = iters >= 0 ? iters : (int)state.iterations;
 
-    if (cudaSetDevice(device) != cudaSuccess) {
-        std::fprintf(stderr, "no usable CUDA device %d (this renderer has no CPU fallback)\n", device);
-        return EXIT_FAILURE;
-    }
-    b200pt* renderer = nullptr;
-    const b200pt_scene pod = scene->pod();
-    const b200pt_scene_ext ext = scene->pod_ext();
-    check(b200pt_create_ext(&pod, &ext, &renderer), "pathtraceInit");
-    check(b200pt_set_options(renderer, &opt), "options");
-
+    // ---- render: one GPU through libb200pt.so, or --gpus K through the multi-GPU layer (libb200mg.so: one host thread
+    // per device, iterations split with stride K, ONE ncclAllReduce of the float SUM image per read-back) ----
+    auto save_preview = [&](int samples_so_far) {       // what the reference's 'S' key does mid-run (main.cpp:176-182, saveImage)
+        const Image img = image_from_sum(state.image.data(), width, height, (float)samples_so_far);
+        img.savePNG(out_base.empty() ? output_basename(state.imageName, startTimeString, (float)samples_so_far)
+                                     : out_base + "." + std::to_string(samples_so_far) + "samp");
+    };
     if (!resume_sum.empty()) {
         FILE* f = std::fopen(resume_sum.c_str(), "rb");
         if (!f || std::fread(state.image.data(), sizeof(float), state.image.size(), f) != state.image.size()) {
@@ -186,31 +203,79 @@ int main(int argc, char** argv)
             return EXIT_FAILURE;
         }
         std::fclose(f);
-        check(b200pt_write_sum(renderer, state.image.data()), "resume");
         if (!iter_first_given) iter_first = samples_done + 1;
     }
-
-    const auto t0 = std::chrono::steady_clock::now();
-    check(b200pt_render(renderer, iter_first, n_iters, iter_stride, nullptr, 1), "pathtrace");
-    check(b200pt_read_sum(renderer, state.image.data()), "image copy");     // pathtrace.cu:524
-    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-
+    const b200pt_scene pod = scene->pod();
+    const b200pt_scene_ext ext = scene->pod_ext();
+    const int chunk = preview_every > 0 ? preview_every : (n_iters > 0 ? n_iters : 1);
     b200pt_stats st;
-    check(b200pt_get_stats(renderer, &st), "stats");
+    double secs = 0.0;
+    float allreduce_ms = 0.f;
+    std::vector<unsigned char> pbo;
+    if (gpus > 1) {
+        if (iter_stride != 1) { std::fprintf(stderr, "--iter-stride and --gpus exclude each other (--gpus splits the iterations itself)\n"); return 1; }
+        b200mg* group = nullptr;
+        b200mg_pt* renderer = nullptr;
+        mg_check(b200mg_create(gpus, nullptr, &group), "device group");
+        mg_check(b200mg_pt_create(group, &pod, &ext, &renderer), "pathtraceInit");
+        mg_check(b200mg_pt_set_options(renderer, &opt), "options");
+        if (!resume_sum.empty()) mg_check(b200mg_pt_write_sum(renderer, state.image.data()), "resume");
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int done = 0; done < n_iters || done == 0; done += chunk) {
+            const int n = std::min(chunk, n_iters - done);
+            mg_check(b200mg_pt_render(renderer, iter_first + done, n), "pathtrace");
+            mg_check(b200mg_pt_reduce_read_sum(renderer, state.image.data(), &allreduce_ms), "all-reduce + image copy");
+            if (preview_every > 0 && done + n < n_iters) save_preview(samples_done + done + n);
+            if (n_iters == 0) break;
+        }
+        secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        mg_check(b200mg_pt_get_stats(renderer, &st), "stats");
+        if (!pbo_out.empty()) {
+            pbo.resize((size_t)width * height * 4);
+            mg_check(b200mg_pt_preview_u8(renderer, iter_first + (n_iters > 0 ? n_iters - 1 : 0), pbo.data()), "sendImageToPBO");
+        }
+        b200mg_pt_destroy(renderer);                    // pathtraceFree
+        b200mg_destroy(group);
+    } else {
+        if (cudaSetDevice(device) != cudaSuccess) {
+            std::fprintf(stderr, "no usable CUDA device %d (this renderer has no CPU fallback)\n", device);
+            return EXIT_FAILURE;
+        }
+        b200pt* renderer = nullptr;
+        check(b200pt_create_ext(&pod, &ext, &renderer), "pathtraceInit");
+        check(b200pt_set_options(renderer, &opt), "options");
+        if (!resume_sum.empty()) check(b200pt_write_sum(renderer, state.image.data()), "resume");
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int done = 0; done < n_iters || done == 0; done += chunk) {
+            const int n = std::min(chunk, n_iters - done);
+            check(b200pt_render(renderer, iter_first + done * iter_stride, n, iter_stride, nullptr, 1), "pathtrace");
+            check(b200pt_read_sum(renderer, state.image.data()), "image copy");     // pathtrace.cu:524
+            if (preview_every > 0 && done + n < n_iters) save_preview(samples_done + done + n);
+            if (n_iters == 0) break;
+        }
+        secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        check(b200pt_get_stats(renderer, &st), "stats");
+        if (!pbo_out.empty()) {
+            const int last_iter = iter_first + (n_iters > 0 ? n_iters - 1 : 0) * iter_stride;
+            void* d_pbo = nullptr;
+            if (cudaMalloc(&d_pbo, (size_t)width * height * 4) != cudaSuccess) return EXIT_FAILURE;
+            check(b200pt_tonemap_u8(renderer, last_iter, d_pbo, nullptr), "sendImageToPBO");
+            pbo.resize((size_t)width * height * 4);
+            if (cudaMemcpy(pbo.data(), d_pbo, pbo.size(), cudaMemcpyDeviceToHost) != cudaSuccess) return EXIT_FAILURE;
+            cudaFree(d_pbo);
+        }
+        b200pt_destroy(renderer);                       // pathtraceFree
+    }
     std::printf("%d iterations of %dx%d, depth %d: %.3f s, %.1f spp/s, %.1f Mpath-segments/s (%llu segments, %llu launches)\n",
                 n_iters, width, height, state.traceDepth, secs, n_iters / secs, (double)st.path_segments / secs / 1e6,
                 (unsigned long long)st.path_segments, (unsigned long long)st.kernel_launches);
-
-    const int last_iter = iter_first + (n_iters > 0 ? n_iters - 1 : 0) * iter_stride;
-    if (!pbo_out.empty()) {
-        void* d_pbo = nullptr;
-        if (cudaMalloc(&d_pbo, (size_t)width * height * 4) != cudaSuccess) return EXIT_FAILURE;
-        check(b200pt_tonemap_u8(renderer, last_iter, d_pbo, nullptr), "sendImageToPBO");
-        std::vector<unsigned char> pbo((size_t)width * height * 4);
-        if (cudaMemcpy(pbo.data(), d_pbo, pbo.size(), cudaMemcpyDeviceToHost) != cudaSuccess) return EXIT_FAILURE;
-        cudaFree(d_pbo);
-        write_raw(pbo_out, pbo.data(), pbo.size());
-    }
+    if (json_stats)
+        std::printf("{\"impl\": \"b200_cli\", \"gpus\": %d, \"iters\": %d, \"width\": %d, \"height\": %d, \"depth\": %d, \"seconds\": %.6f, "
+                    "\"spp_per_s\": %.3f, \"mpath_segments_per_s\": %.3f, \"path_segments\": %llu, \"launches\": %llu, "
+                    "\"last_allreduce_ms\": %.4f}\n",
+                    gpus, n_iters, width, height, state.traceDepth, secs, n_iters / secs, (double)st.path_segments / secs / 1e6,
+                    (unsigned long long)st.path_segments, (unsigned long long)st.kernel_launches, allreduce_ms);
+    if (!pbo_out.empty()) write_raw(pbo_out, pbo.data(), pbo.size());
     if (!sum_out.empty()) write_raw(sum_out, state.image.data(), state.image.size() * sizeof(float));
 
     // saveImage (main.cpp:88-112): `samples` is the number of iterations accumulated
@@ -221,6 +286,5 @@ int main(int argc, char** argv)
         if (want_png) img.savePNG(base);
         if (want_hdr) img.saveHDR(base);
     }
-    b200pt_destroy(renderer);                           // pathtraceFree
     return EXIT_SUCCESS;
 }

@@ -14,6 +14,7 @@
 #include <string>
 #include <vector>
 
+#include "b200_mg.h"
 #include "b200_stream_compaction.hpp"
 
 namespace {
@@ -66,13 +67,15 @@ int main(int argc, char** argv)
     int lg = 20;
     unsigned seed = 565;
     bool cpu_only = false, json = false;
+    int gpus = 1;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         if (a == "--seed" && i + 1 < argc) seed = (unsigned)std::atoi(argv[++i]);
         else if (a == "--cpu-only") cpu_only = true;
         else if (a == "--json") json = true;
+        else if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);
         else if (a[0] != '-') lg = std::atoi(a.c_str());
-        else { std::printf("usage: %s [LG_SIZE] [--seed S] [--cpu-only] [--json]\n", argv[0]); return 1; }
+        else { std::printf("usage: %s [LG_SIZE] [--seed S] [--cpu-only] [--json] [--gpus K]\n", argv[0]); return 1; }
     }
     if (lg < 2 || lg > 30) { std::printf("LG_SIZE must be in [2, 30]\n"); return 1; }
     const int SIZE = 1 << lg, NPOT = SIZE - 3;
@@ -120,6 +123,28 @@ int main(int argc, char** argv)
             printElapsed(rows.back().ms, "(CUDA Measured)");
             printCmpResult(k.n, b, c);
         }
+    }
+
+    // --gpus K: the same scan over K devices of this box (include/b200_mg.h: contiguous shards, ONE all-gather of one
+    // int per device, device-side seeds), host pointers in and out like every other variant of this harness
+    b200mg* group = nullptr;
+    float exchange_ms = 0.f;
+    if (!cpu_only && gpus > 1) {
+        const int rc = b200mg_create(gpus, nullptr, &group);
+        if (rc) { std::printf("b200mg_create(%d): %s\n", gpus, b200mg_error_string(rc)); return 2; }
+        const struct { const char* desc; const char* key; int n; } mcases[] = {
+            {"sharded scan, power-of-two", "sharded_scan_pot", SIZE}, {"sharded scan, non-power-of-two", "sharded_scan_npot", NPOT}};
+        for (const auto& k : mcases) {
+            zero(c);
+            printDesc(k.desc);
+            float ms = 0.f;
+            const int rc2 = b200mg_scan_i32(group, k.n, c, a, &ms, &exchange_ms);
+            if (rc2) { std::printf("b200mg_scan_i32: %s\n", b200mg_error_string(rc2)); return 2; }
+            rows.push_back({k.key, ms});
+            printElapsed(ms, "(CUDA Measured, max over devices, all-gather included)");
+            printCmpResult(k.n, b, c);
+        }
+        rows.push_back({"sharded_scan_all_gather", exchange_ms});
     }
 
     std::printf("\n*****************************\n** STREAM COMPACTION TESTS **\n*****************************\n");
@@ -170,8 +195,25 @@ int main(int argc, char** argv)
         printCmpLenResult(count, expectedNPOT, b, c);
     }
 
+    if (group) {
+        const struct { const char* desc; const char* key; int n; int expected; } mcases[] = {
+            {"sharded compact, power-of-two", "sharded_compact_pot", SIZE, expectedCount},
+            {"sharded compact, non-power-of-two", "sharded_compact_npot", NPOT, expectedNPOT}};
+        for (const auto& k : mcases) {
+            zero(c);
+            printDesc(k.desc);
+            float ms = 0.f;
+            const int rc2 = b200mg_compact_i32(group, k.n, c, a, &count, &ms, &exchange_ms);
+            if (rc2) { std::printf("b200mg_compact_i32: %s\n", b200mg_error_string(rc2)); return 2; }
+            rows.push_back({k.key, ms});
+            printElapsed(ms, "(CUDA Measured, max over devices, all-gather included)");
+            printCmpLenResult(count, k.expected, b, c);
+        }
+        b200mg_destroy(group);
+    }
+
     if (json) {
-        std::printf("{\"n\": %d, \"seed\": %u, \"failures\": %d, \"ms\": {", SIZE, seed, failures);
+        std::printf("{\"n\": %d, \"seed\": %u, \"gpus\": %d, \"failures\": %d, \"ms\": {", SIZE, seed, gpus, failures);
         for (size_t i = 0; i < rows.size(); ++i) std::printf("%s\"%s\": %.4f", i ? ", " : "", rows[i].name, rows[i].ms);
         std::printf("}}\n");
     }
