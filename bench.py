@@ -554,6 +554,46 @@ def render_legs(torch, dist, rank, world, local_rank, args):
     return out
 
 
+def cxx_host_leg(torch, dist, rank, world, args):
+    """The same two sharded paths through the C++ host (north_star: "host code is C++"): ONE process, one host thread per
+    device, NCCL (include/b200_mg.h) -- `cuda_path_tracer --gpus N` and `stream_compaction_test --gpus N`, run by rank 0
+    while the other ranks wait on the rendezvous store (a CPU-side wait: their GPUs stay idle)."""
+    import datetime
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    store = dist.distributed_c10d._get_default_store()
+    out = {}
+    if rank == 0:
+        exe = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
+        try:
+            d = run_json_tool([exe, os.path.join(REPO, "scenes", "cornell.json"), "--gpus", str(world), "--iters",
+                               str(args.strong_iters), "--no-png", "--json"], 600)
+            out["render"] = {"iters": d["iters"], "seconds": d["seconds"], "spp_per_s": d["spp_per_s"],
+                             "mpath_segments_per_s": d["mpath_segments_per_s"], "last_allreduce_ms": d["last_allreduce_ms"],
+                             "how": f"cuda_path_tracer scenes/cornell.json --gpus {world} --iters {args.strong_iters}: wall clock around "
+                                    "render + all-reduce + D2H of the SUM image (first-call allocation included)"}
+        except Exception as e:                                     # noqa: BLE001
+            out["render"] = {"error": str(e)[:200]}
+        exe = os.path.join(REPO, "cuda_pathtracer_b200", "bin", "stream_compaction_test")
+        try:
+            d = run_json_tool([exe, "28", "--gpus", str(world), "--json"], 900)
+            n, ms = d["n"], d["ms"]
+            out["scan_compact"] = {"n": n, "failures": d["failures"], "sharded_scan_pot_ms": ms.get("sharded_scan_pot"),
+                                   "sharded_scan_gbs": 8.0 * n / ms["sharded_scan_pot"] / 1e6 if ms.get("sharded_scan_pot") else None,
+                                   "sharded_compact_pot_ms": ms.get("sharded_compact_pot"), "all_gather_ms": ms.get("sharded_scan_all_gather"),
+                                   "single_gpu_scan_pot_ms": ms.get("thrust_scan_pot"),
+                                   "how": f"stream_compaction_test 28 --gpus {world}: host arrays in and out, device time from the first shard "
+                                          "kernel to the last (all-gather included, copies excluded), max over devices; every result compared "
+                                          "with CPU::scan / CPU::compactWithoutScan by the harness"}
+        except Exception as e:                                     # noqa: BLE001
+            out["scan_compact"] = {"error": str(e)[:200]}
+        store.set("cxx_host_done", "1")
+    else:
+        store.wait(["cxx_host_done"], datetime.timedelta(minutes=25))
+    return {"cxx_host": out} if rank == 0 else {}
+
+
 def run_own(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -659,6 +699,7 @@ def run_own(args, rank, world, local_rank):
     if world > 1 and not args.skip_extras:
         extras.update(render_legs(torch, dist, rank, world, local_rank, args))
         extras.update(sharded_scan_compact_legs(torch, dist, rank, world, lg=args.sharded_lg))
+        extras.update(cxx_host_leg(torch, dist, rank, world, args))
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

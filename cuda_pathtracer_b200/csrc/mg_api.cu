@@ -197,6 +197,13 @@ int b200mg_create(int n_devices, const int* devices, b200mg** out)
         rc = nccl().ok ? nccl_code(nccl().CommInitAll(G->comm.data(), G->K, G->dev.data())) : B200_E_NCCL + 99;
         if (rc) G->comm.clear();
     }
+    if (!rc && G->K > 1) {            // NCCL sets its channels up lazily, at the first collective (tens of ms): pay that here
+        rc = gather_ints(G);
+        for (int g = 0; g < G->K && !rc; ++g) {
+            OnDevice on(G->dev[g]);
+            rc = (int)cudaStreamSynchronize(G->stream[g]);
+        }
+    }
     if (rc) { b200mg_destroy(G); return rc; }
     *out = G;
     return 0;
@@ -384,9 +391,16 @@ int b200mg_scan_i32(b200mg* G, int n, int* odata, const int* idata, float* kerne
         if (r) return r;
         cudaStream_t s = G->stream[g];
         if (e > b) CKC(cudaMemcpyAsync(G->d_in[g], idata + b, sizeof(int) * (size_t)(e - b), cudaMemcpyHostToDevice, s));
+        CKC(cudaStreamSynchronize(s));       // every shard is resident before any device's kernel timer starts (copies are
+        return 0;                            // excluded from kernel_ms, the reference's convention; the devices' copies end at different times)
+    });
+    if (rc) return rc;
+    rc = for_each_device(G, [&](int g) {
+        int b, e;
+        shard_of(n, g, K, b, e);
+        cudaStream_t s = G->stream[g];
         CKC(cudaEventRecord(G->ev[4 * g + 0], s));
-        if (K > 1) r = b200_reduce_i32_dev(G->sc[g], e - b, G->d_in[g], G->d_small[g], s);
-        return r;
+        return K > 1 ? b200_reduce_i32_dev(G->sc[g], e - b, G->d_in[g], G->d_small[g], s) : 0;
     });
     if (rc) return rc;
     // the one exchange: every device learns every shard's total
@@ -431,6 +445,15 @@ int b200mg_compact_i32(b200mg* G, int n, int* odata, const int* idata, int* coun
         if (r) return r;
         cudaStream_t s = G->stream[g];
         if (e > b) CKC(cudaMemcpyAsync(G->d_in[g], idata + b, sizeof(int) * (size_t)(e - b), cudaMemcpyHostToDevice, s));
+        CKC(cudaStreamSynchronize(s));       // (as in the scan: all shards resident before the kernel timers start)
+        return 0;
+    });
+    if (rc) return rc;
+    rc = for_each_device(G, [&](int g) {
+        int b, e;
+        shard_of(n, g, K, b, e);
+        cudaStream_t s = G->stream[g];
+        int r = 0;
         CKC(cudaEventRecord(G->ev[4 * g + 0], s));
         r = b200_compact_i32_dev(G->sc[g], e - b, G->d_out[g], G->d_in[g], G->d_small[g], s);
         if (r) return r;
