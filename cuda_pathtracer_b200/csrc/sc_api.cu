@@ -325,6 +325,53 @@ int b200_compact_i32(int n, int* odata, const int* idata, int* count, float* ker
     return run_hostapi(n, odata, idata, 0, true, count, kernel_ms);
 }
 
+// ---- allocation-free scan (include/b200_sc.h: no counterpart in the reference) ----
+// The look-back kernel's scratch in a file-scope device array instead of a cudaMalloc'd workspace.  In HOST code the
+// name `g_noalloc_desc` is only a stand-in for the symbol, not a device address: the address is fetched once per
+// device, with that device current, through cudaGetSymbolAddress, and THAT pointer goes to the kernel.
+static_assert(SC_LB_TILE == 4096 && SC_LB_STRIDE == 16, "b200_sc.h states one 128-byte descriptor per 4096 ints");
+constexpr size_t NOALLOC_DESC_WORDS = (size_t)(B200_SCAN_NOALLOC_MAX_N / SC_LB_TILE) * SC_LB_STRIDE;
+static_assert(NOALLOC_DESC_WORDS * sizeof(unsigned long long) == B200_SCAN_NOALLOC_SCRATCH_BYTES, "header and array must agree");
+static __device__ __align__(256) unsigned long long g_noalloc_desc[NOALLOC_DESC_WORDS];
+static __device__ __align__(256) unsigned g_noalloc_tickets[64];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct NoallocDevice { unsigned long long* desc; unsigned* tickets; bool ready; };
+NoallocDevice g_noalloc[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mutex;
+}  // namespace
+
+int b200_scan_i32_noalloc(int n, int* d_out, const int* d_in, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_out || !d_in))) return B200_E_BADARG;
+    if (n > B200_SCAN_NOALLOC_MAX_N) return B200_E_TOOLARGE;
+    if (n == 0) return 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return B200_E_NODEVICE; }
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return B200_E_BADARG;
+    NoallocDevice nd;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc[dev].ready) {                  // set-up, once per device, with that device current
+            void *p = nullptr, *t = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_noalloc_desc));
+            CK(cudaGetSymbolAddress(&t, g_noalloc_tickets));
+            g_noalloc[dev].desc = (unsigned long long*)p;
+            g_noalloc[dev].tickets = (unsigned*)t;
+            g_noalloc[dev].ready = true;
+        }
+        nd = g_noalloc[dev];
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    // The array keeps the previous call's descriptors: the ones this launch reads must start as "nothing published"
+    // (epoch 0).  The epoch is then a constant, so a captured graph replays correctly.
+    CK(cudaMemsetAsync(nd.desc, 0, sc_desc_words((unsigned)n) * sizeof(unsigned long long), s));
+    CK(cudaMemsetAsync(nd.tickets, 0, 2 * sizeof(unsigned), s));
+    CK(launch_scan_lookback(d_in, d_out, (unsigned)n, nd.desc, nd.tickets, 1u, nullptr, nullptr, s));
+    return 0;
+}
+
 const char* b200_error_string(int code)
 {
     switch (code) {
@@ -332,6 +379,7 @@ const char* b200_error_string(int code)
     case B200_E_BADARG: return "b200: bad argument";
     case B200_E_NODEVICE: return "b200: no CUDA device (this library has no CPU fallback)";
     case B200_E_NOMEM: return "b200: out of device memory";
+    case B200_E_TOOLARGE: return "b200: n exceeds B200_SCAN_NOALLOC_MAX_N (2^26 ints): the allocation-free scan has a fixed scratch array";
     default: return cudaGetErrorString((cudaError_t)code);
     }
 }

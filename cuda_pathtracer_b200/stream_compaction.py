@@ -31,6 +31,7 @@ def _lib():
         lib.b200_reduce_i32_dev.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                             ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_sc_last_launches.argtypes = [ctypes.c_void_p]
+        lib.b200_scan_i32_noalloc.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_error_string.argtypes = [ctypes.c_int]
         lib.b200_error_string.restype = ctypes.c_char_p
         lib._b200_typed = True
@@ -89,6 +90,16 @@ Naive = _ScanNamespace(NAIVE)
 Efficient = _EfficientNamespace(EFFICIENT)
 Thrust = _ScanNamespace(LOOKBACK)      # the single-pass look-back scan; no Thrust inside
 SinglePass = _EfficientNamespace(LOOKBACK)
+
+
+NOALLOC_MAX_N = 1 << 26
+E_TOOLARGE = 10005
+
+
+def scan_noalloc(n, d_out, d_in, stream=0):
+    """b200_scan_i32_noalloc: the look-back scan on device tensors with its scratch in a static device array of the
+    library -- allocates nothing; n <= NOALLOC_MAX_N (no counterpart in the reference, see include/b200_sc.h)"""
+    check(_lib().b200_scan_i32_noalloc(int(n), _ptr(d_out), _ptr(d_in), stream))
 
 
 class Context:

@@ -45,7 +45,8 @@ enum {
     B200_OK = 0,
     B200_E_BADARG = 10001,
     B200_E_NODEVICE = 10002,
-    B200_E_NOMEM = 10003
+    B200_E_NOMEM = 10003,
+    B200_E_TOOLARGE = 10005 /* b200_scan_i32_noalloc: n exceeds B200_SCAN_NOALLOC_MAX_N */
 };
 
 /* ---- host-or-device pointer entry points (what the reference's API binds to) ---------------- */
@@ -78,6 +79,25 @@ int b200_compact_i32_dev(b200_sc_ctx* ctx, int n, int* d_out, const int* d_in, i
 
 /* Sum of n ints (int32 wrap) into *d_total: the per-shard total exchanged between GPUs. */
 int b200_reduce_i32_dev(b200_sc_ctx* ctx, int n, const int* d_in, int* d_total, void* stream);
+
+/* ---- allocation-free entry point ------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Exclusive scan of n ints, DEVICE pointers, enqueued on `stream` and not synchronised -- the single-pass look-back
+ * kernel of b200_scan_i32_dev(.., B200_SCAN_LOOKBACK, ..), same result bit for bit.  It needs no context: the kernel's
+ * scratch (one 128-byte tile descriptor per 4096 ints) lives in a file-scope `static __device__` array of the library,
+ * B200_SCAN_NOALLOC_SCRATCH_BYTES (2 MiB) on every GPU that loads the library, held until the process exits.  The
+ * call allocates nothing (no cudaMalloc / cudaFree / allocating library routine): it clears the descriptors it is
+ * about to use with cudaMemsetAsync on `stream` and launches the kernel.
+ *   n > B200_SCAN_NOALLOC_MAX_N (2^26 ints = 256 MiB of input)  ->  B200_E_TOOLARGE, nothing is enqueued;
+ *   every call on a device shares that device's array: calls that OVERLAP on the GPU (different streams without an
+ *   ordering between them) race on it -- keep them on one stream or order them with events. */
+enum {
+    B200_SCAN_NOALLOC_MAX_N = 1 << 26,
+    B200_SCAN_NOALLOC_SCRATCH_BYTES = (B200_SCAN_NOALLOC_MAX_N / 4096) * 128
+};
+int b200_scan_i32_noalloc(int n, int* d_out, const int* d_in, void* stream);
 
 /* number of kernels the most recent call on this ctx launched (bench.py's gpu_launches) */
 int b200_sc_last_launches(const b200_sc_ctx* ctx);
