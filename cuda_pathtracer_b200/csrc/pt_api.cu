@@ -51,6 +51,7 @@ struct b200pt {
     int* d_cache_k = nullptr;
     float2* d_hit_uv = nullptr;
     float2* d_cache_uv = nullptr;
+    int* d_cache_perm = nullptr;       // bounce-0 order by material of the cached hits (material sort + cache)
     bool cache_valid = false;
     // triangle meshes / BVH / textures (b200pt_create_ext)
     BvhRec* d_nodes = nullptr;
@@ -271,6 +272,7 @@ int ensure_cache(b200pt* h)
     int r = dev_alloc((void**)&h->d_cache_n, sizeof(float4) * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_cache_k, sizeof(int) * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_cache_uv, sizeof(float2) * (size_t)h->P);
+    if (!r) r = dev_alloc((void**)&h->d_cache_perm, sizeof(int) * (size_t)h->P);
     h->cache_valid = false;
     return r;
 }
@@ -495,7 +497,7 @@ int b200pt_create_ext(const b200pt_scene* sc, const b200pt_scene_ext* ext, b200p
     if (!r) r = dev_alloc((void**)&h->d_mats, sizeof(MatRec) * (size_t)sc->n_materials);
     if (!r) r = dev_alloc((void**)&h->d_image, sizeof(float) * 3 * (size_t)h->P);
     if (!r) r = dev_alloc((void**)&h->d_segments, sizeof(unsigned long long));
-    if (!r) r = dev_alloc((void**)&h->d_tickets, sizeof(int) * (size_t)(h->depth > 0 ? h->depth : 1));
+    if (!r) r = dev_alloc((void**)&h->d_tickets, sizeof(int) * 2 * (size_t)(h->depth > 0 ? h->depth : 1));
     static_assert(sizeof(b200pt_material) == sizeof(MatRec), "material layouts must agree");
     if (!r) r = (int)cudaMemcpy(h->d_prims, prims.data(), sizeof(PrimRec) * prims.size(), cudaMemcpyHostToDevice);
     if (!r) r = (int)cudaMemcpy(h->d_mats, sc->materials, sizeof(MatRec) * (size_t)sc->n_materials, cudaMemcpyHostToDevice);
@@ -518,7 +520,7 @@ int b200pt_destroy(b200pt* h)
     cudaFree(h->d_desc); cudaFree(h->d_tickets); cudaFree(h->d_segments); cudaFree(h->d_image);
     cudaFree(h->d_hit_n); cudaFree(h->d_hit_k); cudaFree(h->d_perm[0]); cudaFree(h->d_perm[1]);
     cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
-    cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv);
+    cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv); cudaFree(h->d_cache_perm);
     cudaFree(h->d_nodes); cudaFree(h->d_tv); cudaFree(h->d_ta); cudaFree(h->d_tex); cudaFree(h->d_texels);
     cudaFree(h->d_gnodes); cudaFree(h->d_gboxes); cudaFree(h->d_gprims); cudaFree(h->d_gmesh);
     b200_sc_ctx_destroy(h->sc);
@@ -534,7 +536,8 @@ int b200pt_set_options(b200pt* h, const b200pt_options* o)
     if (!h || !o || o->batch < 0 || o->batch > PT_MAX_BATCH || o->geom_bvh < -1 || o->geom_bvh > 1) return B200_E_BADARG;
     // the cached first-bounce hits depend on the camera rays: any change of what shapes them drops the cache
     if (o->ssaa != h->opt.ssaa || o->dof != h->opt.dof || o->first_bounce_cache != h->opt.first_bounce_cache ||
-        o->mesh_brute_force != h->opt.mesh_brute_force || o->mesh_no_bbox != h->opt.mesh_no_bbox)
+        o->mesh_brute_force != h->opt.mesh_brute_force || o->mesh_no_bbox != h->opt.mesh_no_bbox ||
+        o->sort_by_material != h->opt.sort_by_material)      // (the cache also keeps the hits' order by material)
         h->cache_valid = false;
     h->opt = *o;
     return 0;
@@ -695,30 +698,47 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             }
             p.epoch = h->epoch;
             p.cache_mode = (b == 0 && cache_on) ? (h->cache_valid ? 2 : 1) : 0;
+            p.perm_shared = 0;
+            p.sort_bins = 0;
             if (split_only) {
                 if (p.cache_mode != 2) { CK(launch_isect(p, h->cfg, s)); h->launches += 1; }
                 p.perm_in = nullptr;
-                CK(launch_shade(p, s));
+                CK(launch_shade(p, h->cfg, s));
                 h->launches += 1;
             } else if (!sort_on) {
                 CK(launch_bounce(p, h->cfg, s));
                 h->launches += 1;
             } else {
                 // computeIntersections -> sort_by_key(materialId) -> shadeMaterials (pathtrace.cu:470-497)
-                if (p.cache_mode != 2) { CK(launch_isect(p, h->cfg, s)); h->launches += 1; }
                 const int bins = sort_bins(h), passes = sort_passes(h);
-                for (int pass = 0; pass < passes; ++pass) {
-                    p.perm_in = pass == 0 ? nullptr : h->d_perm[(pass - 1) & 1];
-                    p.perm_out = h->d_perm[pass & 1];
-                    CK(launch_sort_hist(p, pass, bins, s));
-                    r = b200_scan_i32_dev(h->sc, nb * bins * h->tiles, h->d_hist_scanned, h->d_hist, B200_SCAN_LOOKBACK,
-                                          nullptr, nullptr, s);
-                    if (r) return r;
-                    CK(launch_sort_scatter(p, pass, bins, s));
-                    h->launches += 2 + (uint64_t)b200_sc_last_launches(h->sc);
+                bool hist_done = false;
+#ifdef PT_NO_FUSED_HIST
+                p.sort_bins = 0;
+#else
+                p.sort_bins = passes == 1 ? bins : 0;        // one radix pass: the closest-hit kernel does the counting half where it can
+#endif
+                if (p.cache_mode != 2) { CK(launch_isect(p, h->cfg, s, &hist_done)); h->launches += 1; }
+                if (p.cache_mode == 2) {
+                    // The cached bounce-0 hits are the same every iteration, and so is their stable order by material:
+                    // it was stored when the cache was filled, one permutation for all slots.  No sort at all here.
+                    p.perm_in = h->d_cache_perm;
+                    p.perm_shared = 1;
+                } else {
+                    for (int pass = 0; pass < passes; ++pass) {
+                        p.perm_in = pass == 0 ? nullptr : h->d_perm[(pass - 1) & 1];
+                        p.perm_out = h->d_perm[pass & 1];
+                        if (!(pass == 0 && hist_done)) { CK(launch_sort_hist(p, h->cfg, pass, bins, s)); h->launches += 1; }
+                        r = b200_scan_i32_dev(h->sc, nb * bins * h->tiles, h->d_hist_scanned, h->d_hist, B200_SCAN_LOOKBACK,
+                                              nullptr, nullptr, s);
+                        if (r) return r;
+                        CK(launch_sort_scatter(p, h->cfg, pass, bins, pass == 0 && hist_done, s));
+                        h->launches += 1 + (uint64_t)b200_sc_last_launches(h->sc);
+                    }
+                    p.perm_in = h->d_perm[(passes - 1) & 1];
+                    if (p.cache_mode == 1)                   // slot 0's order of the cached hits, kept beside them
+                        CK(cudaMemcpyAsync(h->d_cache_perm, p.perm_in, sizeof(int) * (size_t)h->P, cudaMemcpyDeviceToDevice, s));
                 }
-                p.perm_in = h->d_perm[(passes - 1) & 1];
-                CK(launch_shade(p, s));
+                CK(launch_shade(p, h->cfg, s));
                 h->launches += 1;
             }
             if (p.cache_mode == 1) h->cache_valid = true;   // later launches are stream-ordered behind the fill

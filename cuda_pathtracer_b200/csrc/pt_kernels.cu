@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_raygen(const __grid_constant__ R
     const int idx = blockIdx.x * PT_THREADS + threadIdx.x;
     if (idx == 0) p.counts[slot] = p.P;             // live paths entering bounce 0
     if (idx == 0 && slot == 0)
-        for (int b = 0; b < p.depth; ++b) p.tickets[b] = 0;     // work-item counters of this batch's bounce launches
+        for (int b = 0; b < 2 * p.depth; ++b) p.tickets[b] = 0; // work-item counters of this batch's bounce launches ([depth..2 depth): closest hit)
     if (idx >= p.P) return;
     const int y = idx / p.cam.W, x = idx - y * p.cam.W;
     const int iter = p.iter0 + slot * p.stride;
@@ -699,7 +699,7 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
     float4* stash = reinterpret_cast<float4*>(smem_raw + sizeof(PersistShared));      // [3][PT_PWARPS][32]
     MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(PersistShared) + PT_STASH_BYTES);
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smats + n_smem_mats);
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE != 2 ? p.mesh.n_smem_nodes : 0));
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE < 2 ? p.mesh.n_smem_nodes : 0));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // ---- prologue: the work-item table of this launch, the first ticket, the staging copies ----
@@ -719,12 +719,13 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
         sh.total_items = base;
         put_item(sh, atomicAdd(p.tickets + p.bounce, 1), 0);
         // a CTA without work must not leave bulk copies in flight when it exits
-        if (sh.item[0][0] >= 0) stage_begin(p, sh.bar, smats, n_smem_mats, snodes, sprims, CACHE != 2);
+        if (sh.item[0][0] >= 0) stage_begin(p, sh.bar, smats, n_smem_mats, snodes, sprims, CACHE < 2);
     }
     if (blockIdx.x == 0 && threadIdx.x < p.batch) {
         const int n = sh.n_live[threadIdx.x];
         if (n == 0) p.counts[(p.bounce + 1) * p.batch + threadIdx.x] = 0;       // nobody else writes a dead slot's count
-        else atomicAdd(p.segments, (unsigned long long)n);
+        // (split pipeline: the closest-hit kernel has counted the segments, unless the first-bounce cache replaced it)
+        else if (CACHE != 3 || p.cache_mode == 2) atomicAdd(p.segments, (unsigned long long)n);
     }
     __syncthreads();
 
@@ -758,10 +759,22 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
         const int n_live = sh.n_live[slot];
         const int idx = tile * PT_PTILE + threadIdx.x;
         const bool active = idx < n_live;
-        PathState s = load_path(p.in, (size_t)slot * p.P + (active ? idx : 0));
+        // CACHE == 3: slot idx of the (material-sorted) order is source slot perm[idx]; the RNG seed uses idx, exactly as
+        // the reference's shading kernel indexes the sorted arrays (pathtrace.cu:479-497)
+        int src = active ? idx : 0;
+        if (CACHE == 3 && active && p.perm_in) src = p.perm_in[(p.perm_shared ? (size_t)0 : (size_t)slot * p.P) + idx];
+        PathState s = load_path(p.in, (size_t)slot * p.P + src);
 
         HitRec h;
-        if (CACHE == 2) {
+        if (CACHE == 3) {
+            const size_t at = (size_t)slot * p.P + src;
+            const float4 hn = p.cache_mode == 2 ? p.cache_n[src] : p.hit_n[at];
+            const float2 huv = p.cache_mode == 2 ? p.cache_uv[src] : p.hit_uv[at];
+            h.t = hn.x; h.n = v3(hn.y, hn.z, hn.w);
+            h.mat = p.cache_mode == 2 ? p.cache_k[src] : (p.hit_k[at] & 0x00ffffff);     // (top byte: in-tile rank, k_isect)
+            h.u = huv.x; h.v = huv.y;
+            mbar_wait(&sh.bar[0], 0u);                // the materials
+        } else if (CACHE == 2) {
             const float4 cn = p.cache_n[active ? idx : 0];
             const float2 cuv = p.cache_uv[active ? idx : 0];
             h.t = cn.x; h.n = v3(cn.y, cn.z, cn.w);
@@ -842,11 +855,39 @@ __global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const
     }
 }
 
+struct SortShared {
+    int cnt[PT_THREADS / 32][256];      // per-warp digit counts
+};
+
+// per-warp counts of each digit and this thread's stable rank among the equal digits of its warp
+__device__ __forceinline__ int warp_digit_rank(SortShared& sh, bool active, int digit, int bins)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int b = lane; b < bins; b += 32) sh.cnt[warp][b] = 0;
+    __syncwarp();
+    const unsigned act = __ballot_sync(FULL_MASK, active);
+    int rank = 0;
+    if (active) {
+        const unsigned peers = __match_any_sync(act, digit);
+        rank = __popc(peers & ((1u << lane) - 1u));
+        if (rank == 0) sh.cnt[warp][digit] = __popc(peers);
+    }
+    return rank;
+}
+
 // ------------------------------------------------------------------------------------------------
 // The split pipeline used when paths are bucketed by material between intersection and shading
 // (thrust::sort_by_key on materialId, pathtrace.cu:410-414,479-491): k_isect writes the hit
 // records, k_sort_hist / (scan) / k_sort_scatter build the stable sorted order as a permutation
 // (LSD radix, 8 bits per pass, one pass for up to 256 materials), k_shade gathers through it.
+//
+// With the material sort on and one radix pass (p.sort_bins > 0) k_isect also does the COUNTING half of the sort -- the
+// material id is in a register here: it writes the tile's digit histogram column (tiles beyond a slot's live range write
+// a zero column, as k_sort_hist does) and packs each path's STABLE RANK AMONG THE EQUAL KEYS OF ITS TILE into the top
+// byte of the stored key, so that the scatter after the scan is a pure streaming pass (k_sort_scatter_packed:
+// offset[key][tile] + rank; no warp match, no shared memory, no barrier).  Config 4: k_isect 16.3 -> 18.x ms instead of
+// + 7.5 ms of k_sort_hist, k_sort_scatter 6.4 -> 3.6 ms (profiles/r2_ab_variants.txt).  A persistent form of this kernel
+// (resident CTAs striding over the tiles, scene staged once per CTA) was measured 18 % SLOWER than one tile per CTA.
 template <int GB>
 __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
 {
@@ -857,7 +898,12 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
     const int n_live = p.counts[p.bounce * p.batch + slot];
-    if (tile * PT_THREADS >= n_live) return;
+    const int bins = p.sort_bins;
+    if (tile * PT_THREADS >= n_live) {
+        int* hist = p.hist + (size_t)slot * bins * p.tiles;
+        for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) hist[(size_t)bb * p.tiles + tile] = 0;
+        return;
+    }
     if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
     bounce_barriers_init(sh.bar);
     stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
@@ -868,13 +914,55 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     const HitRec h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
     if (active) {
         p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
-        p.hit_k[at] = h.mat;
+        if (bins == 0) p.hit_k[at] = h.mat;
         p.hit_uv[at] = make_float2(h.u, h.v);
         if (p.cache_mode == 1 && slot == 0) {
             p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             p.cache_k[idx] = h.mat;
             p.cache_uv[idx] = make_float2(h.u, h.v);
         }
+    }
+    if (bins > 0) {
+
+        __shared__ int cnt[PT_THREADS / 32][256];
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (int bb = lane; bb < bins; bb += 32) cnt[warp][bb] = 0;
+        __syncwarp();
+        const unsigned act = __ballot_sync(FULL_MASK, active);
+        int rank = 0;
+        if (active) {
+            const unsigned peers = __match_any_sync(act, h.mat & 255);
+            rank = __popc(peers & ((1u << lane) - 1u));
+            if (rank == 0) cnt[warp][h.mat & 255] = __popc(peers);
+        }
+        __syncthreads();
+        if (active) {
+            for (int ww = 0; ww < warp; ++ww) rank += cnt[ww][h.mat & 255];
+            p.hit_k[at] = h.mat | (rank << 24);
+        }
+        int* hist = p.hist + (size_t)slot * bins * p.tiles;
+        for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) {
+            int t = 0;
+#pragma unroll
+            for (int ww = 0; ww < PT_THREADS / 32; ++ww) t += cnt[ww][bb];
+            hist[(size_t)bb * p.tiles + tile] = t;
+        }
+    }
+}
+
+// the scatter half of the one-pass material bucketing: keys carry their in-tile rank (k_isect)
+__global__ void __launch_bounds__(PT_THREADS) k_sort_scatter_packed(const __grid_constant__ RenderParams p, int bins)
+{
+    const int items = p.batch * p.tiles;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+        const int slot = w / p.tiles, tile = w - slot * p.tiles;
+        const int n_live = p.counts[p.bounce * p.batch + slot];
+        const int j = tile * PT_THREADS + threadIdx.x;
+        if (j >= n_live) continue;
+        const int* offs = p.hist_scanned + (size_t)slot * bins * p.tiles;
+        const int key = p.hit_k[(size_t)slot * p.P + j];
+        const int pos = offs[(size_t)(key & 255) * p.tiles + tile] - offs[0] + (int)((unsigned)key >> 24);
+        p.perm_out[(size_t)slot * p.P + pos] = j;
     }
 }
 
@@ -933,7 +1021,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
     const int total = sh.total;
-    int* ticket = p.tickets + p.bounce;
+    int* ticket = p.tickets + p.depth + p.bounce;       // (the shade launch of this bounce draws from tickets[bounce])
 
     // per-lane state of the ray in flight
     bool has = false, walking = false;
@@ -1124,7 +1212,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
     const int total = sh.total;
-    int* ticket = p.tickets + p.bounce;
+    int* ticket = p.tickets + p.depth + p.bounce;       // (the shade launch of this bounce draws from tickets[bounce])
 
     bool has = false, walking = false;
     int slot = 0, idx = 0;
@@ -1255,48 +1343,33 @@ __device__ __forceinline__ int sort_digit(const RenderParams& p, int slot, int j
     return (keys[src] >> (8 * pass)) & 255;
 }
 
-struct SortShared {
-    int cnt[PT_THREADS / 32][256];      // per-warp digit counts
-};
-
-// per-warp counts of each digit and this thread's stable rank among the equal digits of its warp
-__device__ __forceinline__ int warp_digit_rank(SortShared& sh, bool active, int digit, int bins)
-{
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int b = lane; b < bins; b += 32) sh.cnt[warp][b] = 0;
-    __syncwarp();
-    const unsigned act = __ballot_sync(FULL_MASK, active);
-    int rank = 0;
-    if (active) {
-        const unsigned peers = __match_any_sync(act, digit);
-        rank = __popc(peers & ((1u << lane) - 1u));
-        if (rank == 0) sh.cnt[warp][digit] = __popc(peers);
-    }
-    return rank;
-}
-
 // hist[(slot * bins + bin) * tiles + tile] = number of elements of `tile` whose digit is `bin`
+// (grid-stride over the batch x tiles work items: most tiles are beyond the live range after a few bounces)
 __global__ void __launch_bounds__(PT_THREADS) k_sort_hist(const __grid_constant__ RenderParams p, int pass, int bins)
 {
     __shared__ SortShared sh;
-    const int slot = blockIdx.y, tile = blockIdx.x;
-    const int n_live = p.counts[p.bounce * p.batch + slot];
-    int* hist = p.hist + (size_t)slot * bins * p.tiles;
-    if (tile * PT_THREADS >= n_live) {               // every tile writes its column: no memset
-        for (int b = threadIdx.x; b < bins; b += PT_THREADS) hist[(size_t)b * p.tiles + tile] = 0;
-        return;
-    }
-    const int j = tile * PT_THREADS + threadIdx.x;
-    const bool active = j < n_live;
-    int src = 0;
-    const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
-    warp_digit_rank(sh, active, digit, bins);
-    __syncthreads();
-    for (int b = threadIdx.x; b < bins; b += PT_THREADS) {
-        int t = 0;
+    const int items = p.batch * p.tiles;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+        const int slot = w / p.tiles, tile = w - slot * p.tiles;
+        const int n_live = p.counts[p.bounce * p.batch + slot];
+        int* hist = p.hist + (size_t)slot * bins * p.tiles;
+        if (tile * PT_THREADS >= n_live) {               // every tile writes its column: no memset
+            for (int b = threadIdx.x; b < bins; b += PT_THREADS) hist[(size_t)b * p.tiles + tile] = 0;
+            continue;
+        }
+        const int j = tile * PT_THREADS + threadIdx.x;
+        const bool active = j < n_live;
+        int src = 0;
+        const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
+        warp_digit_rank(sh, active, digit, bins);
+        __syncthreads();
+        for (int b = threadIdx.x; b < bins; b += PT_THREADS) {
+            int t = 0;
 #pragma unroll
-        for (int w = 0; w < PT_THREADS / 32; ++w) t += sh.cnt[w][b];
-        hist[(size_t)b * p.tiles + tile] = t;
+            for (int ww = 0; ww < PT_THREADS / 32; ++ww) t += sh.cnt[ww][b];
+            hist[(size_t)b * p.tiles + tile] = t;
+        }
+        __syncthreads();
     }
 }
 
@@ -1304,23 +1377,27 @@ __global__ void __launch_bounds__(PT_THREADS) k_sort_hist(const __grid_constant_
 __global__ void __launch_bounds__(PT_THREADS) k_sort_scatter(const __grid_constant__ RenderParams p, int pass, int bins)
 {
     __shared__ SortShared sh;
-    const int slot = blockIdx.y, tile = blockIdx.x;
-    const int n_live = p.counts[p.bounce * p.batch + slot];
-    if (tile * PT_THREADS >= n_live) return;
-    const int* offs = p.hist_scanned + (size_t)slot * bins * p.tiles;
-    const int base = offs[0];                        // everything in the slots before this one
-    const int j = tile * PT_THREADS + threadIdx.x;
-    const bool active = j < n_live;
-    int src = 0;
-    const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
-    const int rank = warp_digit_rank(sh, active, digit, bins);
-    __syncthreads();
-    if (active) {
-        const int warp = threadIdx.x >> 5;
-        int before = 0;
-        for (int w = 0; w < warp; ++w) before += sh.cnt[w][digit];
-        const int pos = offs[(size_t)digit * p.tiles + tile] - base + before + rank;
-        p.perm_out[(size_t)slot * p.P + pos] = src;
+    const int items = p.batch * p.tiles;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+        const int slot = w / p.tiles, tile = w - slot * p.tiles;
+        const int n_live = p.counts[p.bounce * p.batch + slot];
+        if (tile * PT_THREADS >= n_live) continue;
+        const int* offs = p.hist_scanned + (size_t)slot * bins * p.tiles;
+        const int base = offs[0];                        // everything in the slots before this one
+        const int j = tile * PT_THREADS + threadIdx.x;
+        const bool active = j < n_live;
+        int src = 0;
+        const int digit = active ? sort_digit(p, slot, j, pass, src) : 0;
+        const int rank = warp_digit_rank(sh, active, digit, bins);
+        __syncthreads();
+        if (active) {
+            const int warp = threadIdx.x >> 5;
+            int before = 0;
+            for (int ww = 0; ww < warp; ++ww) before += sh.cnt[ww][digit];
+            const int pos = offs[(size_t)digit * p.tiles + tile] - base + before + rank;
+            p.perm_out[(size_t)slot * p.P + pos] = src;
+        }
+        __syncthreads();
     }
 }
 
@@ -1353,7 +1430,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_shade(const __grid_constant__ Re
         const float4 hn = p.cache_mode == 2 ? p.cache_n[src] : p.hit_n[at];
         const float2 huv = p.cache_mode == 2 ? p.cache_uv[src] : p.hit_uv[at];
         h.t = hn.x; h.n = v3(hn.y, hn.z, hn.w);
-        h.mat = p.cache_mode == 2 ? p.cache_k[src] : p.hit_k[at];
+        h.mat = p.cache_mode == 2 ? p.cache_k[src] : (p.hit_k[at] & 0x00ffffff);
         h.u = huv.x; h.v = huv.y;
     }
     mbar_wait(&sh.bar[0], 0u);                       // the materials
@@ -1489,6 +1566,7 @@ cudaError_t configure_kernels()
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 0>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 0>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<2, 0>, pcap);
+    if (e == cudaSuccess) e = allow_smem(k_bounce<3, 0>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 1>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 1>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 2>, pcap);
@@ -1595,8 +1673,9 @@ static size_t dyn_smem_bytes(int n_gnodes)
     return sizeof(DynShared) + (size_t)(n_gnodes < PT_DYN_GNODES ? n_gnodes : PT_DYN_GNODES) * 4 * sizeof(float4);
 }
 
-cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
+cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, bool* hist_done)
 {
+    if (hist_done) *hist_done = false;
     const int mode = search_mode(p);
 #ifndef PT_NO_DYN
     if (mode == 1 && p.mesh.n_nodes == 0) {           // geometry BVH proper, no meshes: dynamic ray fetch
@@ -1638,25 +1717,53 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
     if (mode == 2) k_isect<2><<<grid, PT_THREADS, smem, s>>>(p);
     else if (mode == 1) k_isect<1><<<grid, PT_THREADS, smem, s>>>(p);
     else k_isect<0><<<grid, PT_THREADS, smem, s>>>(p);
+    if (hist_done) *hist_done = p.sort_bins > 0;     // k_isect did the counting half of the sort
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort_hist(const RenderParams& p, int pass, int bins, cudaStream_t s)
+static cudaError_t stride_grid(const RenderParams& p, LaunchCfg& cfg, int per_sm, int& grid)
 {
-    k_sort_hist<<<dim3(p.tiles, p.batch), PT_THREADS, 0, s>>>(p, pass, bins);
+    if (cfg.sm_count == 0) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&cfg.sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+    }
+    const int items = p.batch * p.tiles;
+    grid = cfg.sm_count * per_sm;
+    if (grid > items) grid = items;
+    if (grid < 1) grid = 1;
+    return cudaSuccess;
+}
+
+cudaError_t launch_sort_hist(const RenderParams& p, LaunchCfg& cfg, int pass, int bins, cudaStream_t s)
+{
+    int grid = 0;
+    const cudaError_t e = stride_grid(p, cfg, 8, grid);
+    if (e != cudaSuccess) return e;
+    k_sort_hist<<<grid, PT_THREADS, 0, s>>>(p, pass, bins);
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaStream_t s)
+cudaError_t launch_sort_scatter(const RenderParams& p, LaunchCfg& cfg, int pass, int bins, bool packed, cudaStream_t s)
 {
-    k_sort_scatter<<<dim3(p.tiles, p.batch), PT_THREADS, 0, s>>>(p, pass, bins);
+    int grid = 0;
+    const cudaError_t e = stride_grid(p, cfg, 8, grid);
+    if (e != cudaSuccess) return e;
+    if (packed) k_sort_scatter_packed<<<grid, PT_THREADS, 0, s>>>(p, bins);
+    else k_sort_scatter<<<grid, PT_THREADS, 0, s>>>(p, pass, bins);
     return cudaGetLastError();
 }
 
-cudaError_t launch_shade(const RenderParams& p, cudaStream_t s)
+cudaError_t launch_shade(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
 {
+#ifdef PT_OLD_SHADE
     k_shade<<<dim3(p.tiles, p.batch), PT_THREADS, bounce_smem_bytes(0, p.n_mats, 0), s>>>(p);
     return cudaGetLastError();
+#else
+    // the persistent bounce kernel in its shade-only mode: tiles in ticket order, look-back off the critical path
+    return launch_persistent<3, 0>(p, cfg, persist_smem_bytes(0, p.n_mats, 0, 0), s);
+#endif
 }
 
 cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s)

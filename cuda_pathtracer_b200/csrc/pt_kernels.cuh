@@ -79,7 +79,8 @@ struct RenderParams {
     int P;                             // pixels = paths per iteration
     int tiles;                         // ceil(P / PT_THREADS)
     int ptiles;                        // ceil(P / PT_PTILE): tiles per slot of the persistent bounce kernel
-    int* tickets;                      // [depth]: next work item of each bounce's persistent launch (zeroed by k_raygen)
+    int* tickets;                      // [2 * depth]: next work item of each bounce's persistent launches (zeroed by k_raygen):
+                                       // [bounce] shading / fused bounce, [depth + bounce] closest hit with dynamic ray fetch
     int batch;                         // iterations in flight in this launch (grid.y)
     int iter0, stride;                 // slot s traces iteration iter0 + s * stride
     int bounce;                        // which bounce this launch is
@@ -88,6 +89,8 @@ struct RenderParams {
     float4* hit_n;                     // [batch][P] hit record {t, normal}
     int* hit_k;                        // [batch][P] hit record material id (the sort key; 0 on a miss)
     const int* perm_in;                // [batch][P] sorted position -> source slot (nullptr = identity)
+    int perm_shared;                   // 1: perm_in is ONE [P] permutation shared by all slots (the cached bounce-0 order)
+    int sort_bins;                     // > 0: the closest-hit kernel also writes this launch's digit histogram (pass 0)
     int* perm_out;
     int* hist;                         // [batch][bins][tiles] digit counts per tile
     const int* hist_scanned;           // exclusive scan of hist (flattened)
@@ -106,23 +109,23 @@ struct RenderParams {
 // process do not share or race on it (include/b200_pt.h: several renderers may coexist).
 struct LaunchCfg {
     int sm_count = 0;
-    size_t bounce_smem[3][3] = {};     // [CACHE][GB]: shared memory the cached grid was computed for (0 = not yet)
-    int bounce_grid[3][3] = {};
+    size_t bounce_smem[4][3] = {};     // [CACHE][GB]: shared memory the cached grid was computed for (0 = not yet)
+    int bounce_grid[4][3] = {};
     int dyn_grid = 0;                  // k_isect_dyn
     int dyn_mesh_grid = 0;             // k_isect_dyn_mesh
     size_t dyn_mesh_smem = ~(size_t)0;
-    int bucket_grid = 0;               // k_isect_bucket / k_shade_bucket (one-pass material bucketing)
-    size_t bucket_smem = ~(size_t)0;
 };
 
 size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0, int n_small = 0);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);   // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
-cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);
-cudaError_t launch_sort_hist(const RenderParams& p, int pass, int bins, cudaStream_t s);
-cudaError_t launch_sort_scatter(const RenderParams& p, int pass, int bins, cudaStream_t s);
-cudaError_t launch_shade(const RenderParams& p, cudaStream_t s);
+// hist_done (may be null): set when the launch also wrote the digit histogram of sort pass 0 (p.sort_bins > 0)
+cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, bool* hist_done = nullptr);
+cudaError_t launch_sort_hist(const RenderParams& p, LaunchCfg& cfg, int pass, int bins, cudaStream_t s);
+// packed: the keys carry their in-tile rank (written by a closest-hit launch that reported hist_done)
+cudaError_t launch_sort_scatter(const RenderParams& p, LaunchCfg& cfg, int pass, int bins, bool packed, cudaStream_t s);
+cudaError_t launch_shade(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);
 cudaError_t launch_tonemap(const float* image, int n_pixels, int iter, uchar4* out, cudaStream_t s);
 // per-stage probes on the reference's AoS layouts (PathSegment 12 words, ShadeableIntersection 7 words)
 cudaError_t launch_debug_raygen(const RenderParams& p, int iter, float* segments, cudaStream_t s);
