@@ -62,6 +62,9 @@ struct b200pt {
     MeshScene mesh{};
     // geometry BVH over the sphere / cube primitives (pt_gbvh.cu); rebuilt whenever the primitives change
     float4* d_gnodes = nullptr;
+    uint4* d_qnodes = nullptr;
+    size_t qnodes_cap = 0;
+    std::vector<uint4> host_qnodes;
     float4* d_gboxes = nullptr;
     PrimRec* d_gprims = nullptr;
     int* d_gmesh = nullptr;
@@ -204,7 +207,8 @@ int upload_geom_bvh(b200pt* h, const b200pt_scene* sc, const std::vector<PrimRec
         }
         have = true;
     }
-    build_geom_bvh(prims, cam, mlo, mhi, have, h->host_gnodes, h->host_gprims, h->host_gboxes, h->host_gmesh);
+    float qorg[3] = {0, 0, 0}, qcell[3] = {1, 1, 1};
+    build_geom_bvh(prims, cam, mlo, mhi, have, h->host_gnodes, h->host_gprims, h->host_gboxes, h->host_gmesh, h->host_qnodes, qorg, qcell);
     h->gb = GeomBvh{};
     h->n_indexed = (int)h->host_gprims.size();
     if (h->host_gnodes.empty()) return 0;
@@ -212,7 +216,13 @@ int upload_geom_bvh(b200pt* h, const b200pt_scene* sc, const std::vector<PrimRec
     if (!r) r = grow_buffer((void**)&h->d_gprims, &h->gprims_cap, sizeof(PrimRec) * h->host_gprims.size());
     if (!r) r = grow_buffer((void**)&h->d_gboxes, &h->gboxes_cap, sizeof(float4) * h->host_gboxes.size());
     if (!r) r = grow_buffer((void**)&h->d_gmesh, &h->gmesh_cap, sizeof(int) * (h->host_gmesh.size() + 1));
+    if (!r && !h->host_qnodes.empty()) r = grow_buffer((void**)&h->d_qnodes, &h->qnodes_cap, sizeof(uint4) * h->host_qnodes.size());
     if (r) return r;
+    if (!h->host_qnodes.empty()) {
+        CK(cudaMemcpyAsync(h->d_qnodes, h->host_qnodes.data(), sizeof(uint4) * h->host_qnodes.size(), cudaMemcpyHostToDevice, s));
+        h->gb.qnodes = h->d_qnodes;
+        for (int a = 0; a < 3; ++a) { h->gb.qorg[a] = qorg[a]; h->gb.qcell[a] = qcell[a]; }
+    }
     CK(cudaMemcpyAsync(h->d_gnodes, h->host_gnodes.data(), sizeof(float4) * h->host_gnodes.size(), cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(h->d_gprims, h->host_gprims.data(), sizeof(PrimRec) * h->host_gprims.size(), cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(h->d_gboxes, h->host_gboxes.data(), sizeof(float4) * h->host_gboxes.size(), cudaMemcpyHostToDevice, s));
@@ -522,7 +532,7 @@ int b200pt_destroy(b200pt* h)
     cudaFree(h->d_hist); cudaFree(h->d_hist_scanned); cudaFree(h->d_cache_n); cudaFree(h->d_cache_k);
     cudaFree(h->d_hit_uv); cudaFree(h->d_cache_uv); cudaFree(h->d_cache_perm);
     cudaFree(h->d_nodes); cudaFree(h->d_tv); cudaFree(h->d_ta); cudaFree(h->d_tex); cudaFree(h->d_texels);
-    cudaFree(h->d_gnodes); cudaFree(h->d_gboxes); cudaFree(h->d_gprims); cudaFree(h->d_gmesh);
+    cudaFree(h->d_gnodes); cudaFree(h->d_qnodes); cudaFree(h->d_gboxes); cudaFree(h->d_gprims); cudaFree(h->d_gmesh);
     b200_sc_ctx_destroy(h->sc);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);

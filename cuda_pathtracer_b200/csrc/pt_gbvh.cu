@@ -115,9 +115,10 @@ int build(std::vector<Tmp>& nodes, std::vector<Ref>& refs, int begin, int end, i
 
 void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], const double mesh_lo[3], const double mesh_hi[3],
                     bool have_mesh_bounds, std::vector<float4>& nodes_out, std::vector<PrimRec>& prims_out,
-                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out)
+                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out, std::vector<uint4>& qnodes_out,
+                    float qorg[3], float qcell[3])
 {
-    nodes_out.clear(); prims_out.clear(); boxes_out.clear(); mesh_prims_out.clear();
+    nodes_out.clear(); prims_out.clear(); boxes_out.clear(); mesh_prims_out.clear(); qnodes_out.clear();
     struct Extra { double s[3]; double d_hit, d_t; bool aligned, finite; Box3 tight; };
     std::vector<Extra> extra;
     const double eps = 1.1920928955078125e-7;
@@ -279,6 +280,46 @@ void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], 
         nodes_out[4 * i + 1] = hi4(l.box, ref_of(t.right));
         nodes_out[4 * i + 2] = lo4(r.box, 0);
         nodes_out[4 * i + 3] = hi4(r.box, 0);
+    }
+
+    // The same tree in 32-byte nodes for k_isect_dyn, whose walk is bound by the L1 load path (one 16-byte load per lane
+    // is one tag look-up per lane: four per 64-byte node): 16-bit coordinates on one grid over the root box, lower
+    // corners rounded down and upper corners rounded up by one extra cell -- the boxes only ever grow (a cell is 1/65000
+    // of the scene: 1e-3 for config 5's 80 units), and the decoded value q * cell + org is off by an ulp at most, which the
+    // extra cell covers.  Skipped (qnodes_out stays empty) when a box is not finite.
+    bool finite = true;
+    for (const Extra& ex : extra) finite = finite && ex.finite;
+    const Box3& root = tmp[(size_t)order[0]].box;
+    for (int a = 0; a < 3; ++a) finite = finite && std::isfinite(root.lo[a]) && std::isfinite(root.hi[a]) && root.hi[a] - root.lo[a] < 1e30;
+    if (!finite) return;
+    double org[3], cell[3];
+    for (int a = 0; a < 3; ++a) {
+        const double ext = std::max(root.hi[a] - root.lo[a], 1e-6);
+        cell[a] = ext / 65000.0;
+        org[a] = root.lo[a] - 200.0 * cell[a];               // 65000 cells of the scene + 200 spare ones on either side
+        qorg[a] = (float)org[a];
+        qcell[a] = (float)cell[a];
+    }
+    auto q_lo = [&](double v, int a) {                            // against the FLOAT grid the kernel decodes with
+        const double q = std::floor((v - (double)qorg[a]) / (double)qcell[a]) - 1.0;
+        return (unsigned)std::min(65535.0, std::max(0.0, q));
+    };
+    auto q_hi = [&](double v, int a) {
+        const double q = std::ceil((v - (double)qorg[a]) / (double)qcell[a]) + 1.0;
+        return (unsigned)std::min(65535.0, std::max(0.0, q));
+    };
+    qnodes_out.resize(2 * order.size());
+    for (size_t i = 0; i < order.size(); ++i) {
+        const Tmp& t = tmp[(size_t)order[i]];
+        const Box3 &l = tmp[(size_t)t.left].box, &r = tmp[(size_t)t.right].box;
+        const unsigned c[12] = {q_lo(l.lo[0], 0), q_lo(l.lo[1], 1), q_lo(l.lo[2], 2), q_hi(l.hi[0], 0), q_hi(l.hi[1], 1), q_hi(l.hi[2], 2),
+                                q_lo(r.lo[0], 0), q_lo(r.lo[1], 1), q_lo(r.lo[2], 2), q_hi(r.hi[0], 0), q_hi(r.hi[1], 1), q_hi(r.hi[2], 2)};
+        uint4 A, B;
+        A.x = c[0] | (c[1] << 16); A.y = c[2] | (c[3] << 16); A.z = c[4] | (c[5] << 16); A.w = c[6] | (c[7] << 16);
+        B.x = c[8] | (c[9] << 16); B.y = c[10] | (c[11] << 16);
+        B.z = (unsigned)ref_of(t.left); B.w = (unsigned)ref_of(t.right);
+        qnodes_out[2 * i] = A;
+        qnodes_out[2 * i + 1] = B;
     }
 }
 

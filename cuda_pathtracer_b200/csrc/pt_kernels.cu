@@ -127,6 +127,17 @@ __device__ __forceinline__ void hit_attributes(const MeshScene& M, const PrimRec
     }
 }
 
+// one 16-bit grid coordinate of a 32-byte geometry-BVH node -> float: 0x4B000000 | q is the float 2^23 + q exactly, so the
+// integer-to-float conversion (a quarter-rate instruction) becomes a byte permute and an add
+__device__ __forceinline__ float qdec_lo(unsigned w, float cell, float org)
+{
+    return fmaf(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)) - 8388608.0f, cell, org);
+}
+__device__ __forceinline__ float qdec_hi(unsigned w, float cell, float org)
+{
+    return fmaf(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)) - 8388608.0f, cell, org);
+}
+
 // conservative ray / box test of the geometry BVH: entry distance, or a negative value on a miss.
 // Not parity-critical (it only prunes), so plain fast arithmetic; fminf / fmaxf drop the NaNs of
 // 0 * inf, which makes a degenerate slab "no constraint".
@@ -986,6 +997,9 @@ __global__ void __launch_bounds__(PT_THREADS) k_sort_scatter_packed(const __grid
 #ifndef PT_DYN_STEPS
 #define PT_DYN_STEPS 8
 #endif
+#ifndef PT_DYN_CULL
+#define PT_DYN_CULL 0
+#endif
 #ifndef PT_DYN_GNODES
 #define PT_DYN_GNODES 16           // staged nodes (1 KB); more takes L1 capacity away from the rest of the tree (512: 137 spp/s, 64: 142, 16: 144)
 #endif
@@ -996,14 +1010,26 @@ struct DynShared {
     int pad_;
     int base[PT_MAX_BATCH + 2];       // exclusive prefix of the slots' live counts
 };
+#ifndef PT_DYN_POOL
+#define PT_DYN_POOL 0                 // 1: warp-cooperative exact tests (k_isect_dyn) -- measured slower, see the A/B record
+#endif
+#ifndef PT_DYN_DRAIN_LANES
+#define PT_DYN_DRAIN_LANES 1          // lanes that must need their candidates tested before the warp does it
+#endif
+struct DynWarpShared {                // per warp: the dealing pool and the way back of the results
+    unsigned pool[PT_THREADS / 32][32];
+    unsigned long long res[PT_THREADS / 32][32];
+    float4 aux[PT_THREADS / 32][32];
+};
 
 __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     DynShared& sh = *reinterpret_cast<DynShared*>(smem_raw);
-    const float4* snodes_g = reinterpret_cast<const float4*>(smem_raw + sizeof(DynShared));
+    const uint4* snodes_q = reinterpret_cast<const uint4*>(smem_raw + sizeof(DynShared));
     const int lane = threadIdx.x & 31;
     const int n_staged = p.gb.n_nodes < PT_DYN_GNODES ? p.gb.n_nodes : PT_DYN_GNODES;
+    const V3 qorg = v3(p.gb.qorg[0], p.gb.qorg[1], p.gb.qorg[2]), qcell = v3(p.gb.qcell[0], p.gb.qcell[1], p.gb.qcell[2]);
     bounce_barriers_init(sh.bar);
     if (threadIdx.x == 0) {
         int run = 0;
@@ -1014,9 +1040,9 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
         sh.base[p.batch] = run;
         sh.total = run;
         if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
-        const unsigned bytes = (unsigned)(n_staged * 4 * sizeof(float4));
+        const unsigned bytes = (unsigned)(n_staged * 2 * sizeof(uint4));
         mbar_expect_tx(&sh.bar[0], bytes);
-        bulk_g2s(const_cast<float4*>(snodes_g), p.gb.nodes, bytes, &sh.bar[0]);
+        bulk_g2s(const_cast<uint4*>(snodes_q), p.gb.qnodes, bytes, &sh.bar[0]);
     }
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
@@ -1031,11 +1057,14 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
     int hit = -1;
     Cand best;
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
+    static_assert(PT_GBVH_LEAF == 1, "the walk below takes a negative child reference for ONE primitive");
+#if PT_DYN_POOL
+    __shared__ DynWarpShared wsh;
+#endif
     int stack[64];
     int cand_prim[PT_GCAND];
     float cand_t[PT_GCAND];
-    int sp = 0, nc = 0, node = 0;
-    int lp_first = 0, lp_left = 0;                    // primitives of the leaf at hand whose own boxes are still to be tested
+    int sp = 0, nc = 0, node = 0, top = 0;            // top: the newest stack entry (entries below it are in stack[0 .. sp-2])
     bool exhausted = false;                           // warp-uniform: the ticket counter has run past the last ray
 
     for (;;) {
@@ -1060,7 +1089,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                     t_min = 3.402823466e+38f;
                     hit = -1;
                     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
-                    sp = 0; nc = 0; node = 0; lp_left = 0;
+                    sp = 0; nc = 0; node = 0;
                     // a NaN direction (glm::refract past the critical angle) hits nothing in the reference
                     walking = d.x == d.x && d.y == d.y && d.z == d.z;
                     has = true;
@@ -1072,63 +1101,126 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
         if (idle == FULL_MASK) break;                 // only once exhausted: nothing in flight, nothing to fetch
 
         // ---- walk: box tests only, candidates listed ----
-        // A step tests TWO boxes whatever the lane stands at: the two child boxes of an inner node, or the own
-        // boxes of the next two primitives of a leaf (both are four consecutive float4: lo, hi, lo, hi) -- so the
-        // lanes at leaves and the lanes at inner nodes run the same instructions.  (Looping over a leaf's
-        // primitives inside the node visit ran at 3 of 32 threads and was a third of all instructions,
-        // profiles/r25_config5_k_isect_dyn_raw.csv.)
+        // The tree is built down to ONE primitive per leaf (PT_GBVH_LEAF == 1), so a child reference is either an inner
+        // node or a primitive whose own padded box IS the child box just tested: every step is "fetch one 64-byte node,
+        // test its two boxes", whatever the lane stands at, and what follows is a handful of selects -- a primitive child
+        // that was hit goes onto the candidate list, a node child is visited (near one first, far one pushed).  (With
+        // four primitives per leaf the lanes at leaves ran their own code at 8-11 of 32 threads, a third of the walk's
+        // instructions, profiles/r2e_config5_k_isect_dyn_raw.csv.)  The top of the visit stack lives in a register:
+        // a pop hands it over at once and the load of the entry below it has the whole next node visit to arrive (the
+        // pop's local-memory load used to be the largest single stall of the kernel, 22 % of all samples).
         for (int step = 0; step < PT_DYN_STEPS; ++step) {
-            const bool go = has && walking && nc <= PT_GCAND - 16;
+            const bool go = has && walking && nc <= PT_GCAND - 2;
             if (!__any_sync(FULL_MASK, go)) break;
             if (go) {
                 const float t_lim = fmaf(t_min, 1.0001f, 1e-4f);
-                const bool leaf = lp_left > 0;
-                const float4* q = leaf ? p.gb.boxes + 2 * (size_t)lp_first
-                                       : (node < n_staged ? snodes_g + 4 * node : p.gb.nodes + 4 * (size_t)node);
-                const float4* q2p = (leaf && lp_left == 1) ? q : q + 2;      // a leaf's last odd primitive: no second box
-                const float4 q0 = q[0], q1 = q[1], q2 = q2p[0], q3 = q2p[1];
-                const float tl = gbox_entry(q0, q1, o, inv, t_lim), tr = gbox_entry(q2, q3, o, inv, t_lim);
-                int ref = 0;
-                bool have_ref = false;
-                if (leaf) {
-                    if (tl >= 0.0f) { cand_prim[nc] = lp_first; cand_t[nc] = tl; ++nc; }
-                    if (lp_left > 1 && tr >= 0.0f) { cand_prim[nc] = lp_first + 1; cand_t[nc] = tr; ++nc; }
-                    const int done = lp_left > 1 ? 2 : 1;
-                    lp_first += done;
-                    lp_left -= done;
-                    if (lp_left > 0) continue;                     // more primitives of this leaf
+                // 32-byte node: two 16-byte loads instead of four (this walk is bound by the L1 load path: every 16-byte load
+                // of 32 lanes standing at 32 different nodes is 32 tag look-ups; ncu l1tex throughput 92 % of peak with the
+                // 64-byte nodes, profiles/r2e_config5_k_isect_dyn_raw.csv)
+                const uint4* q = node < n_staged ? snodes_q + 2 * node : p.gb.qnodes + 2 * (size_t)node;
+                const uint4 A = q[0], B = q[1];
+                float4 q0, q1, q2, q3;
+                q0.x = qdec_lo(A.x, qcell.x, qorg.x); q0.y = qdec_hi(A.x, qcell.y, qorg.y); q0.z = qdec_lo(A.y, qcell.z, qorg.z);
+                q1.x = qdec_hi(A.y, qcell.x, qorg.x); q1.y = qdec_lo(A.z, qcell.y, qorg.y); q1.z = qdec_hi(A.z, qcell.z, qorg.z);
+                q2.x = qdec_lo(A.w, qcell.x, qorg.x); q2.y = qdec_hi(A.w, qcell.y, qorg.y); q2.z = qdec_lo(B.x, qcell.z, qorg.z);
+                q3.x = qdec_hi(B.x, qcell.x, qorg.x); q3.y = qdec_lo(B.y, qcell.y, qorg.y); q3.z = qdec_hi(B.y, qcell.z, qorg.z);
+                float t0 = gbox_entry(q0, q1, o, inv, t_lim), t1 = gbox_entry(q2, q3, o, inv, t_lim);
+                int r0 = (int)B.z, r1 = (int)B.w;
+                if (t1 >= 0.0f && (!(t0 >= 0.0f) || t1 < t0)) {            // near child first
+                    const int r = r0; r0 = r1; r1 = r;
+                    const float t = t0; t0 = t1; t1 = t;
+                }
+                const bool ok0 = t0 >= 0.0f, ok1 = t1 >= 0.0f;
+                if (ok0 && r0 < 0) { cand_prim[nc] = (~r0) >> 3; cand_t[nc] = t0; ++nc; }
+                if (ok1 && r1 < 0) { cand_prim[nc] = (~r1) >> 3; cand_t[nc] = t1; ++nc; }
+                const bool n0 = ok0 && r0 >= 0, n1 = ok1 && r1 >= 0;
+                if (n0 && n1) {                                            // push the far node
+                    stack[sp > 0 ? sp - 1 : 0] = top;
+                    top = r1;
+                    ++sp;
+                }
+                if (n0 || n1) {
+                    node = n0 ? r0 : r1;
+                } else if (sp > 0) {                                       // pop
+                    node = top;
+                    --sp;
+                    top = stack[sp > 0 ? sp - 1 : 0];
                 } else {
-                    int ref_near = __float_as_int(q0.w), ref_far = __float_as_int(q1.w);
-                    bool near_ok = tl >= 0.0f, far_ok = tr >= 0.0f;
-                    if (far_ok && (!near_ok || tr < tl)) {
-                        const int r = ref_near; ref_near = ref_far; ref_far = r;
-                        const bool bb = near_ok; near_ok = far_ok; far_ok = bb;
-                    }
-                    if (near_ok) {
-                        ref = ref_near; have_ref = true;
-                        if (far_ok) stack[sp++] = ref_far;         // inner node or leaf: visited after the near side
-                    } else if (far_ok) {
-                        ref = ref_far; have_ref = true;
-                    }
-                }
-                if (!have_ref) {
-                    if (sp > 0) { ref = stack[--sp]; have_ref = true; }
-                    else walking = false;
-                }
-                if (have_ref) {
-                    if (ref >= 0) {
-                        node = ref;
-                    } else {                                       // a leaf: its primitives' own boxes come next
-                        const int v = ~ref;
-                        lp_first = v >> 3;
-                        lp_left = (v & 7) + 1;
-                    }
+                    walking = false;
                 }
             }
         }
 
         // ---- exact tests of the listed candidates, once some lane needs them ----
-        const bool need = has && nc > 0 && (!walking || nc > PT_GCAND - 16);
+        const bool need = has && nc > 0 && (!walking || nc > PT_GCAND - 2);
+#if PT_DYN_POOL
+        // WARP-COOPERATIVE: the pending candidates of all lanes are pooled and dealt out one per lane, whoever's ray they
+        // belong to.  (One ray per lane, a lane testing its own candidates, ran the exact sphere / cube tests -- a third of the
+        // kernel's instructions -- at 5 of 32 threads: few lanes have candidates at the same time, and the loop runs as long
+        // as the lane with the most.)  A round: every lane proposes its next candidate that is not behind its current hit,
+        // nearest first, then -- while the 32 places are not full -- its second, ...; lane i takes pool entry i = (primitive,
+        // owner lane), fetches the owner's ray with shuffles and runs the exact test; the results go back to the owner as the
+        // lexicographic minimum of (t, scene index) -- a 64-bit shared-memory atomicMin on (float bits, index): t > 0, so the
+        // bit patterns order like the values -- which is the hit the reference's ascending loop with its strict `<` keeps
+        // (pathtrace.cu:280); the tester that holds the minimum hands over what the normal needs.
+        // (with PT_DYN_DRAIN_LANES > 1 the warp waits for that many finished walks -- fuller pools, later pruning -- unless a
+        // list is full or no lane can walk on)
+        const bool can_walk = has && walking && nc <= PT_GCAND - 2;
+        if (__popc(__ballot_sync(FULL_MASK, need)) >= PT_DYN_DRAIN_LANES || __any_sync(FULL_MASK, has && nc > PT_GCAND - 2) ||
+            (!__any_sync(FULL_MASK, can_walk) && __any_sync(FULL_MASK, need))) {
+            unsigned* pool = wsh.pool[threadIdx.x >> 5];
+            unsigned long long* res = wsh.res[threadIdx.x >> 5];
+            float4* raux = wsh.aux[threadIdx.x >> 5];
+            int k = 0;
+            for (;;) {
+                int cnt = 0;
+                for (int pass = 0; pass < PT_GCAND && cnt < 32; ++pass) {
+                    const float lim = fmaf(t_min, 1.0001f, 1e-4f);
+                    while (has && k < nc && cand_t[k] > lim) ++k;
+                    const bool have = has && k < nc;
+                    const unsigned m = __ballot_sync(FULL_MASK, have);
+                    if (!m) break;
+                    const int at = cnt + __popc(m & ((1u << lane) - 1u));
+                    if (have && at < 32) { pool[at] = ((unsigned)cand_prim[k] << 5) | (unsigned)lane; ++k; }
+                    cnt = min(32, cnt + __popc(m));
+                }
+                if (cnt == 0) break;
+                res[lane] = ~0ull;
+                __syncwarp();
+                const unsigned e = lane < cnt ? pool[lane] : (unsigned)lane;
+                const int owner = (int)(e & 31u);
+                const V3 ro = v3(__shfl_sync(FULL_MASK, o.x, owner), __shfl_sync(FULL_MASK, o.y, owner), __shfl_sync(FULL_MASK, o.z, owner));
+                const V3 rd = v3(__shfl_sync(FULL_MASK, d.x, owner), __shfl_sync(FULL_MASK, d.y, owner), __shfl_sync(FULL_MASK, d.z, owner));
+                Cand c;
+                c.t = -1.0f; c.outside = true; c.aux = v3(0.f, 0.f, 0.f);
+                unsigned long long key = ~0ull;
+                if (lane < cnt) {
+                    const PrimRec& g = p.gb.prims[e >> 5];
+                    c = prim_test(g, ro, rd);
+                    if (c.t > 0.0f) {
+                        key = ((unsigned long long)__float_as_uint(c.t) << 32) | (unsigned)g.pad0;
+                        atomicMin(&res[owner], key);
+                    }
+                }
+                __syncwarp();
+                if (key != ~0ull && res[owner] == key) raux[owner] = make_float4(c.aux.x, c.aux.y, c.aux.z, c.outside ? 1.0f : 0.0f);
+                __syncwarp();
+                const unsigned long long mine = res[lane];
+                if (mine != ~0ull) {
+                    const float t = __uint_as_float((unsigned)(mine >> 32));
+                    const int gi = (int)(unsigned)mine;
+                    if (t_min > t || (t_min == t && gi < hit)) {
+                        const float4 a4 = raux[lane];
+                        t_min = t;
+                        hit = gi;
+                        best.t = t; best.aux = v3(a4.x, a4.y, a4.z); best.outside = a4.w != 0.0f;
+                    }
+                }
+                __syncwarp();
+            }
+            nc = 0;
+        }
+#else
         if (__any_sync(FULL_MASK, need)) {
             if (has && nc > 0) {
                 int k = 0;
@@ -1136,8 +1228,15 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                     const float lim = fmaf(t_min, 1.0001f, 1e-4f);
                     while (k < nc && cand_t[k] > lim) ++k;
                     if (k >= nc) break;
-                    const PrimRec& g = p.gb.prims[cand_prim[k]];
+                    const int ci = cand_prim[k];
+                    const PrimRec& g = p.gb.prims[ci];
                     ++k;
+#if PT_DYN_CULL
+                    // the cheap conservative test against the primitive's true shape (closest_small's): the world box of a
+                    // sphere or a rotated cube is mostly empty, and t_lo is a lower bound of the distance the exact test reports
+                    float t_lo;
+                    if (!cull_test(p.gb.crecs[2 * ci], p.gb.crecs[2 * ci + 1], g, o, d, inv, t_lo) || t_lo > t_min) continue;
+#endif
                     const Cand c = prim_test(g, o, d);
                     const int gi = g.pad0;
                     // lexicographic minimum of (t, index): what the ascending loop with strict `<` finds
@@ -1150,6 +1249,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                 nc = 0;
             }
         }
+#endif
 
         // ---- finished rays: the hit record goes to the ray's own index ----
         if (has && !walking && nc == 0) {
@@ -1571,7 +1671,7 @@ cudaError_t configure_kernels()
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 1>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<0, 2>, pcap);
     if (e == cudaSuccess) e = allow_smem(k_bounce<1, 2>, pcap);
-    if (e == cudaSuccess) e = allow_smem(k_isect_dyn, (int)(sizeof(DynShared) + (size_t)PT_DYN_GNODES * 4 * sizeof(float4)));
+    if (e == cudaSuccess) e = allow_smem(k_isect_dyn, (int)(sizeof(DynShared) + (size_t)PT_DYN_GNODES * 2 * sizeof(uint4)));
     if (e == cudaSuccess) e = allow_smem(k_isect_dyn_mesh, cap);
 
     if (e == cudaSuccess) e = allow_smem(k_isect<0>, cap);
@@ -1670,7 +1770,7 @@ cudaError_t launch_bounce(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s)
 
 static size_t dyn_smem_bytes(int n_gnodes)
 {
-    return sizeof(DynShared) + (size_t)(n_gnodes < PT_DYN_GNODES ? n_gnodes : PT_DYN_GNODES) * 4 * sizeof(float4);
+    return sizeof(DynShared) + (size_t)(n_gnodes < PT_DYN_GNODES ? n_gnodes : PT_DYN_GNODES) * 2 * sizeof(uint4);
 }
 
 cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, bool* hist_done)
@@ -1678,7 +1778,7 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, 
     if (hist_done) *hist_done = false;
     const int mode = search_mode(p);
 #ifndef PT_NO_DYN
-    if (mode == 1 && p.mesh.n_nodes == 0) {           // geometry BVH proper, no meshes: dynamic ray fetch
+    if (mode == 1 && p.mesh.n_nodes == 0 && p.gb.qnodes) {   // geometry BVH proper, no meshes: dynamic ray fetch
         const size_t smem = dyn_smem_bytes(p.gb.n_nodes);
         if (cfg.dyn_grid == 0) {
             const cudaError_t e = persistent_grid(k_isect_dyn, cfg, dyn_smem_bytes(1 << 30), cfg.dyn_grid);

@@ -23,7 +23,12 @@ constexpr int PT_SMEM_GNODES = PT_SMEM_GNODES_N;   // geometry-BVH nodes staged 
                                            // one tile per CTA (every tile re-stages them): config 5 89.4 spp/s with 32, 87.2 with 64,
                                            // 85.2 with 192, 83.5 with 512, 63.2 with 1024 (profiles/r5_ab_variants.txt); the rest of
                                            // the tree is served by L1 / L2
-constexpr int PT_GBVH_LEAF = 4;            // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference)
+#ifndef PT_GBVH_LEAF_N
+#define PT_GBVH_LEAF_N 1
+#endif
+constexpr int PT_GBVH_LEAF = PT_GBVH_LEAF_N;   // primitives per geometry-BVH leaf (at most 8: 3 bits of the child reference).  1: a child
+                                           // reference is an inner node or ONE primitive whose padded box is the child box itself
+                                           // (what k_isect_dyn's uniform walk step needs; 4 was the round-1 value)
 constexpr int PT_GBVH_AUTO = 1;            // geom_bvh = auto: use the BVH from this many sphere / cube primitives (with fewer
                                            // than a leaf's worth the tree is one node and the per-primitive boxes do the culling)
 constexpr int PT_SMALL_MAX = 24;           // sphere / cube primitives up to which the small-scene search replaces the tree
@@ -53,6 +58,12 @@ struct GeomBvh {
     const PrimRec* prims;              // copies in leaf order; pad0 = index in the scene's primitive array
     const float4* boxes;               // padded world box of each of them: {lo, -} {hi, -}
     const float4* crecs;               // cull records (two float4 per primitive, same order; pt_gbvh.cu)
+    const uint4* qnodes;               // the same tree in 32-byte nodes (two uint4): both child boxes as 12 unsigned 16-bit
+                                       // coordinates on ONE grid over the scene (qorg + q * qcell, rounded outwards), then
+                                       // the two child references.  nullptr: not available (a box is not finite).
+                                       //   A = {c0.lo.x | c0.lo.y << 16, c0.lo.z | c0.hi.x << 16, c0.hi.y | c0.hi.z << 16, c1.lo.x | c1.lo.y << 16}
+                                       //   B = {c1.lo.z | c1.hi.x << 16, c1.hi.y | c1.hi.z << 16, ref0, ref1}
+    float qorg[3], qcell[3];
     const int* mesh_prims;             // indices of the MESH primitives, ascending
     int n_nodes;                       // 0 = not in use (linear scan over the staged primitives)
     int n_smem_nodes;
@@ -142,6 +153,7 @@ bool bounce_is_persistent(const RenderParams& p);
 // (pad0 = scene index) with their padded boxes, and the indices of the MESH primitives.  Empty nodes_out: nothing to index.
 void build_geom_bvh(const std::vector<PrimRec>& prims, const double cam_pos[3], const double mesh_lo[3], const double mesh_hi[3],
                     bool have_mesh_bounds, std::vector<float4>& nodes_out, std::vector<PrimRec>& prims_out,
-                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out);
+                    std::vector<float4>& boxes_out, std::vector<int>& mesh_prims_out, std::vector<uint4>& qnodes_out,
+                    float qorg[3], float qcell[3]);
 
 }  // namespace ptk
