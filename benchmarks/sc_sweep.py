@@ -43,6 +43,27 @@ def time_op(fn, iters, flush):
     return times[len(times) // 2], times[0]
 
 
+def time_stream(fn_of_k, n_sets, launches):
+    """per-launch time of `launches` back-to-back launches cycling through n_sets distinct (input, output) pairs whose
+    total size exceeds the L2 (so every launch reads cold data), one CUDA-event pair around the whole train: what a
+    launch costs INSIDE a stream of work (the single-launch numbers above it carry ~10 us of launch + event latency)"""
+    stream = torch.cuda.current_stream()
+    for k in range(n_sets):
+        fn_of_k(k)
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(launches):
+            fn_of_k(i % n_sets)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1) / launches
+        best = ms if best is None else min(best, ms)
+    return best
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--lg", type=int, nargs="+", default=[20, 22, 24, 26, 28])
@@ -76,6 +97,20 @@ def main():
             row["compact_ms"] = med
             row["compact_gbs"] = (4.0 * n + 4.0 * k) / med / 1e6
             row["compact_frac"] = row["compact_gbs"] / peak
+            if lg <= 24:
+                # in-stream: rotate over enough buffer pairs to exceed the 126 MB L2 (8 B per element per pair)
+                n_sets = max(2, (300 << 20) // (8 * n) + 1)
+                ins = [torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda") for _ in range(n_sets)]
+                outs = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(n_sets)]
+                launches = max(64, 2 * n_sets)
+                for name, variant in (("lookback", sc.LOOKBACK), ("efficient", sc.EFFICIENT)):
+                    ms = time_stream(lambda k: ctx.scan(n, outs[k], ins[k], variant, stream=s), n_sets, launches)
+                    row[name + "_stream_ms"] = ms
+                    row[name + "_stream_frac"] = 8.0 * n / ms / 1e6 / peak
+                ms = time_stream(lambda k: ctx.compact(n, outs[k], ins[k], cnt, stream=s), n_sets, launches)
+                row["compact_stream_ms"] = ms
+                row["compact_stream_frac"] = (4.0 * n + 4.0 * int(cnt.item())) / ms / 1e6 / peak
+                del ins, outs
             med, best = time_op(lambda: ctx.reduce(n, a, cnt, stream=s), args.iters, flush)
             row["reduce_ms"] = med
             row["reduce_gbs"] = 4.0 * n / med / 1e6
