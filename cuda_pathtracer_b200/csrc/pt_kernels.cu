@@ -53,8 +53,24 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+#ifndef PT_MBAR_HINT_NS
+#define PT_MBAR_HINT_NS 0
+#endif
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
 {
+#if PT_MBAR_HINT_NS > 0
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"((unsigned)PT_MBAR_HINT_NS)
+        : "memory");
+#else
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -66,6 +82,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
         "}\n" ::"r"(smem_u32(bar)),
         "r"(parity)
         : "memory");
+#endif
 }
 
 struct BounceShared {
@@ -665,7 +682,7 @@ struct alignas(16) PersistShared {
     // cannot be posted before the answer to request it - 2 has been consumed, so a waiter never sees the
     // barrier more than one phase ahead.
     unsigned long long req_bar[2], resp_bar[2];
-    int warp_cnt[2][8];                   // survivors per compute warp, by tile parity
+    int warp_cnt[2][PT_PWARPS + 1];       // survivors per compute warp, by tile parity
     int item[2][4];                       // {slot (-1: no more work), tile, -, -} of the tile with this parity
     int req[2][4];                        // mailbox to the scan warp: {slot, tile (-1: stop), aggregate, last tile of the slot}
     int resp[2];                          // exclusive prefix of the tile with this parity
@@ -680,7 +697,7 @@ static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it m
 // three that the natural 74 registers allow: +4.8 % path segments/s on the Cornell box (profiles/r5_ab_variants.txt).
 // A cp.async prefetch of the next tile's paths, tried at the same time, changed nothing at 3 CTAs and lost 1 % at 4.
 #ifndef PT_BOUNCE_MIN_CTAS
-#define PT_BOUNCE_MIN_CTAS 4
+#define PT_BOUNCE_MIN_CTAS (1024 / PT_BTHREADS)
 #endif
 #ifndef PT_LB_K
 #define PT_LB_K 1
@@ -702,7 +719,7 @@ __device__ __forceinline__ void put_item(PersistShared& sh, int w, int parity)
 }
 
 template <int CACHE, int GB>
-__global__ void __launch_bounds__(PT_THREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const __grid_constant__ RenderParams p)
+__global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(const __grid_constant__ RenderParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     PersistShared& sh = *reinterpret_cast<PersistShared*>(smem_raw);
@@ -1696,7 +1713,7 @@ bool bounce_is_persistent(const RenderParams& p)
 
 // CTAs of a persistent launch: as many as are resident at once (more would only queue up behind them)
 template <typename K>
-static cudaError_t persistent_grid(K kernel, LaunchCfg& cfg, size_t smem, int& grid)
+static cudaError_t persistent_grid(K kernel, LaunchCfg& cfg, size_t smem, int& grid, int threads = PT_THREADS)
 {
     if (cfg.sm_count == 0) {
         int dev = 0;
@@ -1705,7 +1722,7 @@ static cudaError_t persistent_grid(K kernel, LaunchCfg& cfg, size_t smem, int& g
         if (e != cudaSuccess) return e;
     }
     int per_sm = 0;
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, PT_THREADS, smem);
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
     if (e != cudaSuccess) return e;
     grid = cfg.sm_count * (per_sm > 0 ? per_sm : 1);
     if (grid < 1) grid = 1;
@@ -1718,13 +1735,13 @@ static cudaError_t launch_persistent(const RenderParams& p, LaunchCfg& cfg, size
     // the occupancy query is a host-side table lookup, but cache it anyway per shared-memory size (per handle)
     if (cfg.bounce_smem[CACHE][GB] != smem + 1) {
         int g = 0;
-        const cudaError_t e = persistent_grid(k_bounce<CACHE, GB>, cfg, smem, g);
+        const cudaError_t e = persistent_grid(k_bounce<CACHE, GB>, cfg, smem, g, PT_BTHREADS);
         if (e != cudaSuccess) return e;
         cfg.bounce_grid[CACHE][GB] = g;
         cfg.bounce_smem[CACHE][GB] = smem + 1;
     }
     const int items = p.batch * p.ptiles, grid = cfg.bounce_grid[CACHE][GB];
-    k_bounce<CACHE, GB><<<grid < items ? grid : items, PT_THREADS, smem, s>>>(p);
+    k_bounce<CACHE, GB><<<grid < items ? grid : items, PT_BTHREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 

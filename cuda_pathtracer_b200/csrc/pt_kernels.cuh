@@ -8,9 +8,13 @@
 namespace ptk {
 
 constexpr int PT_THREADS = 256;            // paths per tile / threads per CTA
-constexpr int PT_PWARPS = 7;                // compute warps of the persistent fused bounce kernel; its eighth warp
+#ifndef PT_PWARPS_N
+#define PT_PWARPS_N 7
+#endif
+constexpr int PT_PWARPS = PT_PWARPS_N;      // compute warps of the persistent fused bounce kernel; one more warp
                                            // only runs the look-backs of the CTA's tiles (k_bounce, pt_kernels.cu)
 constexpr int PT_PTILE = PT_PWARPS * 32;   // paths per tile of that kernel
+constexpr int PT_BTHREADS = PT_PTILE + 32; // threads of its CTAs
 constexpr int PT_MAX_BATCH = 64;           // iterations in flight (b200pt_options::batch upper bound)
 constexpr int PT_CHUNK = 256;              // primitives staged per shared-memory buffer (40 KB)
 constexpr int PT_SMEM_MATS = 256;          // materials kept in shared memory (12 KB)
