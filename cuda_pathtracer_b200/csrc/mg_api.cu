@@ -137,14 +137,15 @@ int ensure_staging(b200mg* G, int g, size_t ints)
 // ONE all-gather of one int per device: small[0] of every device -> small[4 .. 4+K) of every device
 int gather_ints(b200mg* G)
 {
+    // (the events go around the group: NCCL enqueues a group's kernels at ncclGroupEnd, not at the call inside it)
+    for (int g = 0; g < G->K; ++g) { OnDevice on(G->dev[g]); cudaEventRecord(G->ev[4 * g + 2], G->stream[g]); }
     ncclResult_t r = nccl().GroupStart();
     for (int g = 0; g < G->K && r == ncclSuccess; ++g) {
         OnDevice on(G->dev[g]);
-        cudaEventRecord(G->ev[4 * g + 2], G->stream[g]);
         r = nccl().AllGather(G->d_small[g], G->d_small[g] + 4, 1, ncclInt32, G->comm[g], G->stream[g]);
-        cudaEventRecord(G->ev[4 * g + 3], G->stream[g]);
     }
     const ncclResult_t r2 = nccl().GroupEnd();
+    for (int g = 0; g < G->K; ++g) { OnDevice on(G->dev[g]); cudaEventRecord(G->ev[4 * g + 3], G->stream[g]); }
     return nccl_code(r != ncclSuccess ? r : r2);
 }
 
@@ -186,8 +187,8 @@ int b200mg_create(int n_devices, const int* devices, b200mg** out)
     for (int g = 0; g < G->K && !rc; ++g) {
         OnDevice on(G->dev[g]);
         cudaError_t e = cudaStreamCreateWithFlags(&G->stream[g], cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaMalloc((void**)&G->d_small[g], sizeof(int) * (4 + 2 * K + 4));
-        if (e == cudaSuccess) e = cudaMemset(G->d_small[g], 0, sizeof(int) * (4 + 2 * K + 4));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&G->d_small[g], sizeof(int) * (16 + 2 * K));
+        if (e == cudaSuccess) e = cudaMemset(G->d_small[g], 0, sizeof(int) * (16 + 2 * K));
         for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreate(&G->ev[4 * g + k]);
         rc = (int)e;
         if (!rc) rc = b200_sc_ctx_create(&G->sc[g]);
@@ -196,6 +197,15 @@ int b200mg_create(int n_devices, const int* devices, b200mg** out)
         G->comm.assign(K, nullptr);
         rc = nccl().ok ? nccl_code(nccl().CommInitAll(G->comm.data(), G->K, G->dev.data())) : B200_E_NCCL + 99;
         if (rc) G->comm.clear();
+    }
+    for (int g = 0; g < G->K && !rc; ++g) {      // load the scan library's kernels on every device (CUDA loads modules lazily)
+        OnDevice on(G->dev[g]);
+        int* s4 = G->d_small[g];
+        rc = b200_reduce_i32_dev(G->sc[g], 4, s4 + 4, s4, G->stream[g]);
+        if (!rc) rc = b200_scan_i32_dev(G->sc[g], 4, s4 + 4, s4, B200_SCAN_LOOKBACK, nullptr, nullptr, G->stream[g]);
+        if (!rc) rc = b200_compact_i32_dev(G->sc[g], 4, s4 + 4, s4, s4 + 8, G->stream[g]);
+        if (!rc) rc = (int)cudaMemsetAsync(s4, 0, sizeof(int) * 12, G->stream[g]);
+        if (!rc) rc = (int)cudaStreamSynchronize(G->stream[g]);
     }
     if (!rc && G->K > 1) {            // NCCL sets its channels up lazily, at the first collective (tens of ms): pay that here
         rc = gather_ints(G);
@@ -317,18 +327,18 @@ int b200mg_pt_reduce_read_sum(b200mg_pt* R, float* host_rgb, float* allreduce_ms
         R->reduced = true;
         return b200pt_read_sum(R->h[0], host_rgb);
     }
+    for (int g = 0; g < G->K; ++g) { OnDevice on(G->dev[g]); cudaEventRecord(G->ev[4 * g + 2], G->stream[g]); }
     ncclResult_t r = nccl().GroupStart();
     for (int g = 0; g < G->K && r == ncclSuccess; ++g) {
         OnDevice on(G->dev[g]);
         void* img = nullptr;
         const int rc = b200pt_sum_device_ptr(R->h[g], &img, nullptr);
         if (rc) { nccl().GroupEnd(); return rc; }
-        cudaEventRecord(G->ev[4 * g + 2], G->stream[g]);
         r = nccl().AllReduce(img, R->d_red[g], n, ncclFloat, ncclSum, G->comm[g], G->stream[g]);
-        cudaEventRecord(G->ev[4 * g + 3], G->stream[g]);
     }
     const ncclResult_t r2 = nccl().GroupEnd();
     if (r != ncclSuccess || r2 != ncclSuccess) return nccl_code(r != ncclSuccess ? r : r2);
+    for (int g = 0; g < G->K; ++g) { OnDevice on(G->dev[g]); cudaEventRecord(G->ev[4 * g + 3], G->stream[g]); }
     {
         OnDevice on(G->dev[0]);
         CKC(cudaMemcpyAsync(host_rgb, R->d_red[0], n * sizeof(float), cudaMemcpyDeviceToHost, G->stream[0]));
@@ -388,6 +398,7 @@ int b200mg_scan_i32(b200mg* G, int n, int* odata, const int* idata, float* kerne
         int b, e;
         shard_of(n, g, K, b, e);
         int r = ensure_staging(G, g, (size_t)(e - b));
+        if (!r) r = b200_sc_ctx_reserve(G->sc[g], e - b);      // the look-back workspace too: no allocation inside the timed region
         if (r) return r;
         cudaStream_t s = G->stream[g];
         if (e > b) CKC(cudaMemcpyAsync(G->d_in[g], idata + b, sizeof(int) * (size_t)(e - b), cudaMemcpyHostToDevice, s));
@@ -442,6 +453,7 @@ int b200mg_compact_i32(b200mg* G, int n, int* odata, const int* idata, int* coun
         int b, e;
         shard_of(n, g, K, b, e);
         int r = ensure_staging(G, g, (size_t)(e - b));
+        if (!r) r = b200_sc_ctx_reserve(G->sc[g], e - b);
         if (r) return r;
         cudaStream_t s = G->stream[g];
         if (e > b) CKC(cudaMemcpyAsync(G->d_in[g], idata + b, sizeof(int) * (size_t)(e - b), cudaMemcpyHostToDevice, s));

@@ -179,6 +179,15 @@ int b200_sc_ctx_destroy(b200_sc_ctx* c)
     return 0;
 }
 
+int b200_sc_ctx_reserve(b200_sc_ctx* c, int n)
+{
+    if (!c || n < 0) return B200_E_BADARG;
+    if (n == 0) return 0;
+    int r = ensure_lookback(c, (unsigned)n);
+    if (!r) r = ensure((void**)&c->level_sums, &c->level_cap, efficient_level_ints((unsigned)n), sizeof(int), false);
+    return r;
+}
+
 int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int variant,
                       const int* d_seed, int* d_total, void* stream)
 {

@@ -31,6 +31,7 @@ def _lib():
         lib.b200_reduce_i32_dev.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                             ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_sc_last_launches.argtypes = [ctypes.c_void_p]
+        lib.b200_sc_ctx_reserve.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.b200_scan_i32_noalloc.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_error_string.argtypes = [ctypes.c_int]
         lib.b200_error_string.restype = ctypes.c_char_p
@@ -130,6 +131,9 @@ class Context:
 
     def reduce(self, n, d_in, d_total, stream=0):
         check(_lib().b200_reduce_i32_dev(self._h, int(n), _ptr(d_in), _ptr(d_total), stream))
+
+    def reserve(self, n):
+        check(_lib().b200_sc_ctx_reserve(self._h, int(n)))
 
     def last_launches(self):
         return _lib().b200_sc_last_launches(self._h)

@@ -66,6 +66,10 @@ typedef struct b200_sc_ctx b200_sc_ctx; /* workspace: tile descriptors, level su
 int b200_sc_ctx_create(b200_sc_ctx** ctx);
 int b200_sc_ctx_destroy(b200_sc_ctx* ctx);
 
+/* Grow the context's workspace (tile descriptors, level sums) to what a scan / compact of n ints needs, so that later
+ * calls with up to n elements allocate nothing (the workspace otherwise grows on first use). */
+int b200_sc_ctx_reserve(b200_sc_ctx* ctx, int n);
+
 /* All pointers are device pointers; work is enqueued on `stream` (a cudaStream_t) and NOT
  * synchronised.  d_seed (may be NULL) is one device int added to every output element: the
  * exclusive prefix of the totals of the shards that precede this one (multi-GPU scan).
