@@ -45,6 +45,33 @@ def test_no_silent_cpu_fallback():
     assert not o.any()
 
 
+def test_no_silent_cpu_fallback_multi_gpu_and_noalloc():
+    """the multi-GPU layer and the allocation-free scan fail loudly too when there is no CUDA device"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from cuda_pathtracer_b200 import stream_compaction as sc
+    from cuda_pathtracer_b200.multigpu import DeviceGroup
+    with pytest.raises(pkg.B200Error) as e:
+        DeviceGroup(1)
+    assert e.value.code == 10002                      # B200_E_NODEVICE
+    with pytest.raises(pkg.B200Error):
+        sc.scan_noalloc(8, np.zeros(8, dtype=np.int32), np.arange(8, dtype=np.int32))
+    with pytest.raises(pkg.B200Error) as e:           # the size limit is checked before anything touches the device
+        sc.scan_noalloc(sc.NOALLOC_MAX_N + 1, np.zeros(8, dtype=np.int32), np.arange(8, dtype=np.int32))
+    assert e.value.code == sc.E_TOOLARGE
+
+
+def test_cli_usage_of_the_new_flags(repo_root):
+    """--gpus and --iter-stride exclude each other; unknown flags are a usage error (exit 1), as in the reference"""
+    import subprocess
+    exe = os.path.join(repo_root, "cuda_pathtracer_b200", "bin", "cuda_path_tracer")
+    scene = os.path.join(repo_root, "scenes", "cornell_tiny.json")
+    r = subprocess.run([exe, scene, "--gpus", "2", "--iter-stride", "2"], capture_output=True, text=True)
+    assert r.returncode == 1 and "exclude" in r.stderr
+    assert subprocess.run([exe, scene, "--preview-every"], capture_output=True).returncode == 1
+
+
 def test_product_does_not_reference_oracle(repo_root):
     """the product tree never imports / links / names oracle/ code"""
     for root, _, files in os.walk(os.path.join(repo_root, "cuda_pathtracer_b200")):
