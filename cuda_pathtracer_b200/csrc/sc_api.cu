@@ -21,7 +21,7 @@ struct b200_sc_ctx {
     unsigned epoch = 0;
     unsigned long long* desc = nullptr;   // tile descriptors (look-back)
     size_t desc_cap = 0;                  // in words
-    unsigned* tickets = nullptr;          // 2 tickets
+    unsigned* tickets = nullptr;          // 4 counters: [0], [1] tile tickets by epoch parity (SC_LB_TICKET builds), [2], [3] k_compact_ws
     int* level_sums = nullptr;            // tile sums of every level of the work-efficient scan
     size_t level_cap = 0;                 // in ints
     int* scratch[2] = {nullptr, nullptr}; // naive ping-pong
@@ -153,8 +153,8 @@ int b200_sc_ctx_create(b200_sc_ctx** out)
     if (!c) return B200_E_NOMEM;
     cudaError_t e = cudaGetDevice(&c->device);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->tickets, 2 * sizeof(unsigned));
-    if (e == cudaSuccess) e = cudaMemset(c->tickets, 0, 2 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->tickets, 4 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(c->tickets, 0, 4 * sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->small, 4 * sizeof(int));
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
@@ -252,7 +252,7 @@ int b200_compact_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int
     if (n == 0) { CK(cudaMemsetAsync(d_count, 0, sizeof(int), s)); return 0; }
     int r = ensure_lookback(c, (unsigned)n);
     if (r) return r;
-    CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, s));
+    CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
     c->last_launches = 1;
     return 0;
 }

@@ -89,8 +89,38 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
 }
 
 cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
-                                    unsigned* tickets, unsigned epoch, int* d_count, cudaStream_t s)
+                                    unsigned* tickets, unsigned epoch, int* d_count, int num_sms, cudaStream_t s)
 {
+#if SC_COMPACT_WS
+    using C = sct::Cfg<SC_WS_THREADS, SC_WS_VEC>;
+    constexpr size_t smem = sct::compact_ws_smem_bytes<C>();
+    // as many CTAs as are resident at once.  Function attributes are per DEVICE: set up once for each device that launches
+    // (a process may drive several, include/b200_mg.h)
+    static int per_sm_of[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (per_sm_of[dev] == 0) {
+        int a = 0, b = 0;
+        cudaError_t e = cudaFuncSetAttribute(sct::k_compact_ws<C, true, LBW, STRIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(sct::k_compact_ws<C, false, LBW, STRIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, sct::k_compact_ws<C, true, LBW, STRIDE>, C::threads + 32, smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sct::k_compact_ws<C, false, LBW, STRIDE>, C::threads + 32, smem);
+        if (e != cudaSuccess) return e;
+        per_sm_of[dev] = (a < b ? a : b) > 0 ? (a < b ? a : b) : -1;
+    }
+    const int per_sm = per_sm_of[dev];
+    if (per_sm <= 0) return cudaErrorLaunchOutOfResources;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + C::tile - 1) / C::tile);
+    unsigned grid = (unsigned)(per_sm * num_sms);
+    if (grid > tiles) grid = tiles;
+    // (the descriptor array is sized for the smaller scan tiles: sc_desc_words)
+    if (aligned16(d_in))
+        sct::k_compact_ws<C, true, LBW, STRIDE><<<grid, C::threads + 32, smem, s>>>(d_in, d_out, n, desc, tickets, epoch, d_count);
+    else
+        sct::k_compact_ws<C, false, LBW, STRIDE><<<grid, C::threads + 32, smem, s>>>(d_in, d_out, n, desc, tickets, epoch, d_count);
+    return cudaGetLastError();
+#else
+    (void)num_sms;
     const unsigned tiles = sc_cp_num_tiles(n);
     static const cudaError_t attr = [] {
         cudaError_t e = cudaFuncSetAttribute(sct::k_compact<CfgCP, true, LBW, TICKET, BACKOFF, STRIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -105,6 +135,7 @@ cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, uns
     else
         sct::k_compact<CfgCP, false, LBW, TICKET, BACKOFF, STRIDE><<<tiles, CfgCP::threads, sct::compact_smem_bytes<CfgCP>(), s>>>(d_in, d_out, n, desc, tickets, epoch, d_count);
     return cudaGetLastError();
+#endif
 }
 
 cudaError_t launch_reduce_tiles(const int* d_in, unsigned n, int* d_tile_sums, cudaStream_t s)

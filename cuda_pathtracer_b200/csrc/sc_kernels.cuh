@@ -36,9 +36,21 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
                                  unsigned* tickets, unsigned epoch, const int* d_seed, int* d_total,
                                  cudaStream_t s);
 
+
 // Single-pass compaction: keep in[i] != 0, order preserving (B5 replacement).
+// (SC_COMPACT_WS: the persistent warp-specialised kernel, look-back off the critical path; tickets[2], tickets[3] are its
+// tile / done counters, zero between launches)
+#ifndef SC_COMPACT_WS
+#define SC_COMPACT_WS 1
+#endif
+#ifndef SC_WS_THREADS
+#define SC_WS_THREADS 256
+#endif
+#ifndef SC_WS_VEC
+#define SC_WS_VEC 8
+#endif
 cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
-                                    unsigned* tickets, unsigned epoch, int* d_count, cudaStream_t s);
+                                    unsigned* tickets, unsigned epoch, int* d_count, int num_sms, cudaStream_t s);
 
 // Work-efficient three-phase scan pieces: per-tile reduce (up-sweep) and per-tile scan with a
 // tile offset (down-sweep).  tile_offsets == nullptr => single tile, offset 0.

@@ -263,6 +263,154 @@ k_compact(const int* __restrict__ in, int* __restrict__ out, unsigned n,
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_compact_ws: the single-pass compaction with the look-back OFF THE CRITICAL PATH (warp-specialised, persistent) --
+// the scheme of the renderer's bounce kernel (pt_kernels.cu: k_bounce).  In k_compact every tile's warps stand at a barrier
+// while warp 0 looks back over its predecessors (ncu: that barrier is the largest stall, 8 warps per issue slot).  Here
+//   * a CTA is C::warps compute warps + 1 look-back warp and keeps drawing tiles from an atomic ticket (so a tile's
+//     predecessors are always held by running CTAs: no deadlock whatever the residency);
+//   * the compute warps of tile k count, hand {tile, kept} to the look-back warp through a two-entry mbarrier mailbox, pack
+//     the survivors into one of TWO shared-memory buffers and go straight on;
+//   * one tile later they pick the exclusive prefix up and write the packed run of tile k out (128-bit stores from the first
+//     aligned destination element on, as in k_compact) -- the look-back has had a whole tile's load / count / pack to finish.
+// One named barrier per tile (the warp counts; it also orders the two buffers' reuse).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned ws_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void ws_mbar_init(unsigned long long* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ws_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void ws_mbar_arrive(unsigned long long* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ws_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void ws_mbar_wait(unsigned long long* bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WS_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WS_DONE_%=;\n"
+        "bra WS_WAIT_%=;\n"
+        "WS_DONE_%=:\n"
+        "}\n" ::"r"(ws_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+template <class C>
+struct WsShared {
+    unsigned long long req_bar[2], resp_bar[2];
+    int req[2][2];                 // {tile (-1: stop), kept}
+    int resp[2];                   // exclusive prefix of the tile with this parity
+    unsigned tile[2];              // the CTA's tile of this parity (drawn by thread 0 one iteration ahead)
+    int warp_sums[2][C::warps];
+};
+
+template <class C>
+constexpr size_t compact_ws_smem_bytes() { return (size_t)2 * C::tile * sizeof(int); }
+
+// the packed survivors `packed[0 .. kept)` of one tile -> out[base ..): head scalars, aligned 128-bit body, tail scalars
+template <int THREADS>
+__device__ __forceinline__ void write_run(int* __restrict__ out, const int* packed, int base, int kept)
+{
+    int* dst = out + base;
+    const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
+    int head = mis ? 4 - mis : 0;
+    if (head > kept) head = kept;
+    if ((int)threadIdx.x < head) dst[threadIdx.x] = packed[threadIdx.x];
+    const int body4 = (kept - head) >> 2;
+    int4* dst4 = reinterpret_cast<int4*>(dst + head);
+    for (int q = threadIdx.x; q < body4; q += THREADS) {
+        const int* src = packed + head + 4 * q;
+        st_stream(dst4 + q, make_int4(src[0], src[1], src[2], src[3]));
+    }
+    const int done = head + 4 * body4;
+    if ((int)threadIdx.x < kept - done) dst[done + threadIdx.x] = packed[done + threadIdx.x];
+}
+
+template <class C, bool VEC_OK, int LBW, int STRIDE>
+__global__ void __launch_bounds__(C::threads + 32)
+k_compact_ws(const int* __restrict__ in, int* __restrict__ out, unsigned n, unsigned long long* __restrict__ desc,
+             unsigned* __restrict__ tickets, unsigned epoch, int* __restrict__ d_count)
+{
+    extern __shared__ __align__(16) int packed2[];            // [2][C::tile]
+    __shared__ WsShared<C> sh;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + C::tile - 1) / C::tile);
+    if (threadIdx.x == 0) {
+        ws_mbar_init(&sh.req_bar[0], 1); ws_mbar_init(&sh.req_bar[1], 1);
+        ws_mbar_init(&sh.resp_bar[0], 1); ws_mbar_init(&sh.resp_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sh.tile[0] = atomicAdd(&tickets[2], 1u);              // tickets[2]: next tile, tickets[3]: CTAs done (both zero between launches)
+    }
+    __syncthreads();
+
+    if (warp == C::warps) {                                    // ---- the look-back warp ----
+        for (int it = 0;; ++it) {
+            ws_mbar_wait(&sh.req_bar[it & 1], (unsigned)((it >> 1) & 1));
+            const int tile = sh.req[it & 1][0], kept = sh.req[it & 1][1];
+            if (tile < 0) break;
+            const int e = lb_exclusive_prefix_cfg<LBW, LB_DEFAULT_BACKOFF_NS, STRIDE>(desc, (unsigned)tile, epoch, kept, 0, lane);
+            __syncwarp();                                      // every lane has read the request before it can be answered
+            if (lane == 0) {
+                if ((unsigned)tile == tiles - 1) *d_count = e + kept;
+                sh.resp[it & 1] = e;
+                ws_mbar_arrive(&sh.resp_bar[it & 1]);
+            }
+        }
+        return;
+    }
+
+    // ---- the compute warps ----
+    int prev_kept = 0, it = 0;
+    for (;; ++it) {
+        const unsigned tile = sh.tile[it & 1];                 // written before the previous iteration's barrier
+        if (tile >= tiles) break;                              // uniform over the CTA
+        int4 v[C::vec];
+        load_tile<C, VEC_OK>(in, n, tile, warp, lane, v);      // out-of-range reads as 0 == dropped
+        int s[C::vec], excl[C::vec];
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j)
+            s[j] = (v[j].x != 0) + (v[j].y != 0) + (v[j].z != 0) + (v[j].w != 0);
+        tile_warp_totals<C>(s, sh.warp_sums[it & 1], warp, lane);
+        if (threadIdx.x == 0) sh.tile[(it + 1) & 1] = atomicAdd(&tickets[2], 1u);
+        asm volatile("bar.sync 1, %0;" ::"n"(C::threads) : "memory");
+        const int kept = tile_exclusive_from_totals<C>(s, excl, sh.warp_sums[it & 1], warp, lane);
+        if (threadIdx.x == 0) {
+            sh.req[it & 1][0] = (int)tile;
+            sh.req[it & 1][1] = kept;
+            ws_mbar_arrive(&sh.req_bar[it & 1]);
+        }
+        if (it > 0) {                                          // the previous tile's run, now that its prefix is known
+            ws_mbar_wait(&sh.resp_bar[(it - 1) & 1], (unsigned)(((it - 1) >> 1) & 1));
+            write_run<C::threads>(out, packed2 + ((it - 1) & 1) * C::tile, sh.resp[(it - 1) & 1], prev_kept);
+        }
+        int* packed = packed2 + (it & 1) * C::tile;
+#pragma unroll
+        for (int j = 0; j < C::vec; ++j) {
+            int q = excl[j];
+            if (v[j].x != 0) packed[q++] = v[j].x;
+            if (v[j].y != 0) packed[q++] = v[j].y;
+            if (v[j].z != 0) packed[q++] = v[j].z;
+            if (v[j].w != 0) packed[q++] = v[j].w;
+        }
+        prev_kept = kept;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(C::threads) : "memory");      // the last tile's buffer is complete
+    if (it > 0) {
+        ws_mbar_wait(&sh.resp_bar[(it - 1) & 1], (unsigned)(((it - 1) >> 1) & 1));
+        write_run<C::threads>(out, packed2 + ((it - 1) & 1) * C::tile, sh.resp[(it - 1) & 1], prev_kept);
+    }
+    if (threadIdx.x == 0) {                                    // tell the look-back warp to leave
+        sh.req[it & 1][0] = -1;
+        ws_mbar_arrive(&sh.req_bar[it & 1]);
+        // the last CTA to get here (every CTA has drawn its last ticket by now) re-arms the counters for the next launch
+        if (atomicAdd(&tickets[3], 1u) == gridDim.x - 1) { tickets[2] = 0u; tickets[3] = 0u; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Work-efficient three-phase scan: k_reduce_tiles (up-sweep), recursion on the tile sums,
 // k_downsweep (per-tile scan seeded with the scanned tile sum).  12 B/element.
 // ------------------------------------------------------------------------------------------------
