@@ -216,6 +216,38 @@ def test_sorted_render_bit_exact_vs_reference_cuda(pt, oracle, scene, iters, fla
     r.close()
 
 
+def test_sort_with_more_than_256_materials(pt, oracle):
+    """material ids beyond one radix digit: the LSD passes of the round-1 kernels (k_sort_hist / k_sort_scatter) instead of
+    the one-pass bucketing.  The glass scene's materials replicated to 700 entries, every primitive moved to a copy of its
+    material with a different (large) id -- same shading, another sort order -- bit for bit against the oracle's stable sort"""
+    sc = load_scene("cornell_glass_small")
+    n, M = len(sc.materials), 700
+    assert M % n == 0
+    mats = (pt.Material * M)()
+    for i in range(M):
+        mats[i] = sc.materials[i % n]
+    sc.materials = mats
+    for gi, g in enumerate(sc.geoms):
+        g.materialid = g.materialid + n * ((gi * 37 + 5) % (M // n))
+    assert max(g.materialid for g in sc.geoms) > 255
+    gui = gui_from_flags(["--sort"], batch=1)
+    r = pt.Renderer(sc)
+    r.set_options(gui)
+    r.render(1, 6)
+    img, seg = r.read_sum(), r.stats()["path_segments"]
+    want, segments = oracle.render(sc, gui, 1, 6)
+    assert seg == segments and bits_equal(img, want)
+    # ... and with the first-bounce cache (the cached order by material comes from the last radix pass)
+    gui2 = gui_from_flags(["--sort", "--no-ssaa", "--no-dof"], batch=1)
+    gui2.firstBounceCache = True
+    r.reset()
+    r.set_options(gui2)
+    r.render(1, 5)
+    want2, seg2 = oracle.render(sc, gui2, 1, 5)
+    assert r.stats()["path_segments"] == seg2 and bits_equal(r.read_sum(), want2)
+    r.close()
+
+
 def test_sorted_golden_fixtures_present():
     missing = [c for c in SORT_RENDERS if not have_golden(c[0], c[1], c[3])]
     assert not missing, f"reference-CUDA goldens missing for {missing}: run tests/golden/make_pt_golden.py renders"
