@@ -383,7 +383,10 @@ __device__ __forceinline__ MeshHit bvh_traverse_literal(const MeshScene& M, cons
 // met -- one triangle per lane per trip, instead of a whole leaf whenever ANY lane of the warp
 // stands at one; (2) a node or leaf whose box starts behind the current hit (with a margin far
 // above the rounding of the slab distances) cannot hold a nearer or equal one and is skipped.
-constexpr int PT_MLEAVES = 12;      // listed leaves before the list is worked off
+#ifndef PT_MLEAVES_N
+#define PT_MLEAVES_N 12
+#endif
+constexpr int PT_MLEAVES = PT_MLEAVES_N;      // listed leaves before the list is worked off
 
 // a distance safely beyond t (t may be negative: glm::intersectRayTriangle also reports hits behind the origin)
 __device__ __forceinline__ float prune_limit(float t) { return fmaf(fabsf(t), 1e-4f, t) + 1e-4f; }
