@@ -155,6 +155,41 @@ __device__ __forceinline__ float qdec_hi(unsigned w, float cell, float org)
     return fmaf(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)) - 8388608.0f, cell, org);
 }
 
+// Slab distances of the 32-byte nodes straight from the grid coordinates: with, per ray and axis, ig = cell / d and
+// cg = (org - o) / d, the distance to the plane with grid coordinate q is fma(q, ig, cg) -- a byte permute, an add (q as a
+// float) and the fma: three instructions per plane instead of five (decode to world, subtract the origin, multiply).
+// The product is exact inside the fma; ig and cg carry half an ulp each, i.e. the plane moves by less than 1e-2 of a cell
+// -- the boxes are rounded outwards by a whole one.  (Folding the 2^23 of the conversion trick into cg as well -- two
+// instructions per plane -- costs a whole cell of precision for every 1 / |d|, weakens the pruning of rays that run
+// nearly parallel to an axis and measured 5 % SLOWER.)
+// A direction component of exactly 0 must NOT become 1 / d = inf here: q * inf - inf = NaN, which fminf / fmaxf drop -- "no
+// constraint" on that axis -- and a ray with TWO zero components then passes every box of its column and walks the whole
+// tree.  Such rays exist: the cosine-hemisphere sample with u1 rounding to 1.0 (64 of the 2^31 generator states) leaves an
+// axis-aligned surface exactly along its normal -- about one ray per launch at config 5's size, and its 3.5 ms walk was the
+// tail that made this form 30-45 % slower on bounce 1 (ncu: one SM active 17.9 M cycles, the others 11.1 M,
+// profiles/r2_ab_variants.txt).  1 / d is therefore clamped to +-1e20: the ray then drifts by 1e-20 t along that axis, and the
+// rounding of the two terms (now about 1e21 each) moves a plane by less than 1e-5 -- far inside the outward cell of the boxes.
+struct QRay {
+    V3 ig, cg;
+};
+__device__ __forceinline__ QRay qray(const V3& o, const V3& inv_in, const V3& qorg, const V3& qcell)
+{
+    const V3 inv = v3(fminf(fmaxf(inv_in.x, -1e20f), 1e20f), fminf(fmaxf(inv_in.y, -1e20f), 1e20f), fminf(fmaxf(inv_in.z, -1e20f), 1e20f));
+    QRay r;
+    r.ig = v3(qcell.x * inv.x, qcell.y * inv.y, qcell.z * inv.z);
+    r.cg = v3((qorg.x - o.x) * inv.x, (qorg.y - o.y) * inv.y, (qorg.z - o.z) * inv.z);
+    return r;
+}
+__device__ __forceinline__ float qlo(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)) - 8388608.0f; }
+__device__ __forceinline__ float qhi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)) - 8388608.0f; }
+// entry distance into the box whose planes lie at the distances (ax, bx) x (ay, by) x (az, bz), or negative on a miss
+__device__ __forceinline__ float qbox_entry(float ax, float bx, float ay, float by, float az, float bz, float t_lim)
+{
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_lim));
+    return tn <= tf * 1.00001f + 1e-5f ? tn : -1.0f;
+}
+
 // conservative ray / box test of the geometry BVH: entry distance, or a negative value on a miss.
 // Not parity-critical (it only prunes), so plain fast arithmetic; fminf / fmaxf drop the NaNs of
 // 0 * inf, which makes a degenerate slab "no constraint".
@@ -1014,6 +1049,9 @@ __global__ void __launch_bounds__(PT_THREADS) k_sort_scatter_packed(const __grid
 #ifndef PT_DYN_STEPS
 #define PT_DYN_STEPS 8
 #endif
+#ifndef PT_DYN_QFMA
+#define PT_DYN_QFMA 1              // slab distances as fma(q, cell / d, (org - o) / d) straight from the grid coordinates
+#endif
 #ifndef PT_DYN_CULL
 #define PT_DYN_CULL 0
 #endif
@@ -1070,6 +1108,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
     bool has = false, walking = false;
     int slot = 0, idx = 0;
     V3 o = v3(0.f, 0.f, 0.f), d = o, inv = o;
+    QRay qr;
+    qr.ig = o; qr.cg = o;
     float t_min = 3.402823466e+38f;
     int hit = -1;
     Cand best;
@@ -1103,6 +1143,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                     o = v3(a.x, a.y, a.z);
                     d = v3(b.x, b.y, b.z);
                     inv = v3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
+                    qr = qray(o, inv, qorg, qcell);
                     t_min = 3.402823466e+38f;
                     hit = -1;
                     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
@@ -1136,12 +1177,21 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                 // 64-byte nodes, profiles/r2e_config5_k_isect_dyn_raw.csv)
                 const uint4* q = node < n_staged ? snodes_q + 2 * node : p.gb.qnodes + 2 * (size_t)node;
                 const uint4 A = q[0], B = q[1];
+#if PT_DYN_QFMA
+                float t0 = qbox_entry(fmaf(qlo(A.x), qr.ig.x, qr.cg.x), fmaf(qhi(A.y), qr.ig.x, qr.cg.x),
+                                      fmaf(qhi(A.x), qr.ig.y, qr.cg.y), fmaf(qlo(A.z), qr.ig.y, qr.cg.y),
+                                      fmaf(qlo(A.y), qr.ig.z, qr.cg.z), fmaf(qhi(A.z), qr.ig.z, qr.cg.z), t_lim);
+                float t1 = qbox_entry(fmaf(qlo(A.w), qr.ig.x, qr.cg.x), fmaf(qhi(B.x), qr.ig.x, qr.cg.x),
+                                      fmaf(qhi(A.w), qr.ig.y, qr.cg.y), fmaf(qlo(B.y), qr.ig.y, qr.cg.y),
+                                      fmaf(qlo(B.x), qr.ig.z, qr.cg.z), fmaf(qhi(B.y), qr.ig.z, qr.cg.z), t_lim);
+#else
                 float4 q0, q1, q2, q3;
                 q0.x = qdec_lo(A.x, qcell.x, qorg.x); q0.y = qdec_hi(A.x, qcell.y, qorg.y); q0.z = qdec_lo(A.y, qcell.z, qorg.z);
                 q1.x = qdec_hi(A.y, qcell.x, qorg.x); q1.y = qdec_lo(A.z, qcell.y, qorg.y); q1.z = qdec_hi(A.z, qcell.z, qorg.z);
                 q2.x = qdec_lo(A.w, qcell.x, qorg.x); q2.y = qdec_hi(A.w, qcell.y, qorg.y); q2.z = qdec_lo(B.x, qcell.z, qorg.z);
                 q3.x = qdec_hi(B.x, qcell.x, qorg.x); q3.y = qdec_lo(B.y, qcell.y, qorg.y); q3.z = qdec_hi(B.y, qcell.z, qorg.z);
                 float t0 = gbox_entry(q0, q1, o, inv, t_lim), t1 = gbox_entry(q2, q3, o, inv, t_lim);
+#endif
                 int r0 = (int)B.z, r1 = (int)B.w;
                 if (t1 >= 0.0f && (!(t0 >= 0.0f) || t1 < t0)) {            // near child first
                     const int r = r0; r0 = r1; r1 = r;
