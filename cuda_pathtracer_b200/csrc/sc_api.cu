@@ -71,6 +71,20 @@ int ensure_lookback(b200_sc_ctx* c, unsigned n)
 
 // A context is used from one stream at a time (launches sharing its workspace must be stream-ordered, b200_sc.h);
 // the wrap-around wipe is therefore enqueued on the launch stream, behind the launches that still use the old epochs.
+// ping-pong buffers of the naive scan
+int ensure_naive(b200_sc_ctx* c, unsigned n)
+{
+    const size_t want = ((size_t)n + 3) & ~(size_t)3;
+    if (c->scratch_cap >= want) return 0;
+    size_t cap0 = c->scratch_cap, cap1 = c->scratch_cap;
+    int r = ensure((void**)&c->scratch[0], &cap0, want, sizeof(int), false);
+    if (r) return r;
+    r = ensure((void**)&c->scratch[1], &cap1, want, sizeof(int), false);
+    if (r) return r;
+    c->scratch_cap = want;
+    return 0;
+}
+
 unsigned next_epoch(b200_sc_ctx* c, cudaStream_t s)
 {
     c->epoch += 1;
@@ -219,15 +233,8 @@ int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int va
         const int passes = ilog2ceil_u(un);
         const int* src = d_in;
         if (passes > 0) {
-            const size_t want = ((size_t)un + 3) & ~(size_t)3;
-            if (c->scratch_cap < want) {
-                size_t cap0 = c->scratch_cap, cap1 = c->scratch_cap;
-                int r = ensure((void**)&c->scratch[0], &cap0, want, sizeof(int), false);
-                if (r) return r;
-                r = ensure((void**)&c->scratch[1], &cap1, want, sizeof(int), false);
-                if (r) return r;
-                c->scratch_cap = want;
-            }
+            const int rr = ensure_naive(c, un);
+            if (rr) return rr;
             for (int d = 0; d < passes; ++d) {
                 int* dst = c->scratch[d & 1];
                 CK(launch_naive_pass(un, 1u << d, dst, src, s));
@@ -304,6 +311,11 @@ static int run_hostapi(int n, int* odata, const int* idata, int variant, bool co
     }
     if (!out_dev) d_out = c->stage[1];
 
+    // the timer spans the kernels only (the reference's convention, efficient.cu:166-169): the workspace a first call of this
+    // size needs is allocated before it starts
+    r = b200_sc_ctx_reserve(c, n);
+    if (!r && !compact && variant == B200_SCAN_NAIVE) r = ensure_naive(c, (unsigned)n);
+    if (r) return r;
     CK(cudaEventRecord(c->ev0, 0));
     if (compact) r = b200_compact_i32_dev(c, n, d_out, d_in, c->small, nullptr);
     else r = b200_scan_i32_dev(c, n, d_out, d_in, variant, nullptr, nullptr, nullptr);
