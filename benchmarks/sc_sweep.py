@@ -69,6 +69,7 @@ def main():
     ap.add_argument("--lg", type=int, nargs="+", default=[20, 22, 24, 26, 28])
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--ref", action="store_true")
+    ap.add_argument("--stream-max-lg", type=int, default=24, help="in-stream per-launch timing up to this size")
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
     peak, peak_kind = hbm_peak()
@@ -85,7 +86,8 @@ def main():
             out = torch.empty_like(a)
             cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
             row = {"n": n, "lg": lg, "npot": bool(delta)}
-            for name, variant in (("lookback", sc.LOOKBACK), ("efficient", sc.EFFICIENT), ("naive", sc.NAIVE)):
+            for name, variant in (("lookback", sc.LOOKBACK), ("tile", sc.LOOKBACK_TILE), ("ring", sc.LOOKBACK_RING),
+                                  ("efficient", sc.EFFICIENT), ("naive", sc.NAIVE)):
                 if variant == sc.NAIVE and lg > 26:
                     continue
                 med, best = time_op(lambda: ctx.scan(n, out, a, variant, stream=s), args.iters, flush)
@@ -97,13 +99,14 @@ def main():
             row["compact_ms"] = med
             row["compact_gbs"] = (4.0 * n + 4.0 * k) / med / 1e6
             row["compact_frac"] = row["compact_gbs"] / peak
-            if lg <= 24:
+            if lg <= args.stream_max_lg:
                 # in-stream: rotate over enough buffer pairs to exceed the 126 MB L2 (8 B per element per pair)
                 n_sets = max(2, (300 << 20) // (8 * n) + 1)
                 ins = [torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda") for _ in range(n_sets)]
                 outs = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(n_sets)]
                 launches = max(64, 2 * n_sets)
-                for name, variant in (("lookback", sc.LOOKBACK), ("efficient", sc.EFFICIENT)):
+                for name, variant in (("lookback", sc.LOOKBACK), ("tile", sc.LOOKBACK_TILE), ("ring", sc.LOOKBACK_RING),
+                                      ("efficient", sc.EFFICIENT)):
                     ms = time_stream(lambda k: ctx.scan(n, outs[k], ins[k], variant, stream=s), n_sets, launches)
                     row[name + "_stream_ms"] = ms
                     row[name + "_stream_frac"] = 8.0 * n / ms / 1e6 / peak

@@ -519,6 +519,81 @@ static void run_cfg(Env& e)
     run_scan<TH, VEC, 1, true, 100, 16>(e);
 }
 
+// ---- persistent TMA-ring scan (sct::k_scan_tma) ------------------------------------------------------
+template <int STAGE_INTS, int STAGES, int CWARPS, int DELAY, int NLB, int LBW>
+static void run_scan_tma(Env& e)
+{
+    auto k = sct::k_scan_tma<STAGE_INTS, STAGES, CWARPS, DELAY, NLB, LBW, 16>;
+    const size_t smem = sct::scan_tma_smem_bytes<STAGE_INTS, STAGES>();
+    const int threads = sct::scan_tma_threads<STAGE_INTS, CWARPS, NLB>();
+    const unsigned tiles = (unsigned)(((unsigned long long)e.n + STAGE_INTS - 1) / STAGE_INTS);
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    int occ = 0, sms = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, threads, smem));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    unsigned grid = (unsigned)(sms * occ);
+    if (grid > tiles) grid = tiles;
+    if (grid == 0) { printf("{\"op\": \"scan_tma\", \"error\": \"does not fit\"}\n"); return; }
+    CK(cudaMemset(e.d_out, 0xff, (size_t)e.n * 4));
+    unsigned* tk = nullptr;                                     // [2], [3]: the kernel's tile / done counters
+    CK(cudaMalloc(&tk, 16));
+    CK(cudaMemset(tk, 0, 16));
+    auto launch = [&] {
+        e.epoch += 1;
+        k<<<grid, threads, smem>>>(e.d_in, e.d_out, e.n, e.desc, tk, e.epoch, nullptr, e.d_small);
+    };
+    const float ms = median_ms(e, launch);
+    int total = 0, want_total = 0, last_in = 0;
+    CK(cudaMemcpy(&total, e.d_small, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&want_total, e.d_want_scan + (e.n - 1), 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&last_in, e.d_in + (e.n - 1), 4, cudaMemcpyDeviceToHost));
+    const bool ok = same(e, e.d_out, e.d_want_scan, e.n) && total == want_total + last_in;
+    printf("{\"op\": \"scan_tma\", \"stage_ints\": %d, \"stages\": %d, \"cwarps\": %d, \"delay\": %d, \"nlb\": %d, \"window\": %d, "
+           "\"regs\": %d, \"occ\": %d, \"grid\": %u, \"smem\": %zu, \"ms\": %.4f, \"gbs\": %.1f, \"ok\": %s}\n",
+           STAGE_INTS, STAGES, CWARPS, DELAY, NLB, 32 * LBW, fa.numRegs, occ, grid, smem, ms, 8.0 * e.n / ms / 1e6,
+           ok ? "true" : "false");
+    fflush(stdout);
+    CK(cudaFree(tk));
+}
+
+template <int STAGE_INTS, int STAGES, int CWARPS, int DELAY, int NLB, int LBW>
+static void run_compact_tma(Env& e)
+{
+    auto k = sct::k_compact_tma<STAGE_INTS, STAGES, CWARPS, DELAY, NLB, LBW, 16>;
+    const size_t smem = sct::compact_tma_smem_bytes<STAGE_INTS, STAGES>();
+    const int threads = sct::scan_tma_threads<STAGE_INTS, CWARPS, NLB>();
+    const unsigned tiles = (unsigned)(((unsigned long long)e.n + STAGE_INTS - 1) / STAGE_INTS);
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    int occ = 0, sms = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, threads, smem));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    unsigned grid = (unsigned)(sms * occ);
+    if (grid > tiles) grid = tiles;
+    if (grid == 0) { printf("{\"op\": \"compact_tma\", \"error\": \"does not fit\"}\n"); return; }
+    CK(cudaMemset(e.d_out, 0xff, (size_t)e.n * 4));
+    unsigned* tk = nullptr;
+    CK(cudaMalloc(&tk, 16));
+    CK(cudaMemset(tk, 0, 16));
+    auto launch = [&] {
+        e.epoch += 1;
+        k<<<grid, threads, smem>>>(e.d_flags, e.d_out, e.n, e.desc, tk, e.epoch, e.d_small);
+    };
+    const float ms = median_ms(e, launch);
+    int count = -1;
+    CK(cudaMemcpy(&count, e.d_small, 4, cudaMemcpyDeviceToHost));
+    const bool ok = count == e.want_count && same(e, e.d_out, e.d_want_compact, (unsigned)e.want_count);
+    printf("{\"op\": \"compact_tma\", \"stage_ints\": %d, \"stages\": %d, \"cwarps\": %d, \"delay\": %d, \"nlb\": %d, \"window\": %d, "
+           "\"regs\": %d, \"occ\": %d, \"grid\": %u, \"smem\": %zu, \"ms\": %.4f, \"gbs\": %.1f, \"ok\": %s}\n",
+           STAGE_INTS, STAGES, CWARPS, DELAY, NLB, 32 * LBW, fa.numRegs, occ, grid, smem, ms,
+           (4.0 * e.n + 4.0 * e.want_count) / ms / 1e6, ok ? "true" : "false");
+    fflush(stdout);
+    CK(cudaFree(tk));
+}
+
 int main(int argc, char** argv)
 {
     const int lg = argc > 1 ? atoi(argv[1]) : 28;
@@ -563,6 +638,24 @@ int main(int argc, char** argv)
         auto launch2 = [&] { CK(cudaMemcpyAsync(e.d_out, e.d_in, bytes, cudaMemcpyDeviceToDevice)); };
         const float ms2 = median_ms(e, launch2);
         printf("{\"op\": \"cudaMemcpyD2D\", \"ms\": %.4f, \"gbs\": %.1f}\n", ms2, 8.0 * e.n / ms2 / 1e6);
+    }
+    if (argc > 3 && std::string(argv[3]) == "tma") {          // benchmarks/sc_tune 28 10 tma
+        run_scan<128, 8, 1, false, 0, 16>(e);                 // the one-tile-per-CTA kernel the library uses
+        //           ints  stages warps delay nlb window/32
+        run_scan_tma<8192, 7, 8, 3, 4, 1>(e);
+        run_compact<256, 8, 1, false, 0, 16>(e);
+        run_compact_tma<8192, 7, 8, 3, 4, 1>(e);
+        run_compact_tma<8192, 7, 8, 3, 4, 2>(e);
+        run_compact_tma<8192, 7, 8, 3, 6, 1>(e);
+        run_compact_tma<8192, 7, 8, 2, 4, 1>(e);
+        run_compact_tma<8192, 7, 8, 4, 4, 1>(e);
+        run_compact_tma<8192, 6, 8, 2, 4, 1>(e);
+        run_compact_tma<8192, 6, 8, 3, 4, 1>(e);
+        run_compact_tma<8192, 7, 16, 3, 4, 1>(e);
+        run_compact_tma<8192, 7, 4, 3, 4, 1>(e);
+        run_compact_tma<10240, 5, 8, 2, 4, 1>(e);
+        run_compact_tma<4096, 13, 8, 6, 8, 1>(e);
+        return 0;
     }
     if (argc > 3 && std::string(argv[3]) == "persist") {      // benchmarks/sc_tune 28 10 persist
         run_scan<128, 8, 1, false, 0, 16>(e);                 // the one-tile-per-CTA kernels the library used so far

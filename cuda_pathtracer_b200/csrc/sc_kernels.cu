@@ -88,6 +88,37 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
     return cudaGetLastError();
 }
 
+// The persistent TMA-ring scan (sct::k_scan_tma): one CTA per SM, tuned on a B200 with benchmarks/sc_tune.cu
+// (profiles/r2z_sc_tune_tma_*.jsonl): 8192-int stages x 7 (224 KB of shared memory), 8 compute warps, pass B three tiles
+// behind pass A, 4 look-back warps.
+cudaError_t launch_scan_ring(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned* tickets,
+                             unsigned epoch, const int* d_seed, int* d_total, int num_sms, cudaStream_t s)
+{
+    constexpr int STAGE = SC_RING_STAGE_INTS, STAGES = SC_RING_STAGES, CW = SC_RING_WARPS, DELAY = SC_RING_DELAY, NLB = SC_RING_LB_WARPS;
+    auto k = sct::k_scan_tma<STAGE, STAGES, CW, DELAY, NLB, LBW, STRIDE>;
+    constexpr size_t smem = sct::scan_tma_smem_bytes<STAGE, STAGES>();
+    constexpr int threads = sct::scan_tma_threads<STAGE, CW, NLB>();
+    if (!aligned16(d_in) || !aligned16(d_out)) return cudaErrorMisalignedAddress;
+    static int per_sm_of[64] = {0};          // function attributes are per DEVICE (a process may drive several)
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (per_sm_of[dev] == 0) {
+        int a = 0;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k, threads, smem);
+        if (e != cudaSuccess) return e;
+        per_sm_of[dev] = a > 0 ? a : -1;
+    }
+    if (per_sm_of[dev] <= 0) return cudaErrorLaunchOutOfResources;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + STAGE - 1) / STAGE);
+    unsigned grid = (unsigned)(per_sm_of[dev] * num_sms);
+    if (grid > tiles) grid = tiles;
+    k<<<grid, threads, smem, s>>>(d_in, d_out, n, desc, tickets, epoch, d_seed, d_total);
+    return cudaGetLastError();
+}
+
+bool scan_ring_usable(const int* d_in, const int* d_out) { return aligned16(d_in) && aligned16(d_out); }
+
 cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
                                     unsigned* tickets, unsigned epoch, int* d_count, int num_sms, cudaStream_t s)
 {

@@ -36,6 +36,19 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
                                  unsigned* tickets, unsigned epoch, const int* d_seed, int* d_total,
                                  cudaStream_t s);
 
+// The same scan as a persistent TMA ring (sc_tmpl.cuh: k_scan_tma): bulk copies global -> shared -> global, the look-back
+// off the critical path.  Needs 16-byte aligned pointers (scan_ring_usable); tickets[2], tickets[3] are its tile / done
+// counters (zero between launches, shared with k_compact_ws: launches on one context are stream-ordered).  The library
+// takes it from SC_RING_MIN_N elements on (below that the one-tile-per-CTA kernel's shorter ramp wins).
+constexpr int SC_RING_STAGE_INTS = 8192;
+constexpr int SC_RING_STAGES = 7;
+constexpr int SC_RING_WARPS = 8;
+constexpr int SC_RING_DELAY = 3;
+constexpr int SC_RING_LB_WARPS = 4;
+constexpr unsigned SC_RING_MIN_N = 1u << 24;
+cudaError_t launch_scan_ring(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned* tickets,
+                             unsigned epoch, const int* d_seed, int* d_total, int num_sms, cudaStream_t s);
+bool scan_ring_usable(const int* d_in, const int* d_out);
 
 // Single-pass compaction: keep in[i] != 0, order preserving (B5 replacement).
 // (SC_COMPACT_WS: the persistent warp-specialised kernel, look-back off the critical path; tickets[2], tickets[3] are its

@@ -411,6 +411,441 @@ k_compact_ws(const int* __restrict__ in, int* __restrict__ out, unsigned n, unsi
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_scan_tma: the single-pass scan as a persistent TMA ring (one CTA per SM).
+//
+// In k_scan_lookback a tile's loads are issued when its CTA starts and the CTA then stands in the look-back before it can
+// store: the bytes in flight per SM follow the look-back latency.  Here the data never waits in registers:
+//   * ONE thread (the DMA thread) draws tiles from an atomic ticket and moves them with 1-D bulk copies
+//     (cp.async.bulk, SASS UBLKCP): global -> a ring of STAGES shared-memory buffers, completion on an mbarrier, and -- once
+//     a buffer holds the finished scan -- shared -> global as a bulk store.  Loads run STAGES - DELAY - 2 tiles ahead of
+//     the arithmetic whatever the look-back does;
+//   * CWARPS compute warps make two passes over a buffer: A (when the tile lands) sums it -- the per-warp totals go to the
+//     look-back warp through an mbarrier -- and B (DELAY tiles later, when the tile's exclusive prefix has come back)
+//     scans it in place; then fence.proxy.async + an mbarrier hand the buffer to the DMA thread;
+//   * NLB look-back warps (local tile i belongs to warp i % NLB) publish the aggregate, look back, publish the prefix.
+// No CTA-wide barrier after set-up: four mbarriers per stage (full -> req -> resp -> store) in a strict cycle, so the phase
+// parity of use u of a stage is u & 1 for all four.  Tiles are in ticket order and a CTA's tiles ascend, so the smallest
+// tile without a prefix only ever waits on published tiles: no deadlock whatever the residency.
+// Needs 16-byte aligned pointers (bulk copies); the ragged end of the array (n % 4 ints) is moved by the DMA thread itself.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ws_mbar_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(ws_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ws_bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(ws_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(ws_smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void ws_bulk_s2g(void* dst, const void* src, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(ws_smem_u32(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ws_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void ws_bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void ws_bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void ws_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+constexpr unsigned TMA_NO_TILE = 0xffffffffu;
+
+template <int STAGES, int CWARPS>
+struct TmaScanShared {
+    unsigned long long full_bar[STAGES], req_bar[STAGES], resp_bar[STAGES], store_bar[STAGES];
+    unsigned tile[STAGES];         // the tile in this stage (TMA_NO_TILE: no more tiles)
+    unsigned stop_at;              // local index of the first tile that does not exist (written before its full_bar arrive)
+    int resp[STAGES];              // exclusive prefix of that tile
+    int warp_sums[STAGES][CWARPS];
+};
+
+template <int STAGE_INTS, int STAGES>
+constexpr size_t scan_tma_smem_bytes() { return (size_t)STAGES * STAGE_INTS * sizeof(int); }
+
+template <int STAGE_INTS, int CWARPS, int NLB>
+constexpr int scan_tma_threads() { return (CWARPS + 1 + NLB) * 32; }
+
+template <int STAGE_INTS, int STAGES, int CWARPS, int DELAY, int NLB, int LBW, int STRIDE>
+__global__ void __launch_bounds__((CWARPS + 1 + NLB) * 32, 1)
+k_scan_tma(const int* in, int* out, unsigned n, unsigned long long* __restrict__ desc, unsigned* __restrict__ tickets,
+           unsigned epoch, const int* __restrict__ d_seed, int* __restrict__ d_total)
+{
+    static_assert(STAGE_INTS % (CWARPS * 128) == 0, "a stage is a whole number of 128-bit vectors per lane");
+    static_assert(DELAY + 2 <= STAGES && NLB <= STAGES, "ring too short");
+    constexpr int VPL = STAGE_INTS / (CWARPS * 128);           // 128-bit vectors per lane per tile
+    constexpr int WARP_INTS = 32 * VPL * 4;
+    extern __shared__ __align__(128) int ring[];                // [STAGES][STAGE_INTS]
+    __shared__ TmaScanShared<STAGES, CWARPS> sh;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + STAGE_INTS - 1) / STAGE_INTS);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            ws_mbar_init(&sh.full_bar[s], 1); ws_mbar_init(&sh.req_bar[s], CWARPS);
+            ws_mbar_init(&sh.resp_bar[s], 1); ws_mbar_init(&sh.store_bar[s], CWARPS);
+        }
+        sh.stop_at = 0xffffffffu;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == CWARPS) {                                       // ---- the DMA thread ----
+        if (lane != 0) return;
+        unsigned issued = 0, stored = 0;
+        bool more = true;
+        unsigned next_t = atomicAdd(&tickets[2], 1u);           // tickets[2]: next tile, tickets[3]: CTAs done (zero between launches)
+        for (;;) {
+            if (more && issued - stored < (unsigned)STAGES) {   // a free stage: the next tile's load
+                const unsigned t = next_t;
+                const int st = (int)(issued % STAGES);
+                if (t >= tiles) {
+                    sh.tile[st] = TMA_NO_TILE;
+                    sh.stop_at = issued;
+                    ws_mbar_arrive(&sh.full_bar[st]);
+                    more = false;
+                    continue;
+                }
+                next_t = atomicAdd(&tickets[2], 1u);            // (one ahead: its round trip hides behind the waits below)
+                sh.tile[st] = t;
+                const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+                const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+                int* buf = ring + (size_t)st * STAGE_INTS;
+                const unsigned whole = valid & ~3u;
+                for (unsigned k = whole; k < valid; ++k) buf[k] = in[base + k];
+                if (whole) {
+                    ws_mbar_expect_tx(&sh.full_bar[st], whole * 4u);
+                    ws_bulk_g2s(buf, in + base, whole * 4u, &sh.full_bar[st]);
+                } else {
+                    ws_mbar_arrive(&sh.full_bar[st]);
+                }
+                ++issued;
+                continue;
+            }
+            if (stored < issued) {                              // the oldest tile: store it once its scan is in the buffer
+                const int st = (int)(stored % STAGES);
+                ws_mbar_wait(&sh.store_bar[st], (stored / STAGES) & 1u);
+                const unsigned t = sh.tile[st];
+                const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+                const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+                const int* buf = ring + (size_t)st * STAGE_INTS;
+                const unsigned whole = valid & ~3u;
+                if (whole) ws_bulk_s2g(out + base, buf, whole * 4u);
+                ws_bulk_commit();
+                for (unsigned k = whole; k < valid; ++k) out[base + k] = buf[k];
+                ws_bulk_wait_read0();                           // the buffer may be overwritten
+                ++stored;
+                continue;
+            }
+            break;
+        }
+        ws_bulk_wait0();
+        // the last CTA to get here (every CTA has drawn its last ticket by now) re-arms the counters for the next launch
+        if (atomicAdd(&tickets[3], 1u) == gridDim.x - 1) { tickets[2] = 0u; tickets[3] = 0u; }
+        return;
+    }
+
+    if (warp > CWARPS) {                                        // ---- the look-back warps ----
+        const int seed = d_seed ? __ldg(d_seed) : 0;
+        for (unsigned i = (unsigned)(warp - CWARPS - 1);; i += NLB) {
+            const int st = (int)(i % STAGES);
+            ws_mbar_wait(&sh.req_bar[st], (i / STAGES) & 1u);
+            if (i >= *(volatile unsigned*)&sh.stop_at) break;
+            const unsigned t = sh.tile[st];
+            int aggregate = 0;
+#pragma unroll
+            for (int w = 0; w < CWARPS; ++w) aggregate += sh.warp_sums[st][w];
+            const int e = lb_exclusive_prefix_cfg<LBW, LB_DEFAULT_BACKOFF_NS, STRIDE>(desc, t, epoch, aggregate, seed, lane);
+            __syncwarp();
+            if (lane == 0) {
+                if (d_total && t == tiles - 1) *d_total = e + aggregate;
+                sh.resp[st] = e;
+                ws_mbar_arrive(&sh.resp_bar[st]);
+            }
+        }
+        return;
+    }
+
+    // ---- the compute warps ----
+    unsigned done_at = 0xffffffffu;
+    for (unsigned i = 0;; ++i) {
+        if (i < done_at) {                                      // pass A over local tile i: its sum
+            const int st = (int)(i % STAGES);
+            ws_mbar_wait(&sh.full_bar[st], (i / STAGES) & 1u);
+            const unsigned t = sh.tile[st];
+            if (t == TMA_NO_TILE) {
+                done_at = i;
+                if (lane == 0) ws_mbar_arrive(&sh.req_bar[st]);  // the look-back warp of local tile i sees stop_at and leaves
+            } else {
+                const int4* p = reinterpret_cast<const int4*>(ring + (size_t)st * STAGE_INTS + warp * WARP_INTS) + lane;
+                const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+                const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+                int s = 0;
+                if (valid == (unsigned)STAGE_INTS) {
+#pragma unroll
+                    for (int j = 0; j < VPL; ++j) { const int4 v = p[j * 32]; s += (v.x + v.y) + (v.z + v.w); }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < VPL; ++j) {
+                        const int4 v = p[j * 32];
+                        const unsigned e = (unsigned)(warp * WARP_INTS + (j * 32 + lane) * 4);
+                        s += (e + 0 < valid ? v.x : 0) + (e + 1 < valid ? v.y : 0) + (e + 2 < valid ? v.z : 0) + (e + 3 < valid ? v.w : 0);
+                    }
+                }
+                s = warp_sum(s);
+                if (lane == 0) {
+                    sh.warp_sums[st][warp] = s;
+                    ws_mbar_arrive(&sh.req_bar[st]);
+                }
+            }
+        }
+        if (i >= (unsigned)DELAY) {                             // pass B over local tile i - DELAY: the scan, in place
+            const unsigned k = i - DELAY;
+            if (k >= done_at) break;
+            const int st = (int)(k % STAGES);
+            ws_mbar_wait(&sh.resp_bar[st], (k / STAGES) & 1u);
+            int carry = sh.resp[st];
+#pragma unroll
+            for (int w = 0; w < CWARPS; ++w) if (w < warp) carry += sh.warp_sums[st][w];
+            int4* p = reinterpret_cast<int4*>(ring + (size_t)st * STAGE_INTS + warp * WARP_INTS) + lane;
+            const unsigned t = sh.tile[st];
+            const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+            const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+            int4 v[VPL];
+            int s[VPL];
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) v[j] = p[j * 32];
+            if (valid != (unsigned)STAGE_INTS) {
+#pragma unroll
+                for (int j = 0; j < VPL; ++j) {
+                    const unsigned e = (unsigned)(warp * WARP_INTS + (j * 32 + lane) * 4);
+                    if (e + 0 >= valid) v[j].x = 0;
+                    if (e + 1 >= valid) v[j].y = 0;
+                    if (e + 2 >= valid) v[j].z = 0;
+                    if (e + 3 >= valid) v[j].w = 0;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) s[j] = (v[j].x + v[j].y) + (v[j].z + v[j].w);
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) {
+                const int inc = warp_inclusive_scan(s[j], lane);
+                p[j * 32] = scan_vec(v[j], carry + inc - s[j]);
+                carry += __shfl_sync(FULL_MASK, inc, 31);
+            }
+            ws_fence_async_smem();                              // generic-proxy writes -> visible to the bulk store
+            __syncwarp();
+            if (lane == 0) ws_mbar_arrive(&sh.store_bar[st]);
+        }
+    }
+    if (NLB > 1) {      // the other look-back warps wait for local tiles done_at + 1 ..: wake them too.  Every compute warp must
+                        // have made its pass-A arrivals first (an early one would fall into a phase that is still open)
+        asm volatile("bar.sync 1, %0;" ::"n"(CWARPS * 32) : "memory");
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 1; q < NLB; ++q) ws_mbar_arrive(&sh.req_bar[(done_at + q) % STAGES]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_compact_tma: stream compaction on the same ring (see k_scan_tma).  Pass A counts the non-zero elements of a stage, pass B
+// -- once the tile's exclusive prefix `base` is back -- packs the survivors IN PLACE: every compute warp first takes its part of
+// the tile into registers, one named barrier, then the survivors go to packed[mis + rank], mis = (out + base) mod 16 bytes, so
+// that the 16-byte aligned part of the run out[base .. base + kept) is also 16-byte aligned in shared memory and leaves as ONE
+// bulk store; the up to 3 + 3 ints before and after it are written by the DMA thread.  A stage is STAGE_INTS + 4 ints.
+// `in` must be 16-byte aligned (bulk loads); `out` may be anything.
+// ------------------------------------------------------------------------------------------------
+template <int STAGE_INTS, int STAGES>
+constexpr size_t compact_tma_smem_bytes() { return (size_t)STAGES * (STAGE_INTS + 4) * sizeof(int); }
+
+template <int STAGE_INTS, int STAGES, int CWARPS, int DELAY, int NLB, int LBW, int STRIDE>
+__global__ void __launch_bounds__((CWARPS + 1 + NLB) * 32, 1)
+k_compact_tma(const int* in, int* out, unsigned n, unsigned long long* __restrict__ desc, unsigned* __restrict__ tickets,
+              unsigned epoch, int* __restrict__ d_count)
+{
+    static_assert(STAGE_INTS % (CWARPS * 128) == 0, "a stage is a whole number of 128-bit vectors per lane");
+    static_assert(DELAY + 2 <= STAGES && NLB <= STAGES, "ring too short");
+    constexpr int VPL = STAGE_INTS / (CWARPS * 128);
+    constexpr int WARP_INTS = 32 * VPL * 4;
+    constexpr int PITCH = STAGE_INTS + 4;
+    extern __shared__ __align__(128) int ring[];                // [STAGES][PITCH]
+    __shared__ TmaScanShared<STAGES, CWARPS> sh;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + STAGE_INTS - 1) / STAGE_INTS);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            ws_mbar_init(&sh.full_bar[s], 1); ws_mbar_init(&sh.req_bar[s], CWARPS);
+            ws_mbar_init(&sh.resp_bar[s], 1); ws_mbar_init(&sh.store_bar[s], CWARPS);
+        }
+        sh.stop_at = 0xffffffffu;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == CWARPS) {                                       // ---- the DMA thread ----
+        if (lane != 0) return;
+        unsigned issued = 0, stored = 0;
+        bool more = true;
+        unsigned next_t = atomicAdd(&tickets[2], 1u);
+        for (;;) {
+            if (more && issued - stored < (unsigned)STAGES) {
+                const unsigned t = next_t;
+                const int st = (int)(issued % STAGES);
+                if (t >= tiles) {
+                    sh.tile[st] = TMA_NO_TILE;
+                    sh.stop_at = issued;
+                    ws_mbar_arrive(&sh.full_bar[st]);
+                    more = false;
+                    continue;
+                }
+                next_t = atomicAdd(&tickets[2], 1u);
+                sh.tile[st] = t;
+                const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+                const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+                int* buf = ring + (size_t)st * PITCH;
+                const unsigned whole = valid & ~3u;
+                for (unsigned k = whole; k < valid; ++k) buf[k] = in[base + k];
+                if (whole) {
+                    ws_mbar_expect_tx(&sh.full_bar[st], whole * 4u);
+                    ws_bulk_g2s(buf, in + base, whole * 4u, &sh.full_bar[st]);
+                } else {
+                    ws_mbar_arrive(&sh.full_bar[st]);
+                }
+                ++issued;
+                continue;
+            }
+            if (stored < issued) {                              // the oldest tile: its packed run goes out
+                const int st = (int)(stored % STAGES);
+                ws_mbar_wait(&sh.store_bar[st], (stored / STAGES) & 1u);
+                int kept = 0;
+#pragma unroll
+                for (int w = 0; w < CWARPS; ++w) kept += sh.warp_sums[st][w];
+                int* dst = out + sh.resp[st];
+                const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
+                int head = mis ? 4 - mis : 0;
+                if (head > kept) head = kept;
+                const int* packed = ring + (size_t)st * PITCH + mis;
+                const int body4 = (kept - head) >> 2;
+                if (body4) ws_bulk_s2g(dst + head, packed + head, (unsigned)body4 * 16u);
+                ws_bulk_commit();
+                for (int k = 0; k < head; ++k) dst[k] = packed[k];
+                for (int k = head + 4 * body4; k < kept; ++k) dst[k] = packed[k];
+                ws_bulk_wait_read0();
+                ++stored;
+                continue;
+            }
+            break;
+        }
+        ws_bulk_wait0();
+        if (atomicAdd(&tickets[3], 1u) == gridDim.x - 1) { tickets[2] = 0u; tickets[3] = 0u; }
+        return;
+    }
+
+    if (warp > CWARPS) {                                        // ---- the look-back warps ----
+        for (unsigned i = (unsigned)(warp - CWARPS - 1);; i += NLB) {
+            const int st = (int)(i % STAGES);
+            ws_mbar_wait(&sh.req_bar[st], (i / STAGES) & 1u);
+            if (i >= *(volatile unsigned*)&sh.stop_at) break;
+            const unsigned t = sh.tile[st];
+            int kept = 0;
+#pragma unroll
+            for (int w = 0; w < CWARPS; ++w) kept += sh.warp_sums[st][w];
+            const int e = lb_exclusive_prefix_cfg<LBW, LB_DEFAULT_BACKOFF_NS, STRIDE>(desc, t, epoch, kept, 0, lane);
+            __syncwarp();
+            if (lane == 0) {
+                if (t == tiles - 1) *d_count = e + kept;
+                sh.resp[st] = e;
+                ws_mbar_arrive(&sh.resp_bar[st]);
+            }
+        }
+        return;
+    }
+
+    // ---- the compute warps ----
+    unsigned done_at = 0xffffffffu;
+    for (unsigned i = 0;; ++i) {
+        if (i < done_at) {                                      // pass A over local tile i: how many it keeps
+            const int st = (int)(i % STAGES);
+            ws_mbar_wait(&sh.full_bar[st], (i / STAGES) & 1u);
+            const unsigned t = sh.tile[st];
+            if (t == TMA_NO_TILE) {
+                done_at = i;
+                if (lane == 0) ws_mbar_arrive(&sh.req_bar[st]);
+            } else {
+                const int4* p = reinterpret_cast<const int4*>(ring + (size_t)st * PITCH + warp * WARP_INTS) + lane;
+                const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+                const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+                int s = 0;
+                if (valid == (unsigned)STAGE_INTS) {
+#pragma unroll
+                    for (int j = 0; j < VPL; ++j) { const int4 v = p[j * 32]; s += (v.x != 0) + (v.y != 0) + (v.z != 0) + (v.w != 0); }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < VPL; ++j) {
+                        const int4 v = p[j * 32];
+                        const unsigned e = (unsigned)(warp * WARP_INTS + (j * 32 + lane) * 4);
+                        s += (e + 0 < valid && v.x != 0) + (e + 1 < valid && v.y != 0) + (e + 2 < valid && v.z != 0) + (e + 3 < valid && v.w != 0);
+                    }
+                }
+                s = warp_sum(s);
+                if (lane == 0) {
+                    sh.warp_sums[st][warp] = s;
+                    ws_mbar_arrive(&sh.req_bar[st]);
+                }
+            }
+        }
+        if (i >= (unsigned)DELAY) {                             // pass B over local tile i - DELAY: pack in place
+            const unsigned k = i - DELAY;
+            if (k >= done_at) break;
+            const int st = (int)(k % STAGES);
+            ws_mbar_wait(&sh.resp_bar[st], (k / STAGES) & 1u);
+            const int mis = (int)((reinterpret_cast<uintptr_t>(out + sh.resp[st]) >> 2) & 3u);
+            int carry = mis;
+#pragma unroll
+            for (int w = 0; w < CWARPS; ++w) if (w < warp) carry += sh.warp_sums[st][w];
+            int* stage = ring + (size_t)st * PITCH;
+            const int4* p = reinterpret_cast<const int4*>(stage + warp * WARP_INTS) + lane;
+            const unsigned t = sh.tile[st];
+            const unsigned long long base = (unsigned long long)t * STAGE_INTS;
+            const unsigned valid = (unsigned long long)n - base < (unsigned long long)STAGE_INTS ? (unsigned)(n - base) : (unsigned)STAGE_INTS;
+            int4 v[VPL];
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) v[j] = p[j * 32];
+            if (valid != (unsigned)STAGE_INTS) {
+#pragma unroll
+                for (int j = 0; j < VPL; ++j) {
+                    const unsigned e = (unsigned)(warp * WARP_INTS + (j * 32 + lane) * 4);
+                    if (e + 0 >= valid) v[j].x = 0;
+                    if (e + 1 >= valid) v[j].y = 0;
+                    if (e + 2 >= valid) v[j].z = 0;
+                    if (e + 3 >= valid) v[j].w = 0;
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(CWARPS * 32) : "memory");   // the whole tile is in registers: overwrite it
+#pragma unroll
+            for (int j = 0; j < VPL; ++j) {
+                const int c = (v[j].x != 0) + (v[j].y != 0) + (v[j].z != 0) + (v[j].w != 0);
+                const int inc = warp_inclusive_scan(c, lane);
+                int q = carry + inc - c;
+                if (v[j].x != 0) stage[q++] = v[j].x;
+                if (v[j].y != 0) stage[q++] = v[j].y;
+                if (v[j].z != 0) stage[q++] = v[j].z;
+                if (v[j].w != 0) stage[q++] = v[j].w;
+                carry += __shfl_sync(FULL_MASK, inc, 31);
+            }
+            ws_fence_async_smem();
+            __syncwarp();
+            if (lane == 0) ws_mbar_arrive(&sh.store_bar[st]);
+        }
+    }
+    if (NLB > 1) {
+        asm volatile("bar.sync 1, %0;" ::"n"(CWARPS * 32) : "memory");
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 1; q < NLB; ++q) ws_mbar_arrive(&sh.req_bar[(done_at + q) % STAGES]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Work-efficient three-phase scan: k_reduce_tiles (up-sweep), recursion on the tile sums,
 // k_downsweep (per-tile scan seeded with the scanned tile sum).  12 B/element.
 // ------------------------------------------------------------------------------------------------

@@ -37,7 +37,11 @@ enum {
     B200_SCAN_LOOKBACK = 0,  /* single pass, decoupled look-back: 8 B/element (Thrust::scan name)     */
     B200_SCAN_EFFICIENT = 1, /* work-efficient reduce / scan-sums / down-sweep: 12 B/element
                                 (Efficient::scan name; the reference's is efficient.cu:138-176)       */
-    B200_SCAN_NAIVE = 2      /* ilog2ceil(n) Hillis-Steele passes (Naive::scan, naive.cu:36-66)       */
+    B200_SCAN_NAIVE = 2,     /* ilog2ceil(n) Hillis-Steele passes (Naive::scan, naive.cu:36-66)       */
+    /* B200_SCAN_LOOKBACK picks between two kernels by size and pointer alignment; these two name them (tests, benchmarks): */
+    B200_SCAN_LOOKBACK_TILE = 3, /* one tile per CTA, loads and stores from registers                                    */
+    B200_SCAN_LOOKBACK_RING = 4  /* persistent, one CTA per SM: TMA bulk copies through a shared-memory ring, look-back
+                                    off the critical path; device pointers must be 16-byte aligned (B200_E_BADARG)      */
 };
 
 /* error codes outside the cudaError_t range */

@@ -36,7 +36,7 @@ def np_exclusive_scan(a):
     return out.astype(np.uint64).astype(np.uint32).view(np.int32)
 
 
-VARIANTS = ["Naive", "Efficient", "Thrust"]
+VARIANTS = ["Naive", "Efficient", "Thrust", "SinglePassTile", "SinglePassRing"]
 SIZES = [1, 2, 3, 4, 5, 31, 32, 33, 63, 64, 65, 255, 256, 257, 4095, 4096, 4097, 8191, 12289,
          (1 << 16) - 3, 1 << 16, (1 << 20) - 3, 1 << 20]
 
@@ -110,6 +110,10 @@ def test_unaligned_pointers(sc, oracle):
     dout = torch.zeros(1 << 14, dtype=torch.int32, device="cuda")
     for v in VARIANTS:
         dout.zero_()
+        if v == "SinglePassRing":                              # bulk copies need 16-byte alignment: asked for by name, it refuses
+            with pytest.raises(Exception, match="10001|argument"):
+                getattr(sc, v).scan(9000, dout[3:], d[1:])
+            continue
         getattr(sc, v).scan(9000, dout[3:], d[1:])             # device pointers, both misaligned
         torch.cuda.synchronize()
         assert np.array_equal(dout[3:9003].cpu().numpy(), oracle.scan(base[1:9001]))
@@ -128,7 +132,7 @@ def test_device_ctx_seed_total_and_reduce(sc):
     seed = torch.tensor([123456], dtype=torch.int32, device="cuda")
     total = torch.zeros(1, dtype=torch.int32, device="cuda")
     want = np_exclusive_scan(a.cpu().numpy())
-    for variant in (sc.LOOKBACK, sc.EFFICIENT, sc.NAIVE):
+    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.EFFICIENT, sc.NAIVE):
         out.zero_(); total.zero_()
         ctx.scan(n, out, a, variant, d_seed=seed, d_total=total)
         torch.cuda.synchronize()
@@ -152,6 +156,9 @@ def test_repeated_launches_reuse_workspace(sc):
         out = torch.empty_like(a)
         cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
         ctx.scan(n, out, a)
+        ring = torch.empty_like(a)
+        ctx.scan(n, ring, a, sc.LOOKBACK_RING)                 # shares the ticket counters with the compaction kernel
+        assert torch.equal(ring, out)
         ctx.compact(n, out, a, cnt)
         torch.cuda.synchronize()
         h = a.cpu().numpy()
@@ -175,7 +182,7 @@ def test_full_size_2p28(sc, delta):
     ctx = sc.Context()
     want = torch.cumsum(a, 0, dtype=torch.int64)
     want = (want - a).to(torch.int32)                 # exclusive, wraps like int32
-    for variant in (sc.LOOKBACK, sc.EFFICIENT):
+    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.EFFICIENT):
         out.zero_()
         ctx.scan(n, out, a, variant)
         torch.cuda.synchronize()
@@ -235,12 +242,35 @@ def test_scan_is_linear_and_shift_consistent(sc):
     y = torch.randint(-2**31, 2**31 - 1, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
     ctx = sc.Context()
     sx, sy, sxy, sh = (torch.empty_like(x) for _ in range(4))
-    for variant in (sc.LOOKBACK, sc.EFFICIENT):
+    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.EFFICIENT):
         ctx.scan(n, sx, x, variant)
         ctx.scan(n, sy, y, variant)
         ctx.scan(n, sxy, x + y, variant)
-        ctx.scan(n - 5, sh, x[5:].contiguous(), variant)
+        ctx.scan(n - 5, sh, x[5:].clone(), variant)     # (a copy: 16-byte aligned, which the ring kernel asks for)
         torch.cuda.synchronize()
         assert torch.equal(sxy, sx + sy)
         assert torch.equal(sh[: n - 5], sx[5:] - sx[5])
+    ctx.close()
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 5, 8191, 8192, 8193, 8195, 7 * 8192, 7 * 8192 + 1, 148 * 8192 - 3, 148 * 8192 * 3 + 2,
+                               (1 << 23) - 3, 1 << 23, (1 << 24) + 1])
+def test_ring_scan_ragged_sizes(sc, n):
+    """the TMA-ring kernel by name at sizes around its stage (8192 ints), ring (7 stages) and grid (148 CTAs) boundaries,
+    with a seed and a total, against the closed form; LOOKBACK itself takes this kernel from 2^24 ints on"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(n)
+    a = torch.randint(-50, 50, (n,), dtype=torch.int32, device="cuda", generator=g)
+    out = torch.full((n + 8,), -7, dtype=torch.int32, device="cuda")
+    seed = torch.tensor([-99], dtype=torch.int32, device="cuda")
+    total = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ctx = sc.Context()
+    want = (torch.cumsum(a, 0, dtype=torch.int64) - a - 99).to(torch.int32)
+    for variant in (sc.LOOKBACK_RING, sc.LOOKBACK):
+        out.fill_(-7); total.zero_()
+        ctx.scan(n, out, a, variant, d_seed=seed, d_total=total)
+        torch.cuda.synchronize()
+        assert torch.equal(out[:n], want)
+        assert bool((out[n:] == -7).all())                      # nothing written past n
+        assert int(total.item()) == int(np.int64(a.sum(dtype=torch.int64).item()) - 99)
     ctx.close()
