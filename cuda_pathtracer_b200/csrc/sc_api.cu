@@ -31,6 +31,7 @@ struct b200_sc_ctx {
     int* small = nullptr;                 // 4 ints: count / total slots for host-pointer calls
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int last_launches = 0;
+    unsigned ring_min_n = SC_RING_MIN_N;  // from how many elements on the TMA-ring kernels run (b200_sc_ctx_set_ring_min_n)
 };
 
 namespace {
@@ -222,7 +223,7 @@ int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int va
     case B200_SCAN_LOOKBACK_RING: {
         const bool ring_ok = scan_ring_usable(d_in, d_out);
         if (variant == B200_SCAN_LOOKBACK_RING && !ring_ok) return B200_E_BADARG;
-        const bool ring = variant == B200_SCAN_LOOKBACK_RING || (variant == B200_SCAN_LOOKBACK && ring_ok && un >= SC_RING_MIN_N);
+        const bool ring = variant == B200_SCAN_LOOKBACK_RING || (variant == B200_SCAN_LOOKBACK && ring_ok && un >= c->ring_min_n);
         int r = ensure_lookback(c, un);
         if (r) return r;
         if (ring) CK(launch_scan_ring(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
@@ -265,8 +266,18 @@ int b200_compact_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int
     if (n == 0) { CK(cudaMemsetAsync(d_count, 0, sizeof(int), s)); return 0; }
     int r = ensure_lookback(c, (unsigned)n);
     if (r) return r;
-    CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
+    if (compact_ring_usable(d_in) && (unsigned)n >= c->ring_min_n)
+        CK(launch_compact_ring(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
+    else
+        CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
     c->last_launches = 1;
+    return 0;
+}
+
+int b200_sc_ctx_set_ring_min_n(b200_sc_ctx* c, int min_n)
+{
+    if (!c || min_n < 0) return B200_E_BADARG;
+    c->ring_min_n = min_n == 0 ? SC_RING_MIN_N : (unsigned)min_n;
     return 0;
 }
 

@@ -119,6 +119,36 @@ cudaError_t launch_scan_ring(const int* d_in, int* d_out, unsigned n, unsigned l
 
 bool scan_ring_usable(const int* d_in, const int* d_out) { return aligned16(d_in) && aligned16(d_out); }
 
+// The compaction on the TMA ring (sct::k_compact_tma), same shape as the scan's: 0.871 of the HBM peak at 2^28 against 0.756
+// for k_compact_ws (profiles/r2z_sc_tune_tma_compact_2p28.jsonl).
+cudaError_t launch_compact_ring(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned* tickets,
+                                unsigned epoch, int* d_count, int num_sms, cudaStream_t s)
+{
+    constexpr int STAGE = SC_RING_STAGE_INTS, STAGES = SC_RING_STAGES, CW = SC_RING_WARPS, DELAY = SC_RING_DELAY, NLB = SC_RING_LB_WARPS;
+    auto k = sct::k_compact_tma<STAGE, STAGES, CW, DELAY, NLB, LBW, STRIDE>;
+    constexpr size_t smem = sct::compact_tma_smem_bytes<STAGE, STAGES>();
+    constexpr int threads = sct::scan_tma_threads<STAGE, CW, NLB>();
+    if (!aligned16(d_in)) return cudaErrorMisalignedAddress;
+    static int per_sm_of[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (per_sm_of[dev] == 0) {
+        int a = 0;
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k, threads, smem);
+        if (e != cudaSuccess) return e;
+        per_sm_of[dev] = a > 0 ? a : -1;
+    }
+    if (per_sm_of[dev] <= 0) return cudaErrorLaunchOutOfResources;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + STAGE - 1) / STAGE);
+    unsigned grid = (unsigned)(per_sm_of[dev] * num_sms);
+    if (grid > tiles) grid = tiles;
+    k<<<grid, threads, smem, s>>>(d_in, d_out, n, desc, tickets, epoch, d_count);
+    return cudaGetLastError();
+}
+
+bool compact_ring_usable(const int* d_in) { return aligned16(d_in); }
+
 cudaError_t launch_compact_lookback(const int* d_in, int* d_out, unsigned n, unsigned long long* desc,
                                     unsigned* tickets, unsigned epoch, int* d_count, int num_sms, cudaStream_t s)
 {

@@ -49,6 +49,10 @@ constexpr unsigned SC_RING_MIN_N = 1u << 24;
 cudaError_t launch_scan_ring(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned* tickets,
                              unsigned epoch, const int* d_seed, int* d_total, int num_sms, cudaStream_t s);
 bool scan_ring_usable(const int* d_in, const int* d_out);
+// ... and the compaction on the same ring (k_compact_tma); only d_in must be 16-byte aligned
+cudaError_t launch_compact_ring(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned* tickets,
+                                unsigned epoch, int* d_count, int num_sms, cudaStream_t s);
+bool compact_ring_usable(const int* d_in);
 
 // Single-pass compaction: keep in[i] != 0, order preserving (B5 replacement).
 // (SC_COMPACT_WS: the persistent warp-specialised kernel, look-back off the critical path; tickets[2], tickets[3] are its

@@ -33,6 +33,7 @@ def _lib():
                                             ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_sc_last_launches.argtypes = [ctypes.c_void_p]
         lib.b200_sc_ctx_reserve.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.b200_sc_ctx_set_ring_min_n.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.b200_scan_i32_noalloc.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         lib.b200_error_string.argtypes = [ctypes.c_int]
         lib.b200_error_string.restype = ctypes.c_char_p
@@ -137,6 +138,10 @@ class Context:
 
     def reserve(self, n):
         check(_lib().b200_sc_ctx_reserve(self._h, int(n)))
+
+    def set_ring_min_n(self, min_n):
+        """from how many elements on the TMA-ring kernels run (0: library default, 1: always, 2**31 - 1: never)"""
+        check(_lib().b200_sc_ctx_set_ring_min_n(self._h, int(min_n)))
 
     def last_launches(self):
         return _lib().b200_sc_last_launches(self._h)

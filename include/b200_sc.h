@@ -74,6 +74,12 @@ int b200_sc_ctx_destroy(b200_sc_ctx* ctx);
  * calls with up to n elements allocate nothing (the workspace otherwise grows on first use). */
 int b200_sc_ctx_reserve(b200_sc_ctx* ctx, int n);
 
+/* Tuning knob: from how many elements on b200_scan_i32_dev(.., B200_SCAN_LOOKBACK, ..) and b200_compact_i32_dev run their
+ * persistent TMA-ring kernels (16-byte aligned device input -- and, for the scan, output -- required; otherwise, and below
+ * the limit, the register-tile kernels run).  0 restores the library default (2^24); 1 = whenever the alignment allows;
+ * INT_MAX = never.  The result is the same bit for bit whichever kernel runs. */
+int b200_sc_ctx_set_ring_min_n(b200_sc_ctx* ctx, int min_n);
+
 /* All pointers are device pointers; work is enqueued on `stream` (a cudaStream_t) and NOT
  * synchronised.  d_seed (may be NULL) is one device int added to every output element: the
  * exclusive prefix of the totals of the shards that precede this one (multi-GPU scan).

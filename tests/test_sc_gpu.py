@@ -274,3 +274,55 @@ def test_ring_scan_ragged_sizes(sc, n):
         assert bool((out[n:] == -7).all())                      # nothing written past n
         assert int(total.item()) == int(np.int64(a.sum(dtype=torch.int64).item()) - 99)
     ctx.close()
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 5, 8191, 8192, 8193, 8195, 7 * 8192 + 1, 148 * 8192 - 3, 148 * 8192 * 3 + 2, (1 << 24) + 1])
+@pytest.mark.parametrize("keep_mod", [1, 2, 4, 1000, 0])
+def test_ring_compact_ragged_sizes(sc, n, keep_mod):
+    """the TMA-ring compaction (forced with set_ring_min_n(1)) at sizes around its stage / ring / grid boundaries, at
+    several densities (keep_mod 1: everything kept, 0: nothing kept), into 16-byte aligned and misaligned outputs, against
+    x[x != 0]; the register-tile kernel (ring off) must give the same"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(n + keep_mod)
+    a = torch.randint(1, 1 << 30, (n,), dtype=torch.int32, device="cuda", generator=g)
+    if keep_mod == 0:
+        a.zero_()
+    elif keep_mod > 1:
+        a = torch.where(a % keep_mod == 0, a, torch.zeros_like(a)) if keep_mod == 1000 else a % keep_mod
+    want = a[a != 0]
+    k = want.numel()
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ctx = sc.Context()
+    for ring_min in (1, 2**31 - 1):
+        ctx.set_ring_min_n(ring_min)
+        for off in (0, 1, 2, 3):
+            out = torch.full((n + 12,), -7, dtype=torch.int32, device="cuda")
+            cnt.fill_(-1)
+            ctx.compact(n, out[off:], a, cnt)
+            torch.cuda.synchronize()
+            assert int(cnt.item()) == k
+            assert torch.equal(out[off:off + k], want)
+            assert bool((out[:off] == -7).all()) and bool((out[off + k:] == -7).all())   # nothing outside the run
+    ctx.close()
+
+
+def test_ring_kernels_interleaved_on_one_context(sc):
+    """ring scan, ring compact and the register-tile kernels back to back on one context (shared descriptors, epochs and
+    ticket counters), sizes that leave CTAs idle and sizes that do not"""
+    import torch
+    ctx = sc.Context()
+    ctx.set_ring_min_n(1)
+    rng = np.random.RandomState(3)
+    for it in range(30):
+        n = int(rng.choice([5, 8192 * 3 + 1, 8192 * 148, 8192 * 400 + 77, 1 << 22]))
+        a = torch.randint(0, 4, (n,), dtype=torch.int32, device="cuda")
+        out, out2 = torch.empty_like(a), torch.empty_like(a)
+        cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ctx.scan(n, out, a)
+        ctx.compact(n, out2, a, cnt)
+        ctx.scan(n, out, a, sc.LOOKBACK_TILE)
+        torch.cuda.synchronize()
+        assert torch.equal(out, (torch.cumsum(a, 0, dtype=torch.int64) - a).to(torch.int32))
+        keep = a[a != 0]
+        assert int(cnt.item()) == keep.numel() and torch.equal(out2[: keep.numel()], keep)
+    ctx.close()
