@@ -43,7 +43,7 @@ def time_op(fn, iters, flush):
     return times[len(times) // 2], times[0]
 
 
-def time_stream(fn_of_k, n_sets, launches):
+def time_stream(fn_of_k, n_sets, launches, blocker=None):
     """per-launch time of `launches` back-to-back launches cycling through n_sets distinct (input, output) pairs whose
     total size exceeds the L2 (so every launch reads cold data), one CUDA-event pair around the whole train: what a
     launch costs INSIDE a stream of work (the single-launch numbers above it carry ~10 us of launch + event latency)"""
@@ -54,6 +54,9 @@ def time_stream(fn_of_k, n_sets, launches):
     best = None
     for _ in range(5):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if blocker is not None:                # ~2 ms of GPU work ahead of the train, so that the host (a ctypes call per
+            for _ in range(20):                # launch: ~6 us) has queued every launch before the first one starts
+                blocker.add_(1)
         e0.record(stream)
         for i in range(launches):
             fn_of_k(i % n_sets)
@@ -87,8 +90,8 @@ def main():
             cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
             row = {"n": n, "lg": lg, "npot": bool(delta)}
             for name, variant in (("lookback", sc.LOOKBACK), ("tile", sc.LOOKBACK_TILE), ("ring", sc.LOOKBACK_RING),
-                                  ("efficient", sc.EFFICIENT), ("naive", sc.NAIVE)):
-                if variant == sc.NAIVE and lg > 26:
+                                  ("wave", sc.LOOKBACK_WAVE), ("efficient", sc.EFFICIENT), ("naive", sc.NAIVE)):
+                if (variant == sc.NAIVE and lg > 26) or (variant == sc.LOOKBACK_WAVE and lg > 22):
                     continue
                 med, best = time_op(lambda: ctx.scan(n, out, a, variant, stream=s), args.iters, flush)
                 row[name + "_ms"] = med
@@ -104,13 +107,15 @@ def main():
                 n_sets = max(2, (300 << 20) // (8 * n) + 1)
                 ins = [torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda") for _ in range(n_sets)]
                 outs = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(n_sets)]
-                launches = max(64, 2 * n_sets)
+                launches = min(256, max(64, 2 * n_sets))
                 for name, variant in (("lookback", sc.LOOKBACK), ("tile", sc.LOOKBACK_TILE), ("ring", sc.LOOKBACK_RING),
-                                      ("efficient", sc.EFFICIENT)):
-                    ms = time_stream(lambda k: ctx.scan(n, outs[k], ins[k], variant, stream=s), n_sets, launches)
+                                      ("wave", sc.LOOKBACK_WAVE), ("efficient", sc.EFFICIENT)):
+                    if variant == sc.LOOKBACK_WAVE and lg > 22:
+                        continue
+                    ms = time_stream(lambda k: ctx.scan(n, outs[k], ins[k], variant, stream=s), n_sets, launches, flush)
                     row[name + "_stream_ms"] = ms
                     row[name + "_stream_frac"] = 8.0 * n / ms / 1e6 / peak
-                ms = time_stream(lambda k: ctx.compact(n, outs[k], ins[k], cnt, stream=s), n_sets, launches)
+                ms = time_stream(lambda k: ctx.compact(n, outs[k], ins[k], cnt, stream=s), n_sets, launches, flush)
                 row["compact_stream_ms"] = ms
                 row["compact_stream_frac"] = (4.0 * n + 4.0 * int(cnt.item())) / ms / 1e6 / peak
                 del ins, outs

@@ -220,13 +220,18 @@ int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int va
     switch (variant) {
     case B200_SCAN_LOOKBACK:
     case B200_SCAN_LOOKBACK_TILE:
-    case B200_SCAN_LOOKBACK_RING: {
+    case B200_SCAN_LOOKBACK_RING:
+    case B200_SCAN_LOOKBACK_WAVE: {
         const bool ring_ok = scan_ring_usable(d_in, d_out);
         if (variant == B200_SCAN_LOOKBACK_RING && !ring_ok) return B200_E_BADARG;
+        const bool wave_ok = scan_wave_usable(un, c->num_sms);
+        if (variant == B200_SCAN_LOOKBACK_WAVE && !wave_ok) return B200_E_BADARG;
         const bool ring = variant == B200_SCAN_LOOKBACK_RING || (variant == B200_SCAN_LOOKBACK && ring_ok && un >= c->ring_min_n);
+        const bool wave = variant == B200_SCAN_LOOKBACK_WAVE || (variant == B200_SCAN_LOOKBACK && !ring && wave_ok && un >= SC_WAVE_MIN_N);
         int r = ensure_lookback(c, un);
         if (r) return r;
-        if (ring) CK(launch_scan_ring(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
+        if (wave) CK(launch_scan_wave(d_in, d_out, un, c->desc, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
+        else if (ring) CK(launch_scan_ring(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
         else CK(launch_scan_lookback(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, s));
         c->last_launches = 1;
         return 0;
@@ -354,7 +359,7 @@ static int run_hostapi(int n, int* odata, const int* idata, int variant, bool co
 
 int b200_scan_i32(int n, int* odata, const int* idata, int variant, float* kernel_ms)
 {
-    if (variant < B200_SCAN_LOOKBACK || variant > B200_SCAN_LOOKBACK_RING) return B200_E_BADARG;
+    if (variant < B200_SCAN_LOOKBACK || variant > B200_SCAN_LOOKBACK_WAVE) return B200_E_BADARG;
     return run_hostapi(n, odata, idata, variant, false, nullptr, kernel_ms);
 }
 

@@ -88,6 +88,37 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
     return cudaGetLastError();
 }
 
+// The single-wave scan (sct::k_scan_wave): 896 threads x {1, 2, 4, 8} vectors, the smallest tile that covers n with at most
+// one CTA per SM.  Returns cudaErrorInvalidValue when n is too large for one wave (the caller then takes another kernel).
+template <int VEC>
+static cudaError_t launch_wave_cfg(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned epoch,
+                                   const int* d_seed, int* d_total, cudaStream_t s)
+{
+    using C = sct::Cfg<SC_WAVE_THREADS, VEC>;
+    const unsigned tiles = (unsigned)(((unsigned long long)n + C::tile - 1) / C::tile);
+    if (aligned16(d_in) && aligned16(d_out))
+        sct::k_scan_wave<C, true, STRIDE><<<tiles, C::threads, 0, s>>>(d_in, d_out, n, desc, epoch, d_seed, d_total);
+    else
+        sct::k_scan_wave<C, false, STRIDE><<<tiles, C::threads, 0, s>>>(d_in, d_out, n, desc, epoch, d_seed, d_total);
+    return cudaGetLastError();
+}
+
+bool scan_wave_usable(unsigned n, int num_sms)
+{
+    return num_sms > 0 && (unsigned long long)n <= (unsigned long long)num_sms * (SC_WAVE_THREADS * 8 * 4);
+}
+
+cudaError_t launch_scan_wave(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned epoch,
+                             const int* d_seed, int* d_total, int num_sms, cudaStream_t s)
+{
+    if (!scan_wave_usable(n, num_sms)) return cudaErrorInvalidValue;
+    const unsigned long long per_sm = ((unsigned long long)n + num_sms - 1) / num_sms;
+    if (per_sm <= SC_WAVE_THREADS * 1 * 4) return launch_wave_cfg<1>(d_in, d_out, n, desc, epoch, d_seed, d_total, s);
+    if (per_sm <= SC_WAVE_THREADS * 2 * 4) return launch_wave_cfg<2>(d_in, d_out, n, desc, epoch, d_seed, d_total, s);
+    if (per_sm <= SC_WAVE_THREADS * 4 * 4) return launch_wave_cfg<4>(d_in, d_out, n, desc, epoch, d_seed, d_total, s);
+    return launch_wave_cfg<8>(d_in, d_out, n, desc, epoch, d_seed, d_total, s);
+}
+
 // The persistent TMA-ring scan (sct::k_scan_tma): one CTA per SM, tuned on a B200 with benchmarks/sc_tune.cu
 // (profiles/r2z_sc_tune_tma_*.jsonl): 8192-int stages x 7 (224 KB of shared memory), 8 compute warps, pass B three tiles
 // behind pass A, 4 look-back warps.

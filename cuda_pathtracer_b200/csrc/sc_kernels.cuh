@@ -36,6 +36,14 @@ cudaError_t launch_scan_lookback(const int* d_in, int* d_out, unsigned n, unsign
                                  unsigned* tickets, unsigned epoch, const int* d_seed, int* d_total,
                                  cudaStream_t s);
 
+// The scan of a SMALL array in one wave of CTAs (sc_tmpl.cuh: k_scan_wave): every CTA reads all its predecessors' aggregates
+// in one round trip.  Usable while n <= num_sms * 28672 ints; the library takes it between SC_WAVE_MIN_N and that limit.
+constexpr int SC_WAVE_THREADS = 896;
+constexpr unsigned SC_WAVE_MIN_N = (1u << 19) + 1u;   // (up to 2^19 the tile kernel is as fast or faster: profiles/r2z_sc_sweep_small.json)
+bool scan_wave_usable(unsigned n, int num_sms);
+cudaError_t launch_scan_wave(const int* d_in, int* d_out, unsigned n, unsigned long long* desc, unsigned epoch,
+                             const int* d_seed, int* d_total, int num_sms, cudaStream_t s);
+
 // The same scan as a persistent TMA ring (sc_tmpl.cuh: k_scan_tma): bulk copies global -> shared -> global, the look-back
 // off the critical path.  Needs 16-byte aligned pointers (scan_ring_usable); tickets[2], tickets[3] are its tile / done
 // counters (zero between launches, shared with k_compact_ws: launches on one context are stream-ordered).  The library

@@ -197,6 +197,52 @@ k_scan_lookback(const int* __restrict__ in, int* __restrict__ out, unsigned n,
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_scan_wave: the single-pass scan for arrays small enough that ONE wave of CTAs (one per SM) holds all of them in
+// registers (n <= #SMs * 28672 ints: up to 2^22 on a B200).  With at most ~148 tiles there is nothing to walk back over:
+// every CTA publishes its aggregate, and thread t of CTA b reads the aggregate of CTA t < b -- all predecessors in ONE
+// round trip, however many there are -- a block sum gives the exclusive prefix.  (k_scan_lookback at 2^22 is 1024 tiles whose
+// 32-descriptor windows and the prefix frontier meet after ~16 dependent round trips: the ramp, not the bandwidth, is
+// what a small scan costs.)  CTAs are dispatched in blockIdx order and wait only on lower ones.
+// ------------------------------------------------------------------------------------------------
+template <class C, bool VEC_OK, int STRIDE>
+__global__ void __launch_bounds__(C::threads, 1)
+k_scan_wave(const int* __restrict__ in, int* __restrict__ out, unsigned n, unsigned long long* __restrict__ desc,
+            unsigned epoch, const int* __restrict__ d_seed, int* __restrict__ d_total)
+{
+    __shared__ int warp_sums[C::warps];
+    __shared__ int pred_sums[C::warps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tile = blockIdx.x;
+    int4 v[C::vec];
+    load_tile<C, VEC_OK>(in, n, tile, warp, lane, v);
+    int s[C::vec], excl[C::vec];
+#pragma unroll
+    for (int j = 0; j < C::vec; ++j) s[j] = v[j].x + v[j].y + v[j].z + v[j].w;
+    tile_warp_totals<C>(s, warp_sums, warp, lane);
+    __syncthreads();
+    const int aggregate = tile_exclusive_from_totals<C>(s, excl, warp_sums, warp, lane);
+    if (threadIdx.x == 0) lb_store(desc + (size_t)tile * STRIDE, lb_pack(epoch, LB_STATUS_A, aggregate));
+    int part = 0;
+    if ((unsigned)(warp * 32) < tile) {                          // (uniform per warp)
+        for (unsigned t = threadIdx.x; t < tile; t += C::threads) {
+            unsigned long long d;
+            do { d = lb_load(desc + (size_t)t * STRIDE); } while ((unsigned)(d >> 34) != epoch);
+            part += (int)(unsigned)d;
+        }
+        part = warp_sum(part);
+    }
+    if (lane == 0) pred_sums[warp] = part;
+    __syncthreads();
+    int tile_exclusive = d_seed ? __ldg(d_seed) : 0;
+    const int pred_warps = (int)((tile + 31u) / 32u) < C::warps ? (int)((tile + 31u) / 32u) : C::warps;
+    for (int w = 0; w < pred_warps; ++w) tile_exclusive += pred_sums[w];
+    if (d_total && threadIdx.x == 0 && tile == gridDim.x - 1) *d_total = tile_exclusive + aggregate;
+#pragma unroll
+    for (int j = 0; j < C::vec; ++j) v[j] = scan_vec(v[j], tile_exclusive + excl[j]);
+    store_tile<C, VEC_OK>(out, n, tile, warp, lane, v);
+}
+
+// ------------------------------------------------------------------------------------------------
 // k_compact: flag + scan + scatter in one pass.  Kept elements of a tile are first packed in
 // shared memory in order, then written as one contiguous run; the run is written with 128-bit
 // stores from the first 16-byte-aligned destination element on.

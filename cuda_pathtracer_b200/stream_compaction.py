@@ -10,7 +10,7 @@ import numpy as np
 from ._lib import B200Error, load
 
 LOOKBACK, EFFICIENT, NAIVE = 0, 1, 2
-LOOKBACK_TILE, LOOKBACK_RING = 3, 4     # the two kernels LOOKBACK picks between, by name (include/b200_sc.h)
+LOOKBACK_TILE, LOOKBACK_RING, LOOKBACK_WAVE = 3, 4, 5     # the kernels LOOKBACK picks between, by name (include/b200_sc.h)
 
 _c_int_p = ctypes.POINTER(ctypes.c_int)
 
@@ -94,6 +94,7 @@ Efficient = _EfficientNamespace(EFFICIENT)
 Thrust = _ScanNamespace(LOOKBACK)      # the single-pass look-back scan; no Thrust inside
 SinglePass = _EfficientNamespace(LOOKBACK)
 SinglePassTile = _ScanNamespace(LOOKBACK_TILE)   # one tile per CTA
+SinglePassWave = _ScanNamespace(LOOKBACK_WAVE)   # one wave of CTAs (small arrays)
 SinglePassRing = _ScanNamespace(LOOKBACK_RING)   # persistent TMA ring (what LOOKBACK runs on large aligned arrays)
 
 

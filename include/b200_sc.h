@@ -38,10 +38,12 @@ enum {
     B200_SCAN_EFFICIENT = 1, /* work-efficient reduce / scan-sums / down-sweep: 12 B/element
                                 (Efficient::scan name; the reference's is efficient.cu:138-176)       */
     B200_SCAN_NAIVE = 2,     /* ilog2ceil(n) Hillis-Steele passes (Naive::scan, naive.cu:36-66)       */
-    /* B200_SCAN_LOOKBACK picks between two kernels by size and pointer alignment; these two name them (tests, benchmarks): */
+    /* B200_SCAN_LOOKBACK picks between three kernels by size and pointer alignment; these name them (tests, benchmarks): */
     B200_SCAN_LOOKBACK_TILE = 3, /* one tile per CTA, loads and stores from registers                                    */
-    B200_SCAN_LOOKBACK_RING = 4  /* persistent, one CTA per SM: TMA bulk copies through a shared-memory ring, look-back
+    B200_SCAN_LOOKBACK_RING = 4, /* persistent, one CTA per SM: TMA bulk copies through a shared-memory ring, look-back
                                     off the critical path; device pointers must be 16-byte aligned (B200_E_BADARG)      */
+    B200_SCAN_LOOKBACK_WAVE = 5  /* small arrays: one wave of CTAs, every CTA sums ALL its predecessors' aggregates in one
+                                    round trip; n <= #SMs * 28672 ints (B200_E_BADARG beyond)                           */
 };
 
 /* error codes outside the cudaError_t range */

@@ -36,7 +36,7 @@ def np_exclusive_scan(a):
     return out.astype(np.uint64).astype(np.uint32).view(np.int32)
 
 
-VARIANTS = ["Naive", "Efficient", "Thrust", "SinglePassTile", "SinglePassRing"]
+VARIANTS = ["Naive", "Efficient", "Thrust", "SinglePassTile", "SinglePassRing", "SinglePassWave"]
 SIZES = [1, 2, 3, 4, 5, 31, 32, 33, 63, 64, 65, 255, 256, 257, 4095, 4096, 4097, 8191, 12289,
          (1 << 16) - 3, 1 << 16, (1 << 20) - 3, 1 << 20]
 
@@ -132,7 +132,7 @@ def test_device_ctx_seed_total_and_reduce(sc):
     seed = torch.tensor([123456], dtype=torch.int32, device="cuda")
     total = torch.zeros(1, dtype=torch.int32, device="cuda")
     want = np_exclusive_scan(a.cpu().numpy())
-    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.EFFICIENT, sc.NAIVE):
+    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.LOOKBACK_WAVE, sc.EFFICIENT, sc.NAIVE):
         out.zero_(); total.zero_()
         ctx.scan(n, out, a, variant, d_seed=seed, d_total=total)
         torch.cuda.synchronize()
@@ -242,7 +242,7 @@ def test_scan_is_linear_and_shift_consistent(sc):
     y = torch.randint(-2**31, 2**31 - 1, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
     ctx = sc.Context()
     sx, sy, sxy, sh = (torch.empty_like(x) for _ in range(4))
-    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.EFFICIENT):
+    for variant in (sc.LOOKBACK, sc.LOOKBACK_TILE, sc.LOOKBACK_RING, sc.LOOKBACK_WAVE, sc.EFFICIENT):
         ctx.scan(n, sx, x, variant)
         ctx.scan(n, sy, y, variant)
         ctx.scan(n, sxy, x + y, variant)
@@ -325,4 +325,35 @@ def test_ring_kernels_interleaved_on_one_context(sc):
         assert torch.equal(out, (torch.cumsum(a, 0, dtype=torch.int64) - a).to(torch.int32))
         keep = a[a != 0]
         assert int(cnt.item()) == keep.numel() and torch.equal(out2[: keep.numel()], keep)
+    ctx.close()
+
+
+def test_wave_scan_sizes_and_limit(sc):
+    """the single-wave kernel by name: every tile shape (896 threads x 1 / 2 / 4 / 8 vectors), ragged ends, misaligned
+    pointers, up to its limit of #SMs x 28672 ints; one element more is refused by name and served by LOOKBACK"""
+    import torch
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    limit = sms * 28672
+    ctx = sc.Context()
+    big = torch.randint(-50, 50, (limit + 9,), dtype=torch.int32, device="cuda")
+    ref = torch.cumsum(big, 0, dtype=torch.int64)
+    out = torch.empty(limit + 16, dtype=torch.int32, device="cuda")
+    total = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for n in (1, 2, 3583, 3584, 3585, sms * 3584 - 1, sms * 3584, sms * 3584 + 1, sms * 7168 + 5, sms * 14336 - 3,
+              sms * 14336 + 4, 1 << 22, limit - 1, limit):
+        for off in (0, 1):
+            a = big[off:off + n]
+            want = (ref[off:off + n] - a - (ref[off - 1] if off else 0)).to(torch.int32)
+            for variant in (sc.LOOKBACK_WAVE, sc.LOOKBACK):
+                out.fill_(-7)
+                ctx.scan(n, out[off:], a, variant, d_total=total)
+                torch.cuda.synchronize()
+                assert torch.equal(out[off:off + n], want), (n, off, variant)
+                assert bool((out[off + n:] == -7).all()) and bool((out[:off] == -7).all())
+                assert int(total.item()) == int((want[-1] + a[-1]).item())
+    with pytest.raises(Exception, match="10001|argument"):
+        ctx.scan(limit + 1, out, big[: limit + 1], sc.LOOKBACK_WAVE)
+    ctx.scan(limit + 1, out, big[: limit + 1], sc.LOOKBACK)
+    torch.cuda.synchronize()
+    assert torch.equal(out[: limit + 1], (ref[: limit + 1] - big[: limit + 1]).to(torch.int32))
     ctx.close()
