@@ -1,3 +1,5 @@
-set -x
 mkdir -p gpurun_out
-timeout 600 python benchmarks/sc_sweep.py --lg 14 16 18 19 20 21 22 23 24 --stream-max-lg 24 --json gpurun_out/sc_sweep3.json > gpurun_out/sc_sweep3.log 2>&1; echo "sweep exit $?"
+timeout 1200 python -m pytest tests/test_pt_gpu.py -x -q -m gpu > gpurun_out/pytest_pt.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/pytest_pt.log
+bash benchmarks/run_ab.sh "config2 " base u0 u4
+bash benchmarks/run_ab.sh "config4" base u0 u4
+bash benchmarks/run_ab.sh "N3 mesh_room 1200" base u0 u4

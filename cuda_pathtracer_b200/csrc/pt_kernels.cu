@@ -85,6 +85,20 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
 #endif
 }
 
+// The small-scene search's records (closest_small) live in STATIC shared memory: their addresses are compile-time constants,
+// so the cull loop's loads are LDS [k * 32 + constant].  Behind the run-time sized arrays of the dynamic allocation (materials,
+// mesh nodes) ptxas rebuilt the base address -- ten instructions -- for every primitive of every ray, 7 % of k_bounce's
+// instructions on the Cornell box (profiles/r2z_config2_cornell_k_bounce_src.csv).  cull == prims + PT_SMALL_MAX.
+template <bool ON>
+struct alignas(16) SmallStageT {
+    PrimRec prims[PT_SMALL_MAX];
+    float4 cull[2 * PT_SMALL_MAX];
+};
+template <>
+struct alignas(16) SmallStageT<false> {
+    PrimRec prims[1];
+};
+
 struct BounceShared {
     unsigned long long bar[2];
     int warp_cnt[PT_THREADS / 32];
@@ -357,6 +371,8 @@ __device__ __forceinline__ void closest_small(const PrimRec* __restrict__ sp, co
     float t1 = INF, t2 = INF;                    // the two smallest t_lo
     int k1 = -1, k2 = -1;
     unsigned cand = 0u;
+    // (a runtime loop on purpose: unrolling the first 4 / 8 steps lost 2 % / 7 % -- spills and instruction-cache misses,
+    //  profiles/r2_ab_variants.txt)
     for (int k = 0; k < n; ++k) {
         float t_lo;
         if (cull_test(cr[2 * k], cr[2 * k + 1], sp[k], o, d, inv, t_lo)) {
@@ -462,7 +478,7 @@ __device__ __forceinline__ void bounce_barriers_init(unsigned long long* bar)
 // producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
 // (with the geometry BVH: the top of that tree instead of primitive chunks)
 __device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long long* bar, MatRec* smats, int n_smem_mats,
-                                            BvhRec* snodes, PrimRec* sprims, bool want_prims)
+                                            BvhRec* snodes, PrimRec* sprims, bool want_prims, float4* scull = nullptr)
 {
     if (threadIdx.x != 0) return;
     if (p.gb.n_nodes > 0) {
@@ -475,7 +491,7 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long
             if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &bar[0]);
             if (node_bytes) bulk_g2s(snodes, p.mesh.nodes, node_bytes, &bar[0]);
             if (r_bytes) bulk_g2s(sprims, p.gb.prims, r_bytes, &bar[0]);
-            if (c_bytes) bulk_g2s(sprims + p.gb.n_small, p.gb.crecs, c_bytes, &bar[0]);
+            if (c_bytes) bulk_g2s(scull ? scull : reinterpret_cast<float4*>(sprims + PT_SMALL_MAX), p.gb.crecs, c_bytes, &bar[0]);
             return;
         }
         const unsigned g_bytes = want_prims ? (unsigned)(p.gb.n_smem_nodes * 4 * sizeof(float4)) : 0u;
@@ -526,7 +542,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
     if (GB) {
         // spheres / cubes first: their nearest hit caps the mesh walk (when nothing behind it can show)
         if (GB == 2) {
-            if (walk) closest_small(sprims, reinterpret_cast<const float4*>(sprims + p.gb.n_small), p.gb.n_small, o, d, t_min, hit, hit_k, best);
+            if (walk) closest_small(sprims, reinterpret_cast<const float4*>(sprims + PT_SMALL_MAX), p.gb.n_small, o, d, t_min, hit, hit_k, best);
         } else if (walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, t_min, hit, best);
         if (p.mesh.n_nodes > 0 && walk) {
             const float cap = p.gb.cap_mesh_walk ? prune_limit(t_min) : 3.402823466e+38f;
@@ -651,7 +667,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_bounce_tile(const __grid_constan
     const int n_smem_mats = p.n_mats <= PT_SMEM_MATS ? p.n_mats : 0;
     MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(BounceShared));
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smats + n_smem_mats);
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE != 2 ? p.mesh.n_smem_nodes : 0));
+    __shared__ SmallStageT<GB == 2> small_st;
+    PrimRec* sprims = GB == 2 ? small_st.prims : reinterpret_cast<PrimRec*>(snodes + (CACHE != 2 ? p.mesh.n_smem_nodes : 0));
 
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
@@ -762,7 +779,8 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
     float4* stash = reinterpret_cast<float4*>(smem_raw + sizeof(PersistShared));      // [3][PT_PWARPS][32]
     MatRec* smats = reinterpret_cast<MatRec*>(smem_raw + sizeof(PersistShared) + PT_STASH_BYTES);
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smats + n_smem_mats);
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + (CACHE < 2 ? p.mesh.n_smem_nodes : 0));
+    __shared__ SmallStageT<GB == 2> small_st;
+    PrimRec* sprims = GB == 2 ? small_st.prims : reinterpret_cast<PrimRec*>(snodes + (CACHE < 2 ? p.mesh.n_smem_nodes : 0));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     // ---- prologue: the work-item table of this launch, the first ticket, the staging copies ----
@@ -957,7 +975,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(BounceShared));
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
+    __shared__ SmallStageT<GB == 2> small_st;
+    PrimRec* sprims = GB == 2 ? small_st.prims : reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
     const int slot = blockIdx.y;
     const int tile = blockIdx.x;
     const int n_live = p.counts[p.bounce * p.batch + slot];
@@ -1360,8 +1379,10 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
     extern __shared__ __align__(128) unsigned char smem_raw[];
     DynShared& sh = *reinterpret_cast<DynShared*>(smem_raw);
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(DynShared));
+    // (dynamic layout here: closest_small runs once per ray, before a walk that lives on L1 hits -- the 4.6 KB of the static
+    //  stage cost this kernel 2.8 %, profiles/r2_ab_variants.txt)
     PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
-    const float4* crecs = reinterpret_cast<const float4*>(sprims + p.gb.n_small);
+    float4* crecs = reinterpret_cast<float4*>(sprims + p.gb.n_small);
     const MeshScene& M = p.mesh;
     const int lane = threadIdx.x & 31;
     bounce_barriers_init(sh.bar);
@@ -1375,7 +1396,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
         sh.total = run;
         if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
     }
-    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
+    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true, crecs);
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
     const int total = sh.total;
@@ -1700,7 +1721,7 @@ __global__ void __launch_bounds__(256) k_debug_shade(const MatRec* __restrict__ 
 size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes, int n_small)
 {
     const int n_chunks = (n_prims + PT_CHUNK - 1) / PT_CHUNK;
-    const size_t prim_bytes = n_small ? (size_t)n_small * (sizeof(PrimRec) + 2 * sizeof(float4))
+    const size_t prim_bytes = n_small ? (size_t)0        // (the small-scene records are in static shared memory: SmallStageT)
                               : n_gnodes ? (size_t)n_gnodes * 4 * sizeof(float4)
                                        : (size_t)(n_chunks > 1 ? 2 * PT_CHUNK : n_prims) * sizeof(PrimRec);
     const size_t mat_bytes = (size_t)(n_mats <= PT_SMEM_MATS ? n_mats : 0) * sizeof(MatRec);
@@ -1858,7 +1879,7 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, 
 #ifndef PT_NO_DYN_MESH
     if (mode == 2 && p.mesh.n_nodes > 0 && !p.mesh.literal_walk && !p.mesh.brute) {   // small scene + meshes
         const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small)
-                            - sizeof(BounceShared) + sizeof(DynShared);
+                            - sizeof(BounceShared) + sizeof(DynShared) + (size_t)p.gb.n_small * (sizeof(PrimRec) + 2 * sizeof(float4));
         if (cfg.dyn_mesh_smem != smem) {
             // The walk lives on L1 hits: ask for no more shared-memory carve-out than the four resident CTAs need
             // (+ 1 KB each that the system reserves).  The driver's own choice is larger: mesh room 661 -> 693 spp/s
