@@ -1,5 +1,3 @@
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_pt_gpu.py -x -q -m gpu > gpurun_out/pytest_pt.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/pytest_pt.log
-bash benchmarks/run_ab.sh "config2 " base u0 u4
-bash benchmarks/run_ab.sh "config4" base u0 u4
-bash benchmarks/run_ab.sh "N3 mesh_room 1200" base u0 u4
+timeout 1200 python -m pytest tests/test_pt_gpu.py tests/test_host_cli.py tests/test_dropin_gpu.py -x -q -m gpu > gpurun_out/pytest_pt.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/pytest_pt.log
+bash benchmarks/run_ab.sh "N3" base

@@ -478,12 +478,14 @@ __device__ __forceinline__ void bounce_barriers_init(unsigned long long* bar)
 // producer (thread 0): stage the materials (optional) and the first one or two primitive chunks
 // (with the geometry BVH: the top of that tree instead of primitive chunks)
 __device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long long* bar, MatRec* smats, int n_smem_mats,
-                                            BvhRec* snodes, PrimRec* sprims, bool want_prims, float4* scull = nullptr)
+                                            BvhRec* snodes, PrimRec* sprims, bool want_prims, float4* scull = nullptr,
+                                            int mesh_nodes = -1)
 {
     if (threadIdx.x != 0) return;
+    const int n_mesh_nodes = mesh_nodes >= 0 ? mesh_nodes : p.mesh.n_smem_nodes;     // nodes of the mesh BVH to stage
     if (p.gb.n_nodes > 0) {
         const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
-        const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
+        const unsigned node_bytes = want_prims ? (unsigned)(n_mesh_nodes * sizeof(BvhRec)) : 0u;
         if (p.gb.n_small > 0) {                  // the records themselves and their cull records, no tree
             const unsigned r_bytes = want_prims ? (unsigned)(p.gb.n_small * sizeof(PrimRec)) : 0u;
             const unsigned c_bytes = want_prims ? (unsigned)(p.gb.n_small * 2 * sizeof(float4)) : 0u;
@@ -504,7 +506,7 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long
     const int n_chunks = (p.n_prims + PT_CHUNK - 1) / PT_CHUNK;
     const int chunk_cap = n_chunks > 1 ? PT_CHUNK : p.n_prims;
     const unsigned mat_bytes = (unsigned)(n_smem_mats * sizeof(MatRec));
-    const unsigned node_bytes = want_prims ? (unsigned)(p.mesh.n_smem_nodes * sizeof(BvhRec)) : 0u;
+    const unsigned node_bytes = want_prims ? (unsigned)(n_mesh_nodes * sizeof(BvhRec)) : 0u;
     const int n0 = want_prims ? min(chunk_cap, p.n_prims) : 0;
     mbar_expect_tx(&bar[0], mat_bytes + node_bytes + (unsigned)(n0 * sizeof(PrimRec)));
     if (mat_bytes) bulk_g2s(smats, p.mats, mat_bytes, &bar[0]);
@@ -1074,8 +1076,12 @@ __global__ void __launch_bounds__(PT_THREADS) k_sort_scatter_packed(const __grid
 #ifndef PT_DYN_CULL
 #define PT_DYN_CULL 0
 #endif
+#ifndef PT_NODE_SPLIT
+#define PT_NODE_SPLIT 1
+#endif
 #ifndef PT_DYN_GNODES
-#define PT_DYN_GNODES 16           // staged nodes (1 KB); more takes L1 capacity away from the rest of the tree (512: 137 spp/s, 64: 142, 16: 144)
+#define PT_DYN_GNODES 0            // staged nodes of the quantised tree: none -- every lane loads its node from global memory through L1 (one code path;
+                                   // 16 staged: 221.5 spp/s, none: 224.6; round 1: 512: 137, 64: 142, 16: 144)
 #endif
 
 struct DynShared {
@@ -1103,6 +1109,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
     const uint4* snodes_q = reinterpret_cast<const uint4*>(smem_raw + sizeof(DynShared));
     const int lane = threadIdx.x & 31;
     const int n_staged = p.gb.n_nodes < PT_DYN_GNODES ? p.gb.n_nodes : PT_DYN_GNODES;
+    const unsigned snodes_s = smem_u32(snodes_q);
     const V3 qorg = v3(p.gb.qorg[0], p.gb.qorg[1], p.gb.qorg[2]), qcell = v3(p.gb.qcell[0], p.gb.qcell[1], p.gb.qcell[2]);
     bounce_barriers_init(sh.bar);
     if (threadIdx.x == 0) {
@@ -1115,8 +1122,12 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
         sh.total = run;
         if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
         const unsigned bytes = (unsigned)(n_staged * 2 * sizeof(uint4));
-        mbar_expect_tx(&sh.bar[0], bytes);
-        bulk_g2s(const_cast<uint4*>(snodes_q), p.gb.qnodes, bytes, &sh.bar[0]);
+        if (bytes) {
+            mbar_expect_tx(&sh.bar[0], bytes);
+            bulk_g2s(const_cast<uint4*>(snodes_q), p.gb.qnodes, bytes, &sh.bar[0]);
+        } else {
+            mbar_arrive(&sh.bar[0]);
+        }
     }
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
@@ -1194,8 +1205,21 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                 // 32-byte node: two 16-byte loads instead of four (this walk is bound by the L1 load path: every 16-byte load
                 // of 32 lanes standing at 32 different nodes is 32 tag look-ups; ncu l1tex throughput 92 % of peak with the
                 // 64-byte nodes, profiles/r2e_config5_k_isect_dyn_raw.csv)
-                const uint4* q = node < n_staged ? snodes_q + 2 * node : p.gb.qnodes + 2 * (size_t)node;
-                const uint4 A = q[0], B = q[1];
+                uint4 A, B;
+#if PT_NODE_SPLIT
+                if (PT_DYN_GNODES > 0 && node < n_staged) {
+                    const unsigned at = snodes_s + 32u * (unsigned)node;
+                    A = lds_u4(at); B = lds_u4(at + 16u);
+                } else {
+                    const uint4* q = p.gb.qnodes + 2 * (size_t)node;
+                    A = __ldg(q); B = __ldg(q + 1);
+                }
+#else
+                {
+                    const uint4* q = node < n_staged ? snodes_q + 2 * node : p.gb.qnodes + 2 * (size_t)node;
+                    A = q[0]; B = q[1];
+                }
+#endif
 #if PT_DYN_QFMA
                 float t0 = qbox_entry(fmaf(qlo(A.x), qr.ig.x, qr.cg.x), fmaf(qhi(A.y), qr.ig.x, qr.cg.x),
                                       fmaf(qhi(A.x), qr.ig.y, qr.cg.y), fmaf(qlo(A.z), qr.ig.y, qr.cg.y),
@@ -1370,6 +1394,10 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
 // nodes in the reference's order and the listed triangles are tested in the order met, so the "first one
 // met wins a tie" rule is untouched.  Trees deep enough for the reference's stack-overflow drop
 // (literal_walk) and the useBVHtree = false mode stay with k_isect.
+#ifndef PT_DYNM_NODES
+#define PT_DYNM_NODES 0          // nodes of the mesh BVH this kernel stages in shared memory: none (256: 733 spp/s, 64 / 32: 738, 0: 755 on the
+                                 // mesh room -- L1 serves the top of the tree as well, and the shared memory it does not lose serves the rest)
+#endif
 #ifndef PT_DYNM_REFILL
 #define PT_DYNM_REFILL 12
 #endif
@@ -1381,7 +1409,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(DynShared));
     // (dynamic layout here: closest_small runs once per ray, before a walk that lives on L1 hits -- the 4.6 KB of the static
     //  stage cost this kernel 2.8 %, profiles/r2_ab_variants.txt)
-    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
+    const int n_stage = p.mesh.n_smem_nodes < PT_DYNM_NODES ? p.mesh.n_smem_nodes : PT_DYNM_NODES;
+    PrimRec* sprims = reinterpret_cast<PrimRec*>(snodes + n_stage);
     float4* crecs = reinterpret_cast<float4*>(sprims + p.gb.n_small);
     const MeshScene& M = p.mesh;
     const int lane = threadIdx.x & 31;
@@ -1396,7 +1425,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
         sh.total = run;
         if (blockIdx.x == 0) atomicAdd(p.segments, (unsigned long long)run);
     }
-    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true, crecs);
+    const unsigned snodes_s = smem_u32(snodes);
+    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true, crecs, n_stage);
     __syncthreads();
     mbar_wait(&sh.bar[0], 0u);
     const int total = sh.total;
@@ -1459,16 +1489,32 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
             if (!__any_sync(FULL_MASK, go)) break;
             if (go) {
                 const float lim = fminf(prune_limit(mh.t), t_cap);
+#if PT_NODE_SPLIT
+                float4 w0, w1, w2;                     // BvhRec as three 16-byte words: lo | sub_areas, hi | axis, first rchild - -
+                if (PT_DYNM_NODES > 0 && cur < n_stage) {
+                    const unsigned at = snodes_s + 48u * (unsigned)cur;
+                    w0 = lds_f4(at); w1 = lds_f4(at + 16u); w2 = lds_f4(at + 32u);
+                } else {
+                    const float4* g = reinterpret_cast<const float4*>(M.nodes + cur);
+                    w0 = __ldg(g); w1 = __ldg(g + 1); w2 = __ldg(g + 2);
+                }
+                const float nlo[3] = {w0.x, w0.y, w0.z}, nhi[3] = {w1.x, w1.y, w1.z};
+                const int nd_sub = __float_as_int(w0.w), nd_axis = __float_as_int(w1.w);
+                const int nd_first = __float_as_int(w2.x), nd_rchild = __float_as_int(w2.y);
+#else
                 const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
+                const float* nlo = nd.lo; const float* nhi = nd.hi;
+                const int nd_sub = nd.sub_areas, nd_axis = nd.axis, nd_first = nd.first, nd_rchild = nd.rchild;
+#endif
                 float entry;
                 bool descend = false;
-                if (bbox_hit(nd.lo, nd.hi, o, minv, entry) && !(entry > lim)) {
-                    if (nd.sub_areas > 0) {
-                        leaf_first[nl] = nd.first; leaf_count[nl] = nd.sub_areas; leaf_entry[nl] = entry; ++nl;
+                if (bbox_hit(nlo, nhi, o, minv, entry) && !(entry > lim)) {
+                    if (nd_sub > 0) {
+                        leaf_first[nl] = nd_first; leaf_count[nl] = nd_sub; leaf_entry[nl] = entry; ++nl;
                     } else {
                         descend = true;
-                        if ((nd.axis == 0 ? d.x : nd.axis == 1 ? d.y : d.z) < 0.0f) { to_visit[sp++] = cur + 1; cur = nd.rchild; }
-                        else { to_visit[sp++] = nd.rchild; cur = cur + 1; }
+                        if ((nd_axis == 0 ? d.x : nd_axis == 1 ? d.y : d.z) < 0.0f) { to_visit[sp++] = cur + 1; cur = nd_rchild; }
+                        else { to_visit[sp++] = nd_rchild; cur = cur + 1; }
                     }
                 }
                 if (!descend) {
@@ -1878,7 +1924,8 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, 
 #endif
 #ifndef PT_NO_DYN_MESH
     if (mode == 2 && p.mesh.n_nodes > 0 && !p.mesh.literal_walk && !p.mesh.brute) {   // small scene + meshes
-        const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small)
+        const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes < PT_DYNM_NODES ? p.mesh.n_smem_nodes : PT_DYNM_NODES,
+                                              p.gb.n_smem_nodes, p.gb.n_small)
                             - sizeof(BounceShared) + sizeof(DynShared) + (size_t)p.gb.n_small * (sizeof(PrimRec) + 2 * sizeof(float4));
         if (cfg.dyn_mesh_smem != smem) {
             // The walk lives on L1 hits: ask for no more shared-memory carve-out than the four resident CTAs need

@@ -234,6 +234,24 @@ __device__ __forceinline__ V3 prim_normal(const PrimRec& g, const Cand& c)
 // (_Z19BVHIntersectionTest...): cross products as FMUL + FFMA(a, b, -t), dot products as
 // fma(z, z', fma(x, x', y*y')), 1/x as rcp.rn, every bounding-box slab as FADD then FMUL.
 
+// Address-space specific 16-byte loads for the tree walks.  A node comes from the staged top of its tree (shared memory) or
+// from the array in global memory; written as `cond ? snodes[i] : gnodes[i]` the compiler selects between two GENERIC
+// addresses -- a divergent branch, eleven instructions to turn the shared offset into a generic address (S2R CgaCtaId, S2R
+// SWINHI, ...) on one side, and generic loads behind it: 14-17 issue slots per node visit, 5-7 % of the walk kernels
+// (profiles/r2z_config5_k_isect_dyn_lines.txt: pt_kernels.cu:1178).  With these a side is one address add and its loads.
+__device__ __forceinline__ float4 lds_f4(unsigned addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_u4(unsigned addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
 struct BvhRec {          // class BVHTree (40 B) padded to three 16-byte words
     float lo[3]; int sub_areas;          // min corner | leaf triangle count (0 = inner node)
     float hi[3]; int axis;               // max corner | split axis of an inner node
@@ -406,19 +424,31 @@ __device__ __forceinline__ MeshHit bvh_traverse(const MeshScene& M, const BvhRec
     const bool neg[3] = {d.x < 0.0f, d.y < 0.0f, d.z < 0.0f};
     const V3 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     bool more = true;
+    const unsigned snodes_s = (unsigned)__cvta_generic_to_shared(snodes);
     while (more) {
         const float lim = fminf(prune_limit(h.t), t_cap);
         while (true) {                                   // the walk: box tests only
-            const BvhRec& nd = cur < M.n_smem_nodes ? snodes[cur] : M.nodes[cur];
+            // (two address-space specific paths instead of a select between generic addresses: see lds_f4)
+            float4 w0, w1, w2;                           // BvhRec as three 16-byte words
+            if (cur < M.n_smem_nodes) {
+                const unsigned at = snodes_s + 48u * (unsigned)cur;
+                w0 = lds_f4(at); w1 = lds_f4(at + 16u); w2 = lds_f4(at + 32u);
+            } else {
+                const float4* g = reinterpret_cast<const float4*>(M.nodes + cur);
+                w0 = __ldg(g); w1 = __ldg(g + 1); w2 = __ldg(g + 2);
+            }
+            const float nlo[3] = {w0.x, w0.y, w0.z}, nhi[3] = {w1.x, w1.y, w1.z};
+            const int nd_sub = __float_as_int(w0.w), nd_axis = __float_as_int(w1.w);
+            const int nd_first = __float_as_int(w2.x), nd_rchild = __float_as_int(w2.y);
             float entry;
             bool descend = false;
-            if (bbox_hit(nd.lo, nd.hi, o, inv, entry) && !(entry > lim)) {
-                if (nd.sub_areas > 0) {
-                    leaf_first[nl] = nd.first; leaf_count[nl] = nd.sub_areas; leaf_entry[nl] = entry; ++nl;
+            if (bbox_hit(nlo, nhi, o, inv, entry) && !(entry > lim)) {
+                if (nd_sub > 0) {
+                    leaf_first[nl] = nd_first; leaf_count[nl] = nd_sub; leaf_entry[nl] = entry; ++nl;
                 } else {
                     descend = true;
-                    if (neg[nd.axis]) { to_visit[sp++] = cur + 1; cur = nd.rchild; }
-                    else { to_visit[sp++] = nd.rchild; cur = cur + 1; }
+                    if (neg[nd_axis]) { to_visit[sp++] = cur + 1; cur = nd_rchild; }
+                    else { to_visit[sp++] = nd_rchild; cur = cur + 1; }
                 }
             }
             if (!descend) {
