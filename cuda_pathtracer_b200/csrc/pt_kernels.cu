@@ -138,20 +138,20 @@ __device__ __forceinline__ void closest_in_chunk(const PrimRec* __restrict__ sp,
 }
 
 // normal / texture coordinate of the winner `g` (scene index `hit`), pathtrace.cu:283-296
-__device__ __forceinline__ void hit_attributes(const MeshScene& M, const PrimRec& g, int hit, const Cand& best, const MeshHit& mh,
+__device__ __forceinline__ void hit_attributes(const MeshScene& M, const PrimTail& g, int hit, const Cand& best, const MeshHit& mh,
                                                int owner, V3& n, float& u, float& v)
 {
     if (M.brute) {
         if (g.type == 2) {
             brute_attributes(M.ta[mh.tri], mh.bx, mh.by, n, u, v);
         } else {
-            n = prim_normal(g, best);
+            n = prim_normal(g.itr, g.type, best);
             if (mh.tri >= 0) { V3 unused; brute_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
         }
     } else if (g.type == 2) {
         tri_attributes(M.ta[mh.tri], mh.bx, mh.by, n, u, v);
     } else {
-        n = prim_normal(g, best);
+        n = prim_normal(g.itr, g.type, best);
         // (sic) a sphere / cube winning AFTER a mesh primitive accepted the BVH hit carries that
         // hit's stale texture coordinate (pathtrace.cu:267,283)
         if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
@@ -578,7 +578,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
     if (hit >= 0) {
         // (small-scene search: a MESH winner is not among the staged records -> hit_k stays behind)
         const bool staged = GB == 2 ? (hit_k >= 0 && sprims[hit_k].pad0 == hit) : (GB == 0 && n_chunks <= 1);
-        const PrimRec& g = staged ? sprims[GB == 2 ? hit_k : hit] : p.prims[hit];
+        const PrimTail g = load_prim_tail(staged, smem_u32(sprims + (GB == 2 ? hit_k : hit)), p.prims + hit);
         hit_attributes(p.mesh, g, hit, best, mh, owner, h.n, h.u, h.v);
         h.t = t_min;
         h.mat = g.material;
@@ -599,12 +599,19 @@ __device__ __forceinline__ PathState load_path(const Pool& pool, size_t at)
 // shadeMaterials + scatterRay for the path at compacted slot `idx`, finalGather for a path that
 // ends here, and the stable single-pass compaction of the survivors into the other pool.
 // Every thread of the CTA must call it.
+#ifndef PT_EXPLICIT_MAT
+#define PT_EXPLICIT_MAT 1
+#endif
 __device__ __forceinline__ bool shade_path(const RenderParams& p, const MatRec* smats, int n_smem_mats, PathState& s,
                                            const HitRec& h, bool active, int slot, int idx)
 {
     bool live = false;
     if (active) {
+#if PT_EXPLICIT_MAT
+        const MatRec m = load_mat(n_smem_mats != 0, smem_u32(smats + h.mat), p.mats + h.mat);
+#else
         const MatRec& m = n_smem_mats ? smats[h.mat] : p.mats[h.mat];
+#endif
         const int iter = p.iter0 + slot * p.stride;
         const V3 base = (m.texture_id != -1 && h.t > 0.0f) ? tex_color(p.mesh, m.texture_id, h.u, h.v)
                                                            : v3(m.color[0], m.color[1], m.color[2]);
@@ -1550,7 +1557,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn_mesh(const __grid_cons
             int hm = 0;
             if (hit >= 0) {
                 const bool staged = hit_k >= 0 && sprims[hit_k].pad0 == hit;
-                const PrimRec& g = staged ? sprims[hit_k] : p.prims[hit];
+                const PrimTail g = load_prim_tail(staged, smem_u32(sprims + hit_k), p.prims + hit);
                 hit_attributes(M, g, hit, best, mh, owner, hn, hu, hv);
                 ht = t_min;
                 hm = g.material;
@@ -1740,7 +1747,7 @@ __global__ void __launch_bounds__(256) k_debug_intersect(const PrimRec* __restri
     int mat = 0;
     float u = 0.f, v = 0.f;
     if (hit >= 0) {
-        hit_attributes(mesh, prims[hit], hit, best, mh, owner, nn, u, v);
+        hit_attributes(mesh, load_prim_tail(false, 0u, prims + hit), hit, best, mh, owner, nn, u, v);
         mat = prims[hit].material;
     }
     o[0] = hit >= 0 ? t_min : -1.0f;

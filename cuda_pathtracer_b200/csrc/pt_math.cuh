@@ -219,12 +219,22 @@ __device__ __forceinline__ Cand prim_test(const PrimRec& g, const V3& o, const V
 }
 
 // normal = normalize(invTranspose * vec4(aux, 0)); the sphere flips it when hit from inside.
-__device__ __forceinline__ V3 prim_normal(const PrimRec& g, const Cand& c)
+__device__ __forceinline__ V3 prim_normal(const float* __restrict__ itr, int type, const Cand& c)
 {
-    V3 n = normalize_exact(xform_vector(g.itr, c.aux));
-    if (g.type == 0 && !c.outside) n = v3(-n.x, -n.y, -n.z);
+    V3 n = normalize_exact(xform_vector(itr, c.aux));
+    if (type == 0 && !c.outside) n = v3(-n.x, -n.y, -n.z);
     return n;
 }
+__device__ __forceinline__ V3 prim_normal(const PrimRec& g, const Cand& c) { return prim_normal(g.itr, g.type, c); }
+
+// The last 64 bytes of a PrimRec -- invTranspose, type, material: all that is read of the WINNING primitive -- taken into
+// registers through an address-space specific path (four 16-byte loads): the winner's record is in shared memory for a
+// staged primitive and in global memory otherwise, and a reference bound to `staged ? sprims[k] : prims[hit]` is a generic
+// pointer (a dozen 4-byte generic loads behind ten instructions of address conversion, see lds_f4 below).
+struct PrimTail {
+    float itr[12];
+    int type, material, pad0, pad1;
+};
 
 
 // ---- triangle meshes: BVH traversal and ray / triangle test ---------------------------------------
@@ -250,6 +260,45 @@ __device__ __forceinline__ uint4 lds_u4(unsigned addr)
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
+}
+
+__device__ __forceinline__ PrimTail load_prim_tail(bool in_shared, unsigned smem_addr, const PrimRec* __restrict__ g)
+{
+    float4 w[4];
+    if (in_shared) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = lds_f4(smem_addr + 96u + 16u * j);
+    } else {
+        const float4* q = reinterpret_cast<const float4*>(g) + 6;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = __ldg(q + j);
+    }
+    PrimTail t;
+    t.itr[0] = w[0].x; t.itr[1] = w[0].y; t.itr[2] = w[0].z; t.itr[3] = w[0].w;
+    t.itr[4] = w[1].x; t.itr[5] = w[1].y; t.itr[6] = w[1].z; t.itr[7] = w[1].w;
+    t.itr[8] = w[2].x; t.itr[9] = w[2].y; t.itr[10] = w[2].z; t.itr[11] = w[2].w;
+    t.type = __float_as_int(w[3].x); t.material = __float_as_int(w[3].y);
+    t.pad0 = __float_as_int(w[3].z); t.pad1 = __float_as_int(w[3].w);
+    return t;
+}
+
+// a material (48 bytes) the same way: three 16-byte loads from the staged copy or from global memory
+__device__ __forceinline__ MatRec load_mat(bool in_shared, unsigned smem_addr, const MatRec* __restrict__ g)
+{
+    float4 w[3];
+    if (in_shared) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) w[j] = lds_f4(smem_addr + 16u * j);
+    } else {
+        const float4* q = reinterpret_cast<const float4*>(g);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) w[j] = __ldg(q + j);
+    }
+    MatRec m;
+    m.color[0] = w[0].x; m.color[1] = w[0].y; m.color[2] = w[0].z; m.spec_exp = w[0].w;
+    m.spec_color[0] = w[1].x; m.spec_color[1] = w[1].y; m.spec_color[2] = w[1].z; m.has_reflective = w[1].w;
+    m.has_refractive = w[2].x; m.ior = w[2].y; m.emittance = w[2].z; m.texture_id = __float_as_int(w[2].w);
+    return m;
 }
 
 struct BvhRec {          // class BVHTree (40 B) padded to three 16-byte words
