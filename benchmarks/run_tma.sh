@@ -1,4 +1,4 @@
 mkdir -p gpurun_out
-python benchmarks/pt_configs.py --no-ref --only "config4 glass" > /dev/null 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/r2z_config4_launches.csv python benchmarks/pt_configs.py --no-ref --only "config4 glass" > gpurun_out/ncu_c4.log 2>&1
-python benchmarks/launch_summary.py gpurun_out/r2z_config4_launches.csv 2>&1 | head -30
+timeout 900 python -m pytest tests/test_pt_gpu.py tests/test_dropin_gpu.py tests/test_host_cli.py -x -q -m gpu > gpurun_out/pytest_pt.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_pt.log
+timeout 900 bash benchmarks/run_ab.sh "config4" base s32
+timeout 300 bash benchmarks/run_ab.sh "N3b" base

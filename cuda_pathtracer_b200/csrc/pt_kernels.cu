@@ -978,6 +978,21 @@ __device__ __forceinline__ int warp_digit_rank(SortShared& sh, bool active, int 
 // offset[key][tile] + rank; no warp match, no shared memory, no barrier).  Config 4: k_isect 16.3 -> 18.x ms instead of
 // + 7.5 ms of k_sort_hist, k_sort_scatter 6.4 -> 3.6 ms (profiles/r2_ab_variants.txt).  A persistent form of this kernel
 // (resident CTAs striding over the tiles, scene staged once per CTA) was measured 18 % SLOWER than one tile per CTA.
+#ifndef PT_ISECT_TILES
+#define PT_ISECT_TILES 16
+#endif
+#ifndef PT_ISECT_STRIDE
+#define PT_ISECT_STRIDE 1
+#endif
+// A CTA takes PT_ISECT_TILES tiles of its slot, strided by the grid (the scene is staged once).  The grid covers every tile of every
+// slot whatever the live counts are (they are device-side), and in the late bounces nearly all CTAs find their tile beyond the
+// live range: with one tile per CTA config 4 launched 129 600 CTAs per bounce, ~100 us of CTA launches for a few microseconds
+// of work -- a quarter of this kernel's time over a step (profiles/r2z_config4_launches.csv).  Strided, not consecutive:
+// the live tiles of a slot (its first ones) then spread evenly over the slot's CTAs (config 4, spp/s: one tile per CTA 2870;
+// 4 / 8 / 16 consecutive tiles 2946 / 2883 / 2720; 4 / 8 / 16 strided 3005 / 3044 / 3047).
+template <int GB>
+__host__ __device__ constexpr int isect_tiles_per_cta() { return GB == 0 ? 1 : PT_ISECT_TILES; }     // (GB == 0 re-arms its chunk barriers per tile)
+
 template <int GB>
 __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
 {
@@ -985,63 +1000,74 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
     BvhRec* snodes = reinterpret_cast<BvhRec*>(smem_raw + sizeof(BounceShared));
     __shared__ SmallStageT<GB == 2> small_st;
+    __shared__ int cnt[PT_THREADS / 32][256];
     PrimRec* sprims = GB == 2 ? small_st.prims : reinterpret_cast<PrimRec*>(snodes + p.mesh.n_smem_nodes);
     const int slot = blockIdx.y;
-    const int tile = blockIdx.x;
     const int n_live = p.counts[p.bounce * p.batch + slot];
     const int bins = p.sort_bins;
-    if (tile * PT_THREADS >= n_live) {
-        int* hist = p.hist + (size_t)slot * bins * p.tiles;
-        for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) hist[(size_t)bb * p.tiles + tile] = 0;
-        return;
-    }
-    if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
-    bounce_barriers_init(sh.bar);
-    stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
-    const int idx = tile * PT_THREADS + threadIdx.x;
-    const bool active = idx < n_live;
-    const size_t at = (size_t)slot * p.P + (active ? idx : 0);
-    const float4 a = p.in.a[at], b = p.in.b[at];
-    const HitRec h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
-    if (active) {
-        p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
-        if (bins == 0) p.hit_k[at] = h.mat;
-        p.hit_uv[at] = make_float2(h.u, h.v);
-        if (p.cache_mode == 1 && slot == 0) {
-            p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
-            p.cache_k[idx] = h.mat;
-            p.cache_uv[idx] = make_float2(h.u, h.v);
+    constexpr int T = isect_tiles_per_cta<GB>();
+    bool staged = false;
+    for (int tt = 0; tt < T; ++tt) {
+#if PT_ISECT_STRIDE
+        const int tile = blockIdx.x + tt * gridDim.x;    // strided: the live tiles of a slot spread evenly over its CTAs
+#else
+        const int tile = blockIdx.x * T + tt;
+#endif
+        if (tile >= p.tiles) break;
+        if (tile * PT_THREADS >= n_live) {               // (uniform over the CTA; the live tiles of a slot come first)
+            int* hist = p.hist + (size_t)slot * bins * p.tiles;
+            for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) hist[(size_t)bb * p.tiles + tile] = 0;
+            continue;
         }
-    }
-    if (bins > 0) {
-
-        __shared__ int cnt[PT_THREADS / 32][256];
-        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        for (int bb = lane; bb < bins; bb += 32) cnt[warp][bb] = 0;
-        __syncwarp();
-        const unsigned act = __ballot_sync(FULL_MASK, active);
-        int rank = 0;
+        if (tile == 0 && threadIdx.x == 0) atomicAdd(p.segments, (unsigned long long)n_live);
+        if (!staged) {
+            bounce_barriers_init(sh.bar);
+            stage_begin(p, sh.bar, nullptr, 0, snodes, sprims, true);
+            staged = true;
+        }
+        const int idx = tile * PT_THREADS + threadIdx.x;
+        const bool active = idx < n_live;
+        const size_t at = (size_t)slot * p.P + (active ? idx : 0);
+        const float4 a = p.in.a[at], b = p.in.b[at];
+        const HitRec h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
         if (active) {
-            const unsigned peers = __match_any_sync(act, h.mat & 255);
-            rank = __popc(peers & ((1u << lane) - 1u));
-            if (rank == 0) cnt[warp][h.mat & 255] = __popc(peers);
+            p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+            if (bins == 0) p.hit_k[at] = h.mat;
+            p.hit_uv[at] = make_float2(h.u, h.v);
+            if (p.cache_mode == 1 && slot == 0) {
+                p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
+                p.cache_k[idx] = h.mat;
+                p.cache_uv[idx] = make_float2(h.u, h.v);
+            }
         }
-        __syncthreads();
-        if (active) {
-            for (int ww = 0; ww < warp; ++ww) rank += cnt[ww][h.mat & 255];
-            p.hit_k[at] = h.mat | (rank << 24);
-        }
-        int* hist = p.hist + (size_t)slot * bins * p.tiles;
-        for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) {
-            int t = 0;
+        if (bins > 0) {
+            const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            for (int bb = lane; bb < bins; bb += 32) cnt[warp][bb] = 0;
+            __syncwarp();
+            const unsigned act = __ballot_sync(FULL_MASK, active);
+            int rank = 0;
+            if (active) {
+                const unsigned peers = __match_any_sync(act, h.mat & 255);
+                rank = __popc(peers & ((1u << lane) - 1u));
+                if (rank == 0) cnt[warp][h.mat & 255] = __popc(peers);
+            }
+            __syncthreads();
+            if (active) {
+                for (int ww = 0; ww < warp; ++ww) rank += cnt[ww][h.mat & 255];
+                p.hit_k[at] = h.mat | (rank << 24);
+            }
+            int* hist = p.hist + (size_t)slot * bins * p.tiles;
+            for (int bb = threadIdx.x; bb < bins; bb += PT_THREADS) {
+                int t = 0;
 #pragma unroll
-            for (int ww = 0; ww < PT_THREADS / 32; ++ww) t += cnt[ww][bb];
-            hist[(size_t)bb * p.tiles + tile] = t;
+                for (int ww = 0; ww < PT_THREADS / 32; ++ww) t += cnt[ww][bb];
+                hist[(size_t)bb * p.tiles + tile] = t;
+            }
+            if (T > 1) __syncthreads();                  // the counts are read: the next tile may clear them
         }
     }
 }
 
-// the scatter half of the one-pass material bucketing: keys carry their in-tile rank (k_isect)
 // Four paths per thread (one 16-byte load of their keys, four independent offset look-ups and stores): with one path per
 // thread the pass ran at the latency of its three dependent memory operations -- 1 TB/s of keys at full occupancy (config 4:
 // 3.6 ms of a 38 ms step).  A CTA takes four consecutive tiles per step, 64 threads each.
@@ -1975,10 +2001,10 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, 
     }
 #endif
     const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
-    const dim3 grid(p.tiles, p.batch);
-    if (mode == 2) k_isect<2><<<grid, PT_THREADS, smem, s>>>(p);
-    else if (mode == 1) k_isect<1><<<grid, PT_THREADS, smem, s>>>(p);
-    else k_isect<0><<<grid, PT_THREADS, smem, s>>>(p);
+    const auto grid_for = [&](int per_cta) { return dim3((unsigned)((p.tiles + per_cta - 1) / per_cta), (unsigned)p.batch); };
+    if (mode == 2) k_isect<2><<<grid_for(isect_tiles_per_cta<2>()), PT_THREADS, smem, s>>>(p);
+    else if (mode == 1) k_isect<1><<<grid_for(isect_tiles_per_cta<1>()), PT_THREADS, smem, s>>>(p);
+    else k_isect<0><<<grid_for(isect_tiles_per_cta<0>()), PT_THREADS, smem, s>>>(p);
     if (hist_done) *hist_done = p.sort_bins > 0;     // k_isect did the counting half of the sort
     return cudaGetLastError();
 }
