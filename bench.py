@@ -220,13 +220,21 @@ def scan_bench(torch, peak):
         ts.sort()
         return ts[len(ts) // 2]
 
-    for name, variant in (("scan_lookback", sc.LOOKBACK), ("scan_efficient", sc.EFFICIENT)):
+    kernels = {"scan_lookback": "k_scan_tma (single pass, persistent TMA ring; what B200_SCAN_LOOKBACK runs from 2^24 aligned ints on)",
+               "scan_lookback_tile": "k_scan_lookback (single pass, one register tile per CTA; B200_SCAN_LOOKBACK_TILE)",
+               "scan_efficient": "k_reduce_tiles + k_downsweep (work-efficient, 12 B/element of traffic, quoted at 8)"}
+    for name, variant in (("scan_lookback", sc.LOOKBACK), ("scan_lookback_tile", sc.LOOKBACK_TILE), ("scan_efficient", sc.EFFICIENT)):
         ms = timed(lambda: ctx.scan(n, out, a, variant, stream=stream.cuda_stream))
-        res[name] = {"ms": ms, "gbs": 8.0 * n / ms / 1e6, "frac": 8.0 * n / ms / 1e6 / peak}
+        res[name] = {"ms": ms, "gbs": 8.0 * n / ms / 1e6, "frac": 8.0 * n / ms / 1e6 / peak, "kernel": kernels[name]}
     ms = timed(lambda: ctx.compact(n, out, b, cnt, stream=stream.cuda_stream))
     k = int(cnt.item())
     res["compact"] = {"ms": ms, "gbs": (4.0 * n + 4.0 * k) / ms / 1e6, "frac": (4.0 * n + 4.0 * k) / ms / 1e6 / peak,
-                      "kept": k}
+                      "kept": k, "kernel": "k_compact_tma (single pass on the TMA ring, in-place packing, bulk-stored runs)"}
+    ctx.set_ring_min_n(2**31 - 1)                                # the register-tile compaction, for the record
+    ms = timed(lambda: ctx.compact(n, out, b, cnt, stream=stream.cuda_stream))
+    res["compact_tile"] = {"ms": ms, "gbs": (4.0 * n + 4.0 * k) / ms / 1e6, "frac": (4.0 * n + 4.0 * k) / ms / 1e6 / peak,
+                           "kernel": "k_compact_ws (persistent, register tiles, look-back warp; ring switched off)"}
+    ctx.set_ring_min_n(0)
     want_scan_tail = int((torch.cumsum(a[-4096:].to(torch.int64), 0)[-1]).item())     # (only used as a smoke value)
     ctx.close()
 

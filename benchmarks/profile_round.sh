@@ -18,7 +18,9 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
     $cmd > $out/${tag}_ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 64 -c 64 -f -o $out/${tag}_k_bounce \
     python bench.py --steps 1 --warmup 1 --skip-extras > $out/${tag}_ncu_bounce.log 2>&1
-ncu --set full --clock-control none --import-source on -k 'regex:k_scan_lookback|k_compact' -s 3 -c 4 -f -o $out/${tag}_k_scan \
+# (sc_sweep at 2^28 launches, five times each: the scan LOOKBACK picks (k_scan_tma), k_scan_lookback, k_scan_tma by name, the work-efficient
+#  pair, the compaction (k_compact_tma); one launch of each kind is kept)
+ncu --set full --clock-control none --import-source on -k 'regex:k_scan_tma|k_compact_tma|k_scan_lookback|k_reduce_tiles|k_downsweep' -s 4 -c 26 -f -o $out/${tag}_k_scan \
     python benchmarks/sc_sweep.py --lg 28 --iters 2 > $out/${tag}_ncu_scan.log 2>&1
 c5="python bench.py --scene synthetic_4096 --iters-per-step 8 --steps 1 --warmup 1 --skip-extras"
 $c5 > $out/${tag}_c5_plain.json 2> $out/${tag}_c5_plain.err || echo "config-5 plain run failed"

@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-bash benchmarks/profile_config.sh r2y "config4 glass" 20 1 "k_isect"
+bash benchmarks/profile_round.sh r2z

@@ -623,6 +623,9 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
     // kernel and its long, uneven loops no longer hold the shading state hostage: config 5 89.5 -> 102.3
     // spp/s, mesh room 355 -> 411 (profiles/r5_ab_variants.txt).  Same hits, same slot order, same seeds: the
     // image does not change.  Small mesh-free scenes (Cornell) keep the fused persistent kernel.
+#ifndef PT_FUSE_RAYGEN
+#define PT_FUSE_RAYGEN 1     // bounce 0 of the persistent fused kernel generates the camera rays itself (no k_raygen launch)
+#endif
 #ifndef PT_SPLIT_MODE
 #define PT_SPLIT_MODE 2      // 0 = never, 1 = scenes with meshes, 2 = + geometry BVH proper, 3 = always (experiment)
 #endif
@@ -692,7 +695,11 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
         p.iter0 = first_iter + done * iter_stride;
         p.in = pools[0];
         p.out = pools[1];
-        CK(launch_raygen(p, s));
+        // the plain fused pipeline on the persistent kernel generates the camera rays inside bounce 0 (RenderParams::raygen)
+        p.cache_mode = 0;
+        const bool fuse_raygen = PT_FUSE_RAYGEN && !split_only && !sort_on && !cache_on && bounce_is_persistent(p);
+        if (fuse_raygen) CK(launch_batch_init(p, s));
+        else CK(launch_raygen(p, s));
         if (h->profiling) {
             if (h->prof_used >= 8192) { r = collect_profile(h); if (r) return r; }
             cudaEvent_t e;
@@ -708,6 +715,7 @@ int b200pt_render(b200pt* h, int first_iter, int n_iters, int iter_stride, void*
             }
             p.epoch = h->epoch;
             p.cache_mode = (b == 0 && cache_on) ? (h->cache_valid ? 2 : 1) : 0;
+            p.raygen = (b == 0 && fuse_raygen) ? 1 : 0;
             p.perm_shared = 0;
             p.sort_bins = 0;
             if (split_only) {

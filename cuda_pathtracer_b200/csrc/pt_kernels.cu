@@ -447,6 +447,13 @@ __global__ void __launch_bounds__(PT_THREADS) k_raygen(const __grid_constant__ R
     p.in.c[at] = make_float4(s.c.x, s.c.y, s.c.z, __int_as_float(s.bounces));
 }
 
+// the bookkeeping of k_raygen without the rays (bounce 0 of k_bounce generates them itself: RenderParams::raygen)
+__global__ void __launch_bounds__(64) k_batch_init(const __grid_constant__ RenderParams p)
+{
+    for (int sl = threadIdx.x; sl < p.batch; sl += 64) p.counts[sl] = p.P;
+    for (int b = threadIdx.x; b < 2 * p.depth; b += 64) p.tickets[b] = 0;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Pieces shared by the fused bounce kernel and the split (material-sorted) pipeline.
 
@@ -853,7 +860,16 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
         // the reference's shading kernel indexes the sorted arrays (pathtrace.cu:479-497)
         int src = active ? idx : 0;
         if (CACHE == 3 && active && p.perm_in) src = p.perm_in[(p.perm_shared ? (size_t)0 : (size_t)slot * p.P) + idx];
-        PathState s = load_path(p.in, (size_t)slot * p.P + src);
+        // Bounce 0 with the cache off: the camera path is computed here (generateRayFromCamera, pathtrace.cu:184-227, the same
+        // function k_raygen calls) instead of being written by k_raygen and read back -- 96 B per path of HBM traffic and a
+        // launch that was 5.3 % of a Cornell step (profiles/r2z_bench_launches.csv).
+        PathState s;
+        if (CACHE == 0 && p.raygen) {
+            const int y = src / p.cam.W, x = src - y * p.cam.W;
+            s = make_camera_path(p.cam, p.opt, p.iter0 + slot * p.stride, p.depth, x, y);
+        } else {
+            s = load_path(p.in, (size_t)slot * p.P + src);
+        }
 
         HitRec h;
         if (CACHE == 3) {
@@ -1871,6 +1887,12 @@ cudaError_t configure_kernels()
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s)
 {
     k_raygen<<<dim3(p.tiles, p.batch), PT_THREADS, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_batch_init(const RenderParams& p, cudaStream_t s)
+{
+    k_batch_init<<<1, 64, 0, s>>>(p);
     return cudaGetLastError();
 }
 

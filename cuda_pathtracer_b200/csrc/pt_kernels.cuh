@@ -112,6 +112,8 @@ struct RenderParams {
     float4* cache_n;                   // [P] first-bounce cache
     int* cache_k;
     int cache_mode;                    // at bounce 0: 0 = off, 1 = fill, 2 = use
+    int raygen;                        // 1 (bounce 0 of the persistent fused kernel only): the paths of this launch are the camera
+                                       // paths, generated in the kernel instead of loaded (launch_batch_init replaces launch_raygen)
     float2* hit_uv;                    // [batch][P] hit record texture coordinate (mesh hits)
     float2* cache_uv;                  // [P]
     MeshScene mesh;                    // triangle meshes / BVH / textures (n_nodes == 0: none)
@@ -133,6 +135,8 @@ struct LaunchCfg {
 
 size_t bounce_smem_bytes(int n_prims, int n_mats, int n_nodes, int n_gnodes = 0, int n_small = 0);
 cudaError_t launch_raygen(const RenderParams& p, cudaStream_t s);
+// the bookkeeping half of k_raygen alone (live counts = P, ticket counters = 0) for a batch whose bounce 0 generates its own rays
+cudaError_t launch_batch_init(const RenderParams& p, cudaStream_t s);
 cudaError_t launch_bounce(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s);   // fused (honours p.cache_mode)
 // split pipeline: closest hit -> hit records; one radix pass = hist, (scan by the caller), scatter; shade
 // hist_done (may be null): set when the launch also wrote the digit histogram of sort pass 0 (p.sort_bins > 0)
