@@ -149,12 +149,12 @@ __device__ __forceinline__ void hit_attributes(const MeshScene& M, const PrimTai
             if (mh.tri >= 0) { V3 unused; brute_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
         }
     } else if (g.type == 2) {
-        tri_attributes(M.ta[mh.tri], mh.bx, mh.by, n, u, v);
+        tri_attributes(load_attr(M.ta, mh.tri), mh.bx, mh.by, n, u, v);
     } else {
         n = prim_normal(g.itr, g.type, best);
         // (sic) a sphere / cube winning AFTER a mesh primitive accepted the BVH hit carries that
         // hit's stale texture coordinate (pathtrace.cu:267,283)
-        if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(M.ta[mh.tri], mh.bx, mh.by, unused, u, v); }
+        if (owner >= 0 && owner < hit) { V3 unused; tri_attributes(load_attr(M.ta, mh.tri), mh.bx, mh.by, unused, u, v); }
     }
 }
 

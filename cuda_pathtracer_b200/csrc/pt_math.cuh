@@ -390,6 +390,19 @@ __device__ __forceinline__ bool tri_test(const TriVert& T, const V3& o, const V3
     return bt >= 0.0f;
 }
 
+// the 48 bytes of a triangle's vertices as three 16-byte loads (nine 4-byte loads otherwise: in a diverged walk every lane is at
+// another triangle, and each load instruction is 32 tag look-ups)
+__device__ __forceinline__ TriVert load_tri(const TriVert* __restrict__ tv, int at)
+{
+    const float4* q = reinterpret_cast<const float4*>(tv + at);
+    const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    TriVert T;
+    T.v0[0] = a.x; T.v0[1] = a.y; T.v0[2] = a.z; T.id = __float_as_int(a.w);
+    T.v1[0] = b.x; T.v1[1] = b.y; T.v1[2] = b.z; T.pad0 = 0;
+    T.v2[0] = c.x; T.v2[1] = c.y; T.v2[2] = c.z; T.pad1 = 0;
+    return T;
+}
+
 constexpr int BVH_MAX_SEARCH_DEPTH = 64;     // intersections.cu:177
 
 // One traversal of the BVH over ALL meshes' triangles.  The reference runs this once per MESH geom
@@ -400,7 +413,7 @@ constexpr int BVH_MAX_SEARCH_DEPTH = 64;     // intersections.cu:177
 __device__ __forceinline__ void tri_candidate(const MeshScene& M, int at, const V3& o, const V3& d, MeshHit& h)
 {
     float bx, by, bt;
-    if (tri_test(M.tv[at], o, d, bx, by, bt)) {
+    if (tri_test(load_tri(M.tv, at), o, d, bx, by, bt)) {
         h.any = true;
         if (h.t == -1.0f || bt < h.t) {      // strict: the first one met wins a tie
             h.t = bt; h.tri = at; h.bx = bx; h.by = by;
@@ -537,7 +550,7 @@ __device__ __forceinline__ bool mesh_brute(const MeshScene& M, const PrimRec& g,
     const int end = g.pad1 < M.n_tris ? g.pad1 : M.n_tris;
     for (int at = g.pad0; at < end; ++at) {
         float bx, by, bt;
-        if (tri_test(M.tv[at], o, d, bx, by, bt) && bt > 0.0f && bt < h.t) {
+        if (tri_test(load_tri(M.tv, at), o, d, bx, by, bt) && bt > 0.0f && bt < h.t) {
             h.any = true; h.t = bt; h.tri = at; h.bx = bx; h.by = by;
         }
     }
@@ -559,6 +572,19 @@ __device__ __forceinline__ void brute_attributes(const TriAttr& A, float bx, flo
 // Triangle::intersect's attribute interpolation for the closest hit (sceneStructs.h:152-154):
 // uv = uv0*(1-x-y) + uv1*x + uv2*y; normal = normalize(n0*x + n1*y + n2*(1-x-y)) -- the weights of
 // the normal are permuted with respect to the uv's (sic).
+// the 64 bytes of a triangle's attributes as four 16-byte loads
+__device__ __forceinline__ TriAttr load_attr(const TriAttr* __restrict__ ta, int at)
+{
+    const float4* q = reinterpret_cast<const float4*>(ta + at);
+    const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    TriAttr A;
+    A.uv[0][0] = a.x; A.uv[0][1] = a.y; A.uv[1][0] = a.z; A.uv[1][1] = a.w;
+    A.uv[2][0] = b.x; A.uv[2][1] = b.y; A.n[0][0] = b.z; A.n[0][1] = b.w;
+    A.n[0][2] = c.x; A.n[1][0] = c.y; A.n[1][1] = c.z; A.n[1][2] = c.w;
+    A.n[2][0] = d.x; A.n[2][1] = d.y; A.n[2][2] = d.z; A.pad = d.w;
+    return A;
+}
+
 __device__ __forceinline__ void tri_attributes(const TriAttr& A, float bx, float by, V3& n, float& u, float& v)
 {
     const float w = __fsub_rn(__fsub_rn(1.0f, bx), by);
