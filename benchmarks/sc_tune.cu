@@ -643,18 +643,20 @@ int main(int argc, char** argv)
         run_scan<128, 8, 1, false, 0, 16>(e);                 // the one-tile-per-CTA kernel the library uses
         //           ints  stages warps delay nlb window/32
         run_scan_tma<8192, 7, 8, 3, 4, 1>(e);
+        run_scan_tma<7168, 8, 8, 3, 4, 1>(e);                 // finer stages: more of them for the same shared memory
+        run_scan_tma<7168, 8, 8, 4, 4, 1>(e);
+        run_scan_tma<6144, 9, 8, 3, 4, 1>(e);
+        run_scan_tma<6144, 9, 8, 4, 4, 1>(e);
+        run_scan_tma<6144, 9, 8, 5, 6, 1>(e);
+        run_scan_tma<5120, 11, 8, 5, 6, 1>(e);
         run_compact<256, 8, 1, false, 0, 16>(e);
         run_compact_tma<8192, 7, 8, 3, 4, 1>(e);
-        run_compact_tma<8192, 7, 8, 3, 4, 2>(e);
-        run_compact_tma<8192, 7, 8, 3, 6, 1>(e);
-        run_compact_tma<8192, 7, 8, 2, 4, 1>(e);
-        run_compact_tma<8192, 7, 8, 4, 4, 1>(e);
-        run_compact_tma<8192, 6, 8, 2, 4, 1>(e);
-        run_compact_tma<8192, 6, 8, 3, 4, 1>(e);
-        run_compact_tma<8192, 7, 16, 3, 4, 1>(e);
-        run_compact_tma<8192, 7, 4, 3, 4, 1>(e);
-        run_compact_tma<10240, 5, 8, 2, 4, 1>(e);
-        run_compact_tma<4096, 13, 8, 6, 8, 1>(e);
+        run_compact_tma<7168, 8, 8, 3, 4, 1>(e);
+        run_compact_tma<7168, 8, 8, 4, 4, 1>(e);
+        run_compact_tma<6144, 9, 8, 3, 4, 1>(e);
+        run_compact_tma<6144, 9, 8, 4, 4, 1>(e);
+        run_compact_tma<6144, 9, 8, 5, 6, 1>(e);
+        run_compact_tma<5120, 11, 8, 5, 6, 1>(e);
         return 0;
     }
     if (argc > 3 && std::string(argv[3]) == "persist") {      // benchmarks/sc_tune 28 10 persist
