@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 200 benchmarks/sc_tune 28 10 tma > gpurun_out/sc_tune_fine_28.jsonl 2> gpurun_out/sc_tune_fine_28.err; echo "exit $?"
-cat gpurun_out/sc_tune_fine_28.jsonl
+timeout 900 python -m pytest tests/test_pt_gpu.py tests/test_dropin_gpu.py tests/test_host_cli.py -x -q -m gpu > gpurun_out/pytest_pt.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_pt.log
+timeout 900 bash benchmarks/run_ab.sh "" pp

@@ -281,7 +281,7 @@ __device__ __forceinline__ void closest_in_gbvh(const RenderParams& p, const flo
             if (k >= nc) break;
             const PrimRec& g = p.gb.prims[cand_prim[k]];
             ++k;
-            const Cand c = prim_test(g, o, d);
+            const Cand c = prim_test_t<true>(g, o, d);
             const int gi = g.pad0;
             // lexicographic minimum of (t, index): what the ascending loop with strict `<` finds
             if (c.t > 0.0f && (t_min > c.t || (t_min == c.t && gi < hit))) {
@@ -767,6 +767,9 @@ static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it m
 #ifndef PT_BOUNCE_MIN_CTAS
 #define PT_BOUNCE_MIN_CTAS (1024 / PT_BTHREADS)
 #endif
+#ifndef PT_PERM_PREFETCH
+#define PT_PERM_PREFETCH 1
+#endif
 #ifndef PT_LB_K
 #define PT_LB_K 1
 #endif
@@ -849,6 +852,7 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
     // ---- the compute warps ----
     float4* my_stash = stash + warp * 32;            // + k * PT_PTILE for word k of the path
     int prev_cnt = 0, prev_off = 0, prev_slot = 0;
+    int perm_next = 0;                               // CACHE == 3: this thread's permutation entry of the NEXT tile
     int it = 0;
     for (;; ++it) {
         const int slot = sh.item[it & 1][0], tile = sh.item[it & 1][1];    // written before the previous tile's barrier
@@ -859,7 +863,11 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
         // CACHE == 3: slot idx of the (material-sorted) order is source slot perm[idx]; the RNG seed uses idx, exactly as
         // the reference's shading kernel indexes the sorted arrays (pathtrace.cu:479-497)
         int src = active ? idx : 0;
-        if (CACHE == 3 && active && p.perm_in) src = p.perm_in[(p.perm_shared ? (size_t)0 : (size_t)slot * p.P) + idx];
+        // (the permutation entry of every tile but the CTA's first was fetched behind the previous tile's barrier: the gather
+        //  below is then ONE dependent memory round trip per tile instead of two -- 45 % of this mode's stall samples were
+        //  long-scoreboard waits on that chain, profiles/r2x_config4_k_bounce_shade_lines.txt)
+        if (CACHE == 3 && active && p.perm_in)
+            src = (PT_PERM_PREFETCH && it > 0) ? perm_next : p.perm_in[(p.perm_shared ? (size_t)0 : (size_t)slot * p.P) + idx];
         // Bounce 0 with the cache off: the camera path is computed here (generateRayFromCamera, pathtrace.cu:184-227, the same
         // function k_raygen calls) instead of being written by k_raygen and read back -- 96 B per path of HBM traffic and a
         // launch that was 5.3 % of a Cornell step (profiles/r2z_bench_launches.csv).
@@ -910,6 +918,13 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
         if (lane == 0) sh.warp_cnt[it & 1][warp] = cnt;
         if (threadIdx.x == 0) put_item(sh, next_w, (it + 1) & 1);
         asm volatile("bar.sync 1, %0;" ::"n"(PT_PTILE) : "memory");
+        if (PT_PERM_PREFETCH && CACHE == 3 && p.perm_in) {       // the next tile is known now: its permutation entry
+            const int nslot = sh.item[(it + 1) & 1][0];
+            if (nslot >= 0) {
+                const int nidx = sh.item[(it + 1) & 1][1] * PT_PTILE + threadIdx.x;
+                if (nidx < sh.n_live[nslot]) perm_next = p.perm_in[(p.perm_shared ? (size_t)0 : (size_t)nslot * p.P) + nidx];
+            }
+        }
         int warp_prefix = 0, aggregate = 0;
 #pragma unroll
         for (int w = 0; w < PT_PWARPS; ++w) {
@@ -1416,7 +1431,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
                     float t_lo;
                     if (!cull_test(p.gb.crecs[2 * ci], p.gb.crecs[2 * ci + 1], g, o, d, inv, t_lo) || t_lo > t_min) continue;
 #endif
-                    const Cand c = prim_test(g, o, d);
+                    const Cand c = prim_test_t<true>(g, o, d);
                     const int gi = g.pad0;
                     // lexicographic minimum of (t, index): what the ascending loop with strict `<` finds
                     if (c.t > 0.0f && (t_min > c.t || (t_min == c.t && gi < hit))) {

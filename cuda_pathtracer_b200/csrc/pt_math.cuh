@@ -91,7 +91,7 @@ __device__ __forceinline__ float rng_u01(uint32_t& x)
 // ---- scene records ---------------------------------------------------------------------------
 // Compact primitive record (160 B, 16-B aligned) built on the host from struct Geom:
 // column c, row r of a glm::mat4 m is m[c*4 + r]; only rows 0..2 are ever used.
-struct PrimRec {
+struct alignas(16) PrimRec {
     float inv[12];   // inverseTransform  [c*3 + r]
     float fwd[12];   // transform
     float itr[12];   // invTranspose
@@ -101,7 +101,7 @@ struct PrimRec {
 };
 static_assert(sizeof(PrimRec) == 160, "PrimRec must stay 160 bytes");
 
-struct MatRec {      // == struct Material, 48 B
+struct alignas(16) MatRec {      // == struct Material, 48 B
     float color[3];
     float spec_exp;
     float spec_color[3];
@@ -191,32 +191,60 @@ __device__ __forceinline__ bool sphere_test(const V3& ro, const V3& rd, float& t
 
 // One primitive against a world-space ray: what computeIntersections' loop body does through
 // box/sphereIntersectionTest (pathtrace.cu:252-258), minus the normal.
-__device__ __forceinline__ Cand prim_test(const PrimRec& g, const V3& o, const V3& d)
+// GLOBAL: the record is in global memory -- its matrices are then taken with 16-byte ld.global.nc loads (three for the
+// inverse, one for the type word, three more for the forward matrix once the ray has hit) instead of two dozen 4-byte ones:
+// in the tree walks every lane tests another primitive, and each load instruction is 32 tag look-ups.
+template <bool GLOBAL>
+__device__ __forceinline__ Cand prim_test_t(const PrimRec& g, const V3& o, const V3& d)
 {
     Cand c;
     c.t = -1.0f;
     c.outside = true;
     c.aux = v3(0.f, 0.f, 0.f);
-    const V3 qo = xform_point(g.inv, o);
-    const V3 qd = normalize_exact(xform_vector(g.inv, d));
+    float inv[12];
+    int type;
+    const float4* q = reinterpret_cast<const float4*>(&g);
+    if (GLOBAL) {
+        const float4 m0 = __ldg(q), m1 = __ldg(q + 1), m2 = __ldg(q + 2), w = __ldg(q + 9);
+        inv[0] = m0.x; inv[1] = m0.y; inv[2] = m0.z; inv[3] = m0.w; inv[4] = m1.x; inv[5] = m1.y; inv[6] = m1.z; inv[7] = m1.w;
+        inv[8] = m2.x; inv[9] = m2.y; inv[10] = m2.z; inv[11] = m2.w;
+        type = __float_as_int(w.x);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) inv[k] = g.inv[k];
+        type = g.type;
+    }
+    const V3 qo = xform_point(inv, o);
+    const V3 qd = normalize_exact(xform_vector(inv, d));
     float t_obj;
-    if (g.type == 1) {                 // CUBE
+    V3 p;
+    if (type == 1) {                   // CUBE
         V3 n;
         if (!box_test(qo, qd, t_obj, n)) return c;
         c.aux = n;
-        const V3 w = xform_point(g.fwd, point_on_ray(qo, qd, t_obj));
-        c.t = distance_exact(o, w);
-    } else if (g.type == 0) {          // SPHERE
+        p = point_on_ray(qo, qd, t_obj);
+    } else if (type == 0) {            // SPHERE
         bool outside;
         if (!sphere_test(qo, qd, t_obj, outside)) return c;
-        const V3 p = point_on_ray(qo, qd, t_obj);
+        p = point_on_ray(qo, qd, t_obj);
         c.aux = p;
         c.outside = outside;
-        const V3 w = xform_point(g.fwd, p);
-        c.t = distance_exact(o, w);
+    } else {
+        return c;
     }
+    float fwd[12];
+    if (GLOBAL) {
+        const float4 m0 = __ldg(q + 3), m1 = __ldg(q + 4), m2 = __ldg(q + 5);
+        fwd[0] = m0.x; fwd[1] = m0.y; fwd[2] = m0.z; fwd[3] = m0.w; fwd[4] = m1.x; fwd[5] = m1.y; fwd[6] = m1.z; fwd[7] = m1.w;
+        fwd[8] = m2.x; fwd[9] = m2.y; fwd[10] = m2.z; fwd[11] = m2.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) fwd[k] = g.fwd[k];
+    }
+    c.t = distance_exact(o, xform_point(fwd, p));
     return c;
 }
+__device__ __forceinline__ Cand prim_test(const PrimRec& g, const V3& o, const V3& d) { return prim_test_t<false>(g, o, d); }
 
 // normal = normalize(invTranspose * vec4(aux, 0)); the sphere flips it when hit from inside.
 __device__ __forceinline__ V3 prim_normal(const float* __restrict__ itr, int type, const Cand& c)
@@ -301,21 +329,21 @@ __device__ __forceinline__ MatRec load_mat(bool in_shared, unsigned smem_addr, c
     return m;
 }
 
-struct BvhRec {          // class BVHTree (40 B) padded to three 16-byte words
+struct alignas(16) BvhRec {          // class BVHTree (40 B) padded to three 16-byte words
     float lo[3]; int sub_areas;          // min corner | leaf triangle count (0 = inner node)
     float hi[3]; int axis;               // max corner | split axis of an inner node
     int first; int rchild; int pad0, pad1;
 };
 static_assert(sizeof(BvhRec) == 48, "BvhRec must stay 48 bytes");
 
-struct TriVert {         // what the intersection test reads: 48 B
+struct alignas(16) TriVert {         // what the intersection test reads: 48 B
     float v0[3]; int id;                 // id = index before the BVH build reordered the triangles
     float v1[3]; int pad0;
     float v2[3]; int pad1;
 };
 static_assert(sizeof(TriVert) == 48, "TriVert must stay 48 bytes");
 
-struct TriAttr {         // what only the closest hit reads: 64 B
+struct alignas(16) TriAttr {         // what only the closest hit reads: 64 B
     float uv[3][2];
     float n[3][3];
     float pad;
