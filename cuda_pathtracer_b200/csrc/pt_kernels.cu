@@ -1451,8 +1451,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect_dyn(const __grid_constant_
             V3 hn = v3(0.f, 0.f, 0.f);
             int hm = 0;
             if (hit >= 0) {
-                const PrimRec& g = p.prims[hit];
-                hn = prim_normal(g, best);
+                const PrimTail g = load_prim_tail(false, 0u, p.prims + hit);      // (four 16-byte loads)
+                hn = prim_normal(g.itr, g.type, best);
                 ht = t_min;
                 hm = g.material;
             }
