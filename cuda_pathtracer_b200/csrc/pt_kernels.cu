@@ -531,7 +531,10 @@ __device__ __forceinline__ void stage_begin(const RenderParams& p, unsigned long
 // GB: the sphere / cube primitives are searched through the geometry BVH (whose top levels lie
 // where the primitive chunks would) instead of the linear scan.
 // GB: 0 = linear scan over the staged primitive chunks, 1 = geometry BVH, 2 = small-scene search
-template <int GB>
+// MESH = false: the caller knows that the scene has no triangle meshes (the persistent kernel's small-scene mode: launch_bounce
+// sends a small scene WITH meshes to the tile kernel) -- the mesh walk, its visit stack and leaf lists and the triangle
+// attributes are then not compiled into the kernel at all.
+template <int GB, bool MESH = true>
 __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsigned long long* bar, const BvhRec* snodes,
                                                      const PrimRec* sprims, bool active, const V3& o, const V3& d)
 {
@@ -542,7 +545,7 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
     best.t = -1.f; best.outside = true; best.aux = v3(0.f, 0.f, 0.f);
     MeshHit mh = no_mesh_hit(), last = no_mesh_hit();
     int owner = -1;
-    if (GB || p.mesh.n_nodes > 0) mbar_wait(&bar[0], 0u);     // the staged top(s) of the tree(s)
+    if (GB || (MESH && p.mesh.n_nodes > 0)) mbar_wait(&bar[0], 0u);     // the staged top(s) of the tree(s)
     // A ray whose direction is NaN (glm::refract past the critical angle, interactions.cu:68) hits
     // nothing in the reference: every t it computes is NaN and `t > 0` fails.  In a tree such a ray
     // passes every box test (NaN compares false) and would visit all of it: skip the trees, same result.
@@ -553,12 +556,12 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
         if (GB == 2) {
             if (walk) closest_small(sprims, reinterpret_cast<const float4*>(sprims + PT_SMALL_MAX), p.gb.n_small, o, d, t_min, hit, hit_k, best);
         } else if (walk) closest_in_gbvh(p, reinterpret_cast<const float4*>(sprims), o, d, t_min, hit, best);
-        if (p.mesh.n_nodes > 0 && walk) {
+        if (MESH && p.mesh.n_nodes > 0 && walk) {
             const float cap = p.gb.cap_mesh_walk ? prune_limit(t_min) : 3.402823466e+38f;
             mh = bvh_traverse(p.mesh, snodes, o, d, cap);       // one traversal serves every MESH primitive
             closest_among_mesh_prims(p, mh, t_min, hit, owner);
         }
-    } else if (p.mesh.n_nodes > 0 && walk && !p.mesh.brute) {
+    } else if (MESH && p.mesh.n_nodes > 0 && walk && !p.mesh.brute) {
         mh = bvh_traverse(p.mesh, snodes, o, d);
     }
     for (int ch = 0; ch < n_chunks; ++ch) {
@@ -586,7 +589,8 @@ __device__ __forceinline__ HitRec closest_hit_staged(const RenderParams& p, unsi
         // (small-scene search: a MESH winner is not among the staged records -> hit_k stays behind)
         const bool staged = GB == 2 ? (hit_k >= 0 && sprims[hit_k].pad0 == hit) : (GB == 0 && n_chunks <= 1);
         const PrimTail g = load_prim_tail(staged, smem_u32(sprims + (GB == 2 ? hit_k : hit)), p.prims + hit);
-        hit_attributes(p.mesh, g, hit, best, mh, owner, h.n, h.u, h.v);
+        if (MESH) hit_attributes(p.mesh, g, hit, best, mh, owner, h.n, h.u, h.v);
+        else h.n = prim_normal(g.itr, g.type, best);
         h.t = t_min;
         h.mat = g.material;
     }
@@ -767,6 +771,9 @@ static_assert(sizeof(PersistShared) % 16 == 0, "the TMA destinations behind it m
 #ifndef PT_BOUNCE_MIN_CTAS
 #define PT_BOUNCE_MIN_CTAS (1024 / PT_BTHREADS)
 #endif
+#ifndef PT_NO_MESH_SPECIAL
+#define PT_NO_MESH_SPECIAL 1      // the persistent kernel's small-scene mode is compiled without the mesh walk (see closest_hit_staged)
+#endif
 #ifndef PT_PERM_PREFETCH
 #define PT_PERM_PREFETCH 1
 #endif
@@ -896,7 +903,7 @@ __global__ void __launch_bounds__(PT_BTHREADS, PT_BOUNCE_MIN_CTAS) k_bounce(cons
             h.u = cuv.x; h.v = cuv.y;
             mbar_wait(&sh.bar[0], 0u);                // the materials
         } else {
-            h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, s.o, s.d);
+            h = closest_hit_staged<GB, (GB != 2) || !PT_NO_MESH_SPECIAL>(p, sh.bar, snodes, sprims, active, s.o, s.d);
             if (CACHE == 1 && slot == 0 && active) {
                 p.cache_n[idx] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
                 p.cache_k[idx] = h.mat;
@@ -1024,8 +1031,8 @@ __device__ __forceinline__ int warp_digit_rank(SortShared& sh, bool active, int 
 template <int GB>
 __host__ __device__ constexpr int isect_tiles_per_cta() { return GB == 0 ? 1 : PT_ISECT_TILES; }     // (GB == 0 re-arms its chunk barriers per tile)
 
-template <int GB>
-__global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ RenderParams p)
+template <int GB, bool MESH = true>
+__global__ void __launch_bounds__(PT_THREADS, 4) k_isect(const __grid_constant__ RenderParams p)    // (64 registers: four CTAs per SM)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BounceShared& sh = *reinterpret_cast<BounceShared*>(smem_raw);
@@ -1060,7 +1067,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_isect(const __grid_constant__ Re
         const bool active = idx < n_live;
         const size_t at = (size_t)slot * p.P + (active ? idx : 0);
         const float4 a = p.in.a[at], b = p.in.b[at];
-        const HitRec h = closest_hit_staged<GB>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
+        const HitRec h = closest_hit_staged<GB, MESH>(p, sh.bar, snodes, sprims, active, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z));
         if (active) {
             p.hit_n[at] = make_float4(h.t, h.n.x, h.n.y, h.n.z);
             if (bins == 0) p.hit_k[at] = h.mat;
@@ -1892,9 +1899,11 @@ cudaError_t configure_kernels()
     if (e == cudaSuccess) e = allow_smem(k_isect_dyn, (int)(sizeof(DynShared) + (size_t)PT_DYN_GNODES * 2 * sizeof(uint4)));
     if (e == cudaSuccess) e = allow_smem(k_isect_dyn_mesh, cap);
 
-    if (e == cudaSuccess) e = allow_smem(k_isect<0>, cap);
-    if (e == cudaSuccess) e = allow_smem(k_isect<1>, cap);
-    if (e == cudaSuccess) e = allow_smem(k_isect<2>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<0, true>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<1, true>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<2, true>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<1, false>, cap);
+    if (e == cudaSuccess) e = allow_smem(k_isect<2, false>, cap);
     if (e == cudaSuccess) e = allow_smem(k_shade, cap);
     return e;
 }
@@ -2039,9 +2048,13 @@ cudaError_t launch_isect(const RenderParams& p, LaunchCfg& cfg, cudaStream_t s, 
 #endif
     const size_t smem = bounce_smem_bytes(p.n_prims, 0, p.mesh.n_smem_nodes, p.gb.n_smem_nodes, p.gb.n_small);
     const auto grid_for = [&](int per_cta) { return dim3((unsigned)((p.tiles + per_cta - 1) / per_cta), (unsigned)p.batch); };
-    if (mode == 2) k_isect<2><<<grid_for(isect_tiles_per_cta<2>()), PT_THREADS, smem, s>>>(p);
-    else if (mode == 1) k_isect<1><<<grid_for(isect_tiles_per_cta<1>()), PT_THREADS, smem, s>>>(p);
-    else k_isect<0><<<grid_for(isect_tiles_per_cta<0>()), PT_THREADS, smem, s>>>(p);
+    // (a scene without triangle meshes runs the instantiations compiled without the mesh walk: see closest_hit_staged)
+    const bool mesh = p.mesh.n_nodes > 0 || !PT_NO_MESH_SPECIAL;
+    if (mode == 2 && mesh) k_isect<2, true><<<grid_for(isect_tiles_per_cta<2>()), PT_THREADS, smem, s>>>(p);
+    else if (mode == 2) k_isect<2, false><<<grid_for(isect_tiles_per_cta<2>()), PT_THREADS, smem, s>>>(p);
+    else if (mode == 1 && mesh) k_isect<1, true><<<grid_for(isect_tiles_per_cta<1>()), PT_THREADS, smem, s>>>(p);
+    else if (mode == 1) k_isect<1, false><<<grid_for(isect_tiles_per_cta<1>()), PT_THREADS, smem, s>>>(p);
+    else k_isect<0, true><<<grid_for(isect_tiles_per_cta<0>()), PT_THREADS, smem, s>>>(p);
     if (hist_done) *hist_done = p.sort_bins > 0;     // k_isect did the counting half of the sort
     return cudaGetLastError();
 }
