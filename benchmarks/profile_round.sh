@@ -20,8 +20,10 @@ ncu --set full --clock-control none --import-source on -k regex:k_bounce -s 64 -
     python bench.py --steps 1 --warmup 1 --skip-extras > $out/${tag}_ncu_bounce.log 2>&1
 # (sc_sweep at 2^28 launches, five times each: the scan LOOKBACK picks (k_scan_tma), k_scan_lookback, k_scan_tma by name, the work-efficient
 #  pair, the compaction (k_compact_tma); one launch of each kind is kept)
+if [ -z "$SKIP_SCAN" ]; then
 ncu --set full --clock-control none --import-source on -k 'regex:k_scan_tma|k_compact_tma|k_scan_lookback|k_reduce_tiles|k_downsweep' -s 4 -c 26 -f -o $out/${tag}_k_scan \
     python benchmarks/sc_sweep.py --lg 28 --iters 2 > $out/${tag}_ncu_scan.log 2>&1
+fi
 c5="python bench.py --scene synthetic_4096 --iters-per-step 8 --steps 1 --warmup 1 --skip-extras"
 $c5 > $out/${tag}_c5_plain.json 2> $out/${tag}_c5_plain.err || echo "config-5 plain run failed"
 ncu --set full --clock-control none --import-source on -k 'regex:k_isect_dyn|k_bounce' -s 32 -c 32 -f -o $out/${tag}_c5 \
@@ -30,7 +32,7 @@ ncu -i $out/${tag}_c5.ncu-rep --page raw --csv > $out/${tag}_c5_raw.csv 2>/dev/n
 python benchmarks/ncu_traffic.py $out/${tag}_c5_raw.csv $out/${tag}_synthetic_4096_traffic.json 'k_isect_dyn|k_bounce' 2
 rm -f $out/${tag}_c5.ncu-rep
 for k in k_bounce k_scan; do
-  ncu -i $out/${tag}_${k}.ncu-rep --page raw --csv > $out/${tag}_${k}_raw.csv 2>/dev/null
+  [ -f $out/${tag}_${k}.ncu-rep ] && ncu -i $out/${tag}_${k}.ncu-rep --page raw --csv > $out/${tag}_${k}_raw.csv 2>/dev/null
 done
 python benchmarks/ncu_traffic.py $out/${tag}_k_bounce_raw.csv $out/${tag}_k_bounce_traffic.json
 # (the source page of 16 launches is > 100 MB and gpurun brings back at most 64 MiB: benchmarks/profile_config.sh
