@@ -226,13 +226,22 @@ int b200_scan_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int va
         if (variant == B200_SCAN_LOOKBACK_RING && !ring_ok) return B200_E_BADARG;
         const bool wave_ok = scan_wave_usable(un, c->num_sms);
         if (variant == B200_SCAN_LOOKBACK_WAVE && !wave_ok) return B200_E_BADARG;
-        const bool ring = variant == B200_SCAN_LOOKBACK_RING || (variant == B200_SCAN_LOOKBACK && ring_ok && un >= c->ring_min_n);
+        bool ring = variant == B200_SCAN_LOOKBACK_RING || (variant == B200_SCAN_LOOKBACK && ring_ok && un >= c->ring_min_n);
         const bool wave = variant == B200_SCAN_LOOKBACK_WAVE || (variant == B200_SCAN_LOOKBACK && !ring && wave_ok && un >= SC_WAVE_MIN_N);
         int r = ensure_lookback(c, un);
         if (r) return r;
-        if (wave) CK(launch_scan_wave(d_in, d_out, un, c->desc, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
-        else if (ring) CK(launch_scan_ring(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, c->num_sms, s));
-        else CK(launch_scan_lookback(d_in, d_out, un, c->desc, c->tickets, next_epoch(c, s), d_seed, d_total, s));
+        const unsigned epoch = next_epoch(c, s);
+        if (wave) {
+            CK(launch_scan_wave(d_in, d_out, un, c->desc, epoch, d_seed, d_total, c->num_sms, s));
+        } else {
+            cudaError_t e = cudaErrorLaunchOutOfResources;
+            if (ring) e = launch_scan_ring(d_in, d_out, un, c->desc, c->tickets, epoch, d_seed, d_total, c->num_sms, s);
+            // a device whose shared memory cannot hold the ring (nothing was launched): the register-tile kernel, unless the ring
+            // was asked for by name
+            if (ring && e == cudaErrorLaunchOutOfResources && variant == B200_SCAN_LOOKBACK) { cudaGetLastError(); ring = false; }
+            if (!ring) e = launch_scan_lookback(d_in, d_out, un, c->desc, c->tickets, epoch, d_seed, d_total, s);
+            CK(e);
+        }
         c->last_launches = 1;
         return 0;
     }
@@ -271,10 +280,15 @@ int b200_compact_i32_dev(b200_sc_ctx* c, int n, int* d_out, const int* d_in, int
     if (n == 0) { CK(cudaMemsetAsync(d_count, 0, sizeof(int), s)); return 0; }
     int r = ensure_lookback(c, (unsigned)n);
     if (r) return r;
-    if (compact_ring_usable(d_in) && (unsigned)n >= c->ring_min_n)
-        CK(launch_compact_ring(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
-    else
-        CK(launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, next_epoch(c, s), d_count, c->num_sms, s));
+    const unsigned epoch = next_epoch(c, s);
+    cudaError_t e = cudaErrorLaunchOutOfResources;
+    const bool ring = compact_ring_usable(d_in) && (unsigned)n >= c->ring_min_n;
+    if (ring) e = launch_compact_ring(d_in, d_out, (unsigned)n, c->desc, c->tickets, epoch, d_count, c->num_sms, s);
+    if (!ring || e == cudaErrorLaunchOutOfResources) {     // (no ring on this device: nothing was launched)
+        if (ring) cudaGetLastError();
+        e = launch_compact_lookback(d_in, d_out, (unsigned)n, c->desc, c->tickets, epoch, d_count, c->num_sms, s);
+    }
+    CK(e);
     c->last_launches = 1;
     return 0;
 }

@@ -137,6 +137,7 @@ cudaError_t launch_scan_ring(const int* d_in, int* d_out, unsigned n, unsigned l
         int a = 0;
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k, threads, smem);
+        if (e == cudaErrorInvalidValue) { cudaGetLastError(); a = 0; e = cudaSuccess; }   // more shared memory than the device has
         if (e != cudaSuccess) return e;
         per_sm_of[dev] = a > 0 ? a : -1;
     }
@@ -167,6 +168,7 @@ cudaError_t launch_compact_ring(const int* d_in, int* d_out, unsigned n, unsigne
         int a = 0;
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k, threads, smem);
+        if (e == cudaErrorInvalidValue) { cudaGetLastError(); a = 0; e = cudaSuccess; }   // more shared memory than the device has
         if (e != cudaSuccess) return e;
         per_sm_of[dev] = a > 0 ? a : -1;
     }

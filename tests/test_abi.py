@@ -83,3 +83,22 @@ def test_product_does_not_reference_oracle(repo_root):
     for line in mk.splitlines():
         if "$(NVCC)" in line or line.startswith(("SC_", "PT_")):
             assert "oracle" not in line, line
+
+
+def test_python_mirror_matches_the_header_enums(repo_root):
+    """the scan-variant selectors and error codes of the ctypes mirror are the header's"""
+    import re
+    from cuda_pathtracer_b200 import stream_compaction as sc
+    text = open(os.path.join(repo_root, "include", "b200_sc.h")).read()
+    vals = {m.group(1): int(m.group(2)) for m in re.finditer(r"\b(B200_[A-Z_]+)\s*=\s*(\d+)", text)}
+    assert vals["B200_SCAN_LOOKBACK"] == sc.LOOKBACK and vals["B200_SCAN_EFFICIENT"] == sc.EFFICIENT
+    assert vals["B200_SCAN_NAIVE"] == sc.NAIVE and vals["B200_SCAN_LOOKBACK_TILE"] == sc.LOOKBACK_TILE
+    assert vals["B200_SCAN_LOOKBACK_RING"] == sc.LOOKBACK_RING and vals["B200_SCAN_LOOKBACK_WAVE"] == sc.LOOKBACK_WAVE
+    assert vals["B200_E_TOOLARGE"] == sc.E_TOOLARGE
+
+
+def test_ring_knob_rejects_bad_arguments_without_a_device():
+    """b200_sc_ctx_set_ring_min_n checks its arguments before it touches anything"""
+    lib = pkg.load("libb200sc.so")
+    lib.b200_sc_ctx_set_ring_min_n.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    assert lib.b200_sc_ctx_set_ring_min_n(None, 1) == 10001          # B200_E_BADARG
